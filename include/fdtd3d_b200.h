@@ -1,0 +1,192 @@
+/*
+ * fdtd3d_b200 -- C ABI of the B200-native Yee-grid leapfrog time step.
+ *
+ * This header is the drop-in boundary.  It replaces, for the GPU path, the C++
+ * entry points of the reference's Source/Cuda/CudaInterface.{h,cu}; every declaration below cites
+ * the reference interface it stands in for (paths relative to the reference repository root).
+ * Plain C: POD structs, raw pointers and sizes only -- no C++ or torch types cross this line.
+ *
+ * Conventions
+ *   - Every function returns 0 on success and a non-zero fdtd_status otherwise; the message of the
+ *     last failure on the calling thread is available from fdtd_last_error().  The library never
+ *     calls exit() (the reference does: Source/Cuda/CudaDefines.h:10-19).
+ *   - "FPValue" is float or double (cfg.value_type = 4 or 8; Source/Kernels/FieldValue.h:7-17),
+ *     "FieldValue" is FPValue or an interleaved (re,im) pair of FPValue when cfg.complex_values
+ *     is set (Source/Kernels/FieldValue.h:22-27).
+ *   - Host arrays are in the reference's linear order unless FDTD_ORDER_NATIVE is requested:
+ *     3D  index = (i*Ny + j)*Nz + k   (Source/Grid/Grid.cpp:138, z fastest)
+ *     2D  index =  i*Ny + j           (Source/Grid/Grid.cpp:82)
+ *   - One value per cell per field crosses the boundary (the `cur` layer); after a run
+ *     prev == cur in the reference, so that is the complete state.
+ */
+#ifndef FDTD3D_B200_H
+#define FDTD3D_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FDTD3D_B200_ABI_VERSION 1
+
+/* Return codes.  FDTD_OK/FDTD_ERROR mirror CudaExitStatus {CUDA_OK, CUDA_ERROR}
+ * (Source/Cuda/CudaDefines.h:4-8); the others refine CUDA_ERROR. */
+typedef enum fdtd_status
+{
+  FDTD_OK = 0,
+  FDTD_ERROR = 1,            /* CUDA runtime / launch failure (message has the CUDA error string) */
+  FDTD_INVALID_ARGUMENT = 2, /* bad config, field id, size or pointer */
+  FDTD_NO_DEVICE = 3,        /* no usable CUDA device: there is no CPU fallback */
+  FDTD_COMM_ERROR = 4        /* NCCL failure or halo exchange requested without a communicator */
+} fdtd_status;
+
+/* Field identifiers.  Order of the E/H/D/B block follows Scheme3D's members
+ * (Source/Scheme/Scheme3D.h:21-33). */
+typedef enum fdtd_field
+{
+  FDTD_EX = 0, FDTD_EY = 1, FDTD_EZ = 2,
+  FDTD_HX = 3, FDTD_HY = 4, FDTD_HZ = 5,
+  FDTD_DX = 6, FDTD_DY = 7, FDTD_DZ = 8,   /* UPML auxiliary fields, only with use_pml */
+  FDTD_BX = 9, FDTD_BY = 10, FDTD_BZ = 11,
+  FDTD_EPS = 12, FDTD_MU = 13,             /* material grids, size N+1 per axis, FPValue (real part) */
+  FDTD_EINC = 14, FDTD_HINC = 15,          /* 1-D incident-wave line, only with use_tfsf */
+  FDTD_FIELD_COUNT = 16
+} fdtd_field;
+
+typedef enum fdtd_order
+{
+  FDTD_ORDER_REFERENCE = 0, /* z fastest (3D) / y fastest (2D): Source/Grid/Grid.cpp:82,138 */
+  FDTD_ORDER_NATIVE = 1     /* x fastest, unpadded: ((k*Ny)+j)*Nx + i -- the device's own order */
+} fdtd_order;
+
+/*
+ * Everything the time step needs that is not an array.  It carries what the reference passes to
+ * cudaExecute3DSteps / cudaExecute2DTMzSteps (Source/Cuda/CudaInterface.cu:356-368, 20-29: layout,
+ * dt, dx, totalStep, processId) plus the Scheme members the reference's CUDA path ignores because
+ * it asserts on PML/TFSF (Source/Scheme/Scheme3D.cpp:3346-3349).
+ * All FPValue-typed quantities are passed as double holding the exact FPValue value.
+ */
+typedef struct fdtd_config
+{
+  int32_t abi_version;     /* FDTD3D_B200_ABI_VERSION */
+  int32_t dims;            /* 3: Scheme3D (GRID_3D); 2: SchemeTMz (GRID_2D), fields Ez,Hx,Hy,Dz,Bx,By */
+  int32_t value_type;      /* 4: VALUE_TYPE f; 8: VALUE_TYPE d (sizeof FPValue) */
+  int32_t complex_values;  /* COMPLEX_FIELD_VALUES */
+  int32_t use_pml;         /* --use-pml  (Scheme3D::usePML)  */
+  int32_t use_tfsf;        /* --use-tfsf (Scheme3D::useTFSF); when 0 the point source is active */
+  int32_t exact_mode;      /* 1: reference evaluation order, IEEE division per cell, no FMA contraction
+                              (bit-for-bit with the reference CPU solver in double);
+                              0: reciprocal tables + FMA (within the stated tolerance) */
+  int32_t device;          /* CUDA device ordinal; cudaInit(device) of Source/Cuda/CudaInterface.cu:934 */
+
+  int64_t size[3];         /* --sizex/y/z; size[2] must be 1 for dims == 2 */
+  int64_t pml_size[3];     /* --pml-sizex/y/z (YeeGridLayout::leftBorderPML) */
+  int64_t tfsf_size[3];    /* --tfsf-sizex/y/z (YeeGridLayout::leftBorderTotalField) */
+  int64_t source_pos[3];   /* point-source cell: (Nx/2,Ny/2,Nz/2) in Scheme3D.cpp:2011-2013,
+                              (70,Ny/2) in SchemeTMz.cpp:1347 */
+
+  double dx;               /* gridStep */
+  double dt;               /* gridTimeStep */
+  double source_frequency; /* sourceFrequency */
+  double rel_phase_velocity; /* Scheme3D::relPhaseVelocity (Scheme3D.cpp:3401);
+                                for dims == 2 the relPhi of SchemeTMz.cpp:35-49 */
+  double angle_teta;       /* YeeGridLayout::incidentWaveAngle1, radians */
+  double angle_phi;        /* incidentWaveAngle2 */
+  double angle_psi;        /* incidentWaveAngle3 */
+
+  /* z-slab decomposition over the GPUs of one box (replaces ParallelGrid's MPI exchange,
+   * Source/Grid/ParallelGrid.cpp:1817-1823).  rank r owns planes [r*(Nz/n), ...), the last rank
+   * takes the remainder (Source/Layout/ParallelYeeGridLayout.cpp:24-36).  nranks == 1: no exchange. */
+  int32_t rank;
+  int32_t nranks;
+
+  int64_t time_step_start; /* value of t for the first step of the next fdtd_run (performNSteps' startStep) */
+} fdtd_config;
+
+typedef struct fdtd_solver *fdtd_handle;
+
+/* Message of the last failure on this thread ("" if none). */
+const char *fdtd_last_error (void);
+
+/* cudaInfo() of Source/Cuda/CudaInterface.cu:939-959: writes a one-line description of `device`
+ * (name, SM count, memory, theoretical bandwidth) into buf. */
+int fdtd_device_info (int device, char *buf, int64_t buflen);
+
+/* Allocates the device-resident state of one Scheme (all fields zero, eps = mu = 1, sigma = 0).
+ * Stands in for the cudaMalloc block of cudaExecute3DSteps (Source/Cuda/CudaInterface.cu:420-470),
+ * but the handle keeps the memory between calls so the timed loop has no allocation or copy. */
+int fdtd_create (const fdtd_config *cfg, fdtd_handle *out);
+int fdtd_destroy (fdtd_handle h);
+
+/* 1-D PML conductivity profile along `axis` (0,1,2), length size[axis]+1, FPValue-typed: the
+ * profile Scheme3D::initGrids writes into the SigmaX/Y/Z grids (Source/Scheme/Scheme3D.cpp:3656-3818;
+ * sigma_x depends on i only, etc.).  Rebuilds the coefficient tables. */
+int fdtd_set_sigma (fdtd_handle h, int axis, const void *profile, int64_t count);
+
+/* Host -> device / device -> host copy of one field for global planes [z0, z0+nz) (dims == 2:
+ * z0 = 0, nz = 1).  Planes outside this rank's slab are ignored.  Replaces the flatten + cudaMemcpy
+ * blocks of Source/Cuda/CudaInterface.cu:492-561 and 816-873.  Host element type: FieldValue for
+ * E/H/D/B/EINC/HINC, FPValue for EPS/MU.  For EINC/HINC the whole line is copied (z0, nz ignored). */
+int fdtd_upload (fdtd_handle h, int field, const void *host, int order, int64_t z0, int64_t nz);
+int fdtd_download (fdtd_handle h, int field, void *host, int order, int64_t z0, int64_t nz);
+
+/* Sets every cell of a field to (re, im). */
+int fdtd_fill (fdtd_handle h, int field, double re, double im);
+
+/* eps := Approximation::approximateSphere (Source/Layout/Approximation.cpp:303-331) evaluated on
+ * the device at every material cell, as Scheme3D::initGrids does (Source/Scheme/Scheme3D.cpp:3413-3442). */
+int fdtd_init_eps_sphere (fdtd_handle h, double cx, double cy, double cz, double radius, double eps_inside);
+
+/* Runs nsteps leapfrog steps: Scheme3D::performNSteps (Source/Scheme/Scheme3D.cpp:1966-2069) or
+ * SchemeTMz::performNSteps (Source/Scheme/SchemeTMz.cpp:1311-1563).  This is what
+ * cudaExecute3DSteps' `while (t < totalStep)` loop does (Source/Cuda/CudaInterface.cu:490-814),
+ * here with PML, TFSF and the reference's point source.  fdtd_run blocks until the steps are done;
+ * fdtd_run_async only enqueues them on the solver's stream and fdtd_sync waits. */
+int fdtd_run (fdtd_handle h, int64_t nsteps);
+int fdtd_run_async (fdtd_handle h, int64_t nsteps);
+int fdtd_sync (fdtd_handle h);
+
+/* Device time of the last completed fdtd_run / fdtd_run_async+fdtd_sync, from CUDA events on the
+ * solver's stream (milliseconds). */
+int fdtd_last_run_ms (fdtd_handle h, float *ms);
+
+/* Number of kernels of this library launched by this handle since creation (bench.py's gpu_launches). */
+int fdtd_launch_count (fdtd_handle h, int64_t *count);
+
+/* Current value of t (number of steps done + time_step_start). */
+int fdtd_get_time_step (fdtd_handle h, int64_t *t);
+
+/* sum over this rank's cells of |cur|^2 of a field, accumulated in double (diagnostic used by the
+ * parity tests at sizes where a full download is impractical; the known-answer vectors of
+ * SURVEY.md §8c are quoted in this form). */
+int fdtd_field_sumsq (fdtd_handle h, int field, double *out);
+
+/* Multi-GPU: NCCL communicator for the z-slab halo exchange (one rank per GPU).  Rank 0 calls
+ * fdtd_comm_unique_id and distributes the 128 bytes out of band (torch.distributed, a file, ...);
+ * then every rank calls fdtd_comm_init with the same id.  Replaces ParallelGridCore's MPI setup
+ * (Source/Grid/ParallelGridCore.cpp) and ParallelGrid::share (Source/Grid/ParallelGrid.cpp:1817). */
+int fdtd_comm_unique_id (void *id128);
+int fdtd_comm_init (fdtd_handle h, const void *id128);
+
+/* Host arrays for the one-shot call below; any pointer may be NULL (field starts at zero and is not
+ * copied back; eps/mu default to 1; sigma to 0). */
+typedef struct fdtd_host_arrays
+{
+  void *field[12];        /* indexed by fdtd_field FDTD_EX..FDTD_BZ, FieldValue, reference order, in/out */
+  const void *eps;        /* FPValue, (Nx+1)(Ny+1)(Nz+1), reference order */
+  const void *mu;
+  const void *sigma[3];   /* FPValue 1-D profiles, size[axis]+1 */
+  void *einc, *hinc;      /* FieldValue, 100*(Nx+Ny+Nz) cells (Source/Scheme/Scheme3D.h:278-279), in/out */
+} fdtd_host_arrays;
+
+/* One-shot drop-in for cudaExecute3DSteps / cudaExecute2DTMzSteps
+ * (Source/Cuda/CudaInterface.cu:356-932, 20-339): allocate, upload host arrays, run total_steps,
+ * copy everything back, free.  *status receives FDTD_OK / FDTD_ERROR like CudaExitStatus *retval. */
+int fdtd_execute_steps (int *status, const fdtd_config *cfg, fdtd_host_arrays *arrays, int64_t total_steps);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* FDTD3D_B200_H */
