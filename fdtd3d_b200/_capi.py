@@ -62,6 +62,8 @@ class HostArrays(C.Structure):
 PROTOTYPES = {
     "fdtd_last_error": (C.c_char_p, []),
     "fdtd_device_info": (C.c_int, [C.c_int, C.c_char_p, C.c_int64]),
+    "fdtd_init_scheme": (C.c_int, [C.POINTER(Config), C.c_double, C.c_double, C.c_double, C.c_double]),
+    "fdtd_pml_sigma_profile": (C.c_int, [C.POINTER(Config), C.c_int, C.c_void_p, C.c_int64]),
     "fdtd_create": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_void_p)]),
     "fdtd_destroy": (C.c_int, [C.c_void_p]),
     "fdtd_set_sigma": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int64]),
@@ -73,6 +75,8 @@ PROTOTYPES = {
     "fdtd_run_async": (C.c_int, [C.c_void_p, C.c_int64]),
     "fdtd_sync": (C.c_int, [C.c_void_p]),
     "fdtd_last_run_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "fdtd_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
+    "fdtd_phase_times": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
     "fdtd_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "fdtd_get_time_step": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "fdtd_field_sumsq": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),

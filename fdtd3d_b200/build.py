@@ -1,0 +1,66 @@
+"""Builds libfdtd3d_b200.so (CUDA kernels + C ABI) in-tree with nvcc for sm_100a.
+
+nvcc cross-compiles without a GPU, so this also runs in the CPU-only build container; the resulting
+.so travels to the GPU box with the repository snapshot.  -fmad=false: exact mode must not contract
+a*b+c into FMA (fast-mode code uses explicit fma intrinsics); host code gets -ffp-contract=off for
+the same reason (coefficient tables).
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+BUILD = os.path.join(CSRC, "build")
+LIB = os.path.join(HERE, "libfdtd3d_b200.so")
+SOURCES = ["kernels3d.cu", "kernels2d.cu", "aux_kernels.cu", "solver.cu", "scheme_init.cpp"]
+HEADERS = ["fdtd_device.cuh", "launch.h", "nccl_dl.h", os.path.join("..", "..", "include", "fdtd3d_b200.h")]
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
+    "-ccbin", "/usr/bin/g++", "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-Xptxas", "-v",
+]
+
+
+def _newer(src, dst):
+    return not os.path.exists(dst) or os.path.getmtime(src) > os.path.getmtime(dst)
+
+
+def build(force=False, verbose=False):
+    os.makedirs(BUILD, exist_ok=True)
+    hdr_paths = [os.path.normpath(os.path.join(CSRC, h)) for h in HEADERS] + [os.path.abspath(__file__)]
+    jobs = []
+    for src in SOURCES:
+        sp = os.path.join(CSRC, src)
+        obj = os.path.join(BUILD, src + ".o")
+        if force or _newer(sp, obj) or any(_newer(h, obj) for h in hdr_paths):
+            jobs.append((sp, obj))
+
+    def compile_one(job):
+        sp, obj = job
+        cmd = [NVCC] + NVCC_FLAGS + ["-c", sp, "-o", obj]
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        with open(obj + ".log", "w") as f:
+            f.write(" ".join(cmd) + "\n" + r.stdout)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed for %s:\n%s" % (sp, r.stdout[-8000:]))
+        return r.stdout
+
+    if jobs:
+        with ThreadPoolExecutor(max_workers=4) as ex:
+            outs = list(ex.map(compile_one, jobs))
+        if verbose:
+            for o in outs:
+                sys.stdout.write(o)
+    objs = [os.path.join(BUILD, s + ".o") for s in SOURCES]
+    if jobs or not os.path.exists(LIB):
+        cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-ccbin", "/usr/bin/g++", "-Xcompiler", "-fPIC", "-ldl"]
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("link failed:\n" + r.stdout)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

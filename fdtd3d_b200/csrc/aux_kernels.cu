@@ -1,0 +1,315 @@
+/*
+ * Small kernels around the two half-step kernels: the 1-D incident-wave line, the step counter,
+ * host-order <-> device-layout conversion, fills, the eps sphere and the |field|^2 reduction.
+ * Compiled with -fmad=false like the rest (exact mode relies on it).
+ */
+#include "fdtd_device.cuh"
+#include "launch.h"
+
+namespace fdtd
+{
+
+namespace
+{
+
+/* ------------------------------------------------------------------ 1-D incident line */
+
+/* Scheme3D::performPlaneWaveESteps, Scheme3D.cpp:24-59: E[i] = E[i] + ce * (H[i-1] - H[i]) for i >= 1,
+ * E[0] = source sample of this step.  In place: the sweep reads only H and the cell's own E. */
+template <typename T, int NC, bool EXACT>
+__global__ void incident_e (const StepParams<T> p)
+{
+  const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.ninc) return;
+  if (i == 0)
+  {
+    const long long s = *p.step;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) p.einc[c] = p.src[s * NC + c];
+    return;
+  }
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
+  {
+    const T e = p.einc[i * NC + c];
+    const T d = p.hinc[(i - 1) * NC + c] - p.hinc[i * NC + c];
+    p.einc[i * NC + c] = EXACT ? e + p.inc_ce * d : fma_t<T> (p.inc_ce, d, e);
+  }
+}
+
+/* Scheme3D::performPlaneWaveHSteps, Scheme3D.cpp:61-82: H[i] = H[i] + ch * (E[i] - E[i+1]), i < n-1 */
+template <typename T, int NC, bool EXACT>
+__global__ void incident_h (const StepParams<T> p)
+{
+  const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.ninc - 1) return;
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
+  {
+    const T h = p.hinc[i * NC + c];
+    const T d = p.einc[i * NC + c] - p.einc[(i + 1) * NC + c];
+    p.hinc[i * NC + c] = EXACT ? h + p.inc_ch * d : fma_t<T> (p.inc_ch, d, h);
+  }
+}
+
+__global__ void tick_kernel (long long *step) { *step += 1; }
+
+/* ------------------------------------------------------------------ layout conversion */
+
+/* 32x32 tiled transpose between the k-fastest staged block and the i-fastest device layout, one j per
+ * blockIdx.y.  CellT = uint32_t / uint64_t / int4. */
+template <typename CellT, bool TO_DEVICE>
+__global__ void reorder_kernel (CellT *dev, CellT *staged, int ia, int ib, int ny, int nzb, int pitch, long long ps,
+                                int kofs, int kmin, int kmax)
+{
+  __shared__ CellT tile[32][33];
+  const int j = blockIdx.y;
+  const int kt = blockIdx.x * 32, it = ia + blockIdx.z * 32;
+  if (TO_DEVICE)
+  {
+    for (int r = threadIdx.y; r < 32; r += blockDim.y)
+    {
+      const int i = it + r, k = kt + threadIdx.x;
+      if (i < ib && k < nzb) tile[r][threadIdx.x] = staged[((long long) (i - ia) * ny + j) * nzb + k];
+    }
+    __syncthreads ();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y)
+    {
+      const int k = kt + r, i = it + threadIdx.x;
+      const int kd = k + kofs;
+      if (i < ib && k < nzb && kd >= kmin && kd < kmax) dev[((long long) kd * ny + j) * pitch + i] = tile[threadIdx.x][r];
+    }
+  }
+  else
+  {
+    for (int r = threadIdx.y; r < 32; r += blockDim.y)
+    {
+      const int k = kt + r, i = it + threadIdx.x;
+      const int kd = k + kofs;
+      if (i < ib && k < nzb && kd >= kmin && kd < kmax) tile[threadIdx.x][r] = dev[((long long) kd * ny + j) * pitch + i];
+    }
+    __syncthreads ();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y)
+    {
+      const int i = it + r, k = kt + threadIdx.x;
+      const int kd = k + kofs;
+      if (i < ib && k < nzb && kd >= kmin && kd < kmax) staged[((long long) (i - ia) * ny + j) * nzb + k] = tile[r][threadIdx.x];
+    }
+  }
+}
+
+template <typename CellT, bool TO_DEVICE>
+__global__ void repitch_kernel (CellT *dev, CellT *staged, int nx, long long nrows, int pitch)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nx) return;
+  for (long long r = blockIdx.y; r < nrows; r += gridDim.y)
+  {
+    if (TO_DEVICE) dev[r * pitch + i] = staged[r * nx + i];
+    else staged[r * nx + i] = dev[r * pitch + i];
+  }
+}
+
+template <typename CellT>
+__global__ void fill_kernel (CellT *dev, long long count, CellT value)
+{
+  for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long) gridDim.x * blockDim.x)
+    dev[i] = value;
+}
+
+/* Approximation::approximateSphere, Approximation.cpp:303-331, at material cell real coordinate m + 0.5
+ * (YeeGridLayout.h:267-270); sqrt is the C double function there, rounded once to FPValue. */
+template <typename T>
+__global__ void eps_sphere_kernel (T *eps, int mx, int my, int nzm, int kz0, int pitchM, long long psM, T cx, T cy, T cz,
+                                   T radius, T eps_in)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  if (i >= mx) return;
+  for (int kl = blockIdx.z; kl < nzm; kl += gridDim.z)
+  {
+    const T px = (T) i + (T) 0.5, py = (T) j + (T) 0.5, pz = (T) (kz0 + kl) + (T) 0.5;
+    const T dxv = px - cx, dyv = py - cy, dzv = pz - cz;
+    const T sum = dxv * dxv + dyv * dyv + dzv * dzv;
+    const T d = (T) sqrt ((double) sum);
+    const T diff = d - radius;
+    T v;
+    if (diff < (T) -0.5) v = eps_in;
+    else if (diff > (T) 0.5) v = (T) 1;
+    else
+    {
+      const T prop = (T) 0.5 - diff;
+      v = prop * eps_in + ((T) 1 - prop) * (T) 1;
+    }
+    eps[(long long) (kl + 1) * psM + (long long) j * pitchM + i] = v;
+  }
+}
+
+/* ------------------------------------------------------------------ reduction */
+
+constexpr int SUMSQ_CTAS = 1184; /* 148 SMs x 8 */
+constexpr int SUMSQ_THREADS = 256;
+
+template <typename T>
+__global__ void __launch_bounds__ (SUMSQ_THREADS)
+sumsq_partial (const T *base, int nscal, long long nrows, long long pitch_scal, double *partials)
+{
+  __shared__ double red[SUMSQ_THREADS / 32];
+  double acc = 0.0;
+  for (long long r = blockIdx.x; r < nrows; r += gridDim.x)
+  {
+    const T *rowp = base + r * pitch_scal;
+    for (int s = threadIdx.x; s < nscal; s += SUMSQ_THREADS)
+    {
+      const double v = (double) rowp[s];
+      acc += v * v;
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) acc += __shfl_down_sync (0xffffffffu, acc, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads ();
+  if (threadIdx.x == 0)
+  {
+    double t = 0.0;
+    for (int w = 0; w < SUMSQ_THREADS / 32; ++w) t += red[w];
+    partials[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__ (SUMSQ_THREADS)
+sumsq_final (const double *partials, int n, double *out)
+{
+  __shared__ double red[SUMSQ_THREADS];
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < n; i += SUMSQ_THREADS) acc += partials[i];
+  red[threadIdx.x] = acc;
+  __syncthreads ();
+  for (int s = SUMSQ_THREADS / 2; s > 0; s >>= 1)
+  {
+    if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+    __syncthreads ();
+  }
+  if (threadIdx.x == 0) *out = red[0];
+}
+
+template <typename CellT>
+cudaError_t reorder_t (bool to_device, void *dev, void *staged, int ia, int ib, int ny, int nzb, int pitch, long long ps,
+                       int kofs, int kmin, int kmax, cudaStream_t stream)
+{
+  dim3 block (32, 8);
+  dim3 grid ((nzb + 31) / 32, ny, (ib - ia + 31) / 32);
+  if (to_device)
+    reorder_kernel<CellT, true><<<grid, block, 0, stream>>> ((CellT *) dev, (CellT *) staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax);
+  else
+    reorder_kernel<CellT, false><<<grid, block, 0, stream>>> ((CellT *) dev, (CellT *) staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax);
+  return cudaGetLastError ();
+}
+
+template <typename CellT>
+cudaError_t repitch_t (bool to_device, void *dev, void *staged, int nx, long long nrows, int pitch, cudaStream_t stream)
+{
+  dim3 block (128);
+  dim3 grid ((nx + 127) / 128, (unsigned) (nrows < 16384 ? nrows : 16384));
+  if (to_device) repitch_kernel<CellT, true><<<grid, block, 0, stream>>> ((CellT *) dev, (CellT *) staged, nx, nrows, pitch);
+  else repitch_kernel<CellT, false><<<grid, block, 0, stream>>> ((CellT *) dev, (CellT *) staged, nx, nrows, pitch);
+  return cudaGetLastError ();
+}
+
+} /* namespace */
+
+template <typename T>
+cudaError_t launch_incident (bool e_phase, const StepParams<T> &p, bool cplx, bool exact, cudaStream_t stream)
+{
+  const int threads = 256;
+  const int blocks = (int) ((p.ninc + threads - 1) / threads);
+  const int key = (e_phase ? 4 : 0) | (cplx ? 2 : 0) | (exact ? 1 : 0);
+  switch (key)
+  {
+    case 0: incident_h<T, 1, false><<<blocks, threads, 0, stream>>> (p); break;
+    case 1: incident_h<T, 1, true><<<blocks, threads, 0, stream>>> (p); break;
+    case 2: incident_h<T, 2, false><<<blocks, threads, 0, stream>>> (p); break;
+    case 3: incident_h<T, 2, true><<<blocks, threads, 0, stream>>> (p); break;
+    case 4: incident_e<T, 1, false><<<blocks, threads, 0, stream>>> (p); break;
+    case 5: incident_e<T, 1, true><<<blocks, threads, 0, stream>>> (p); break;
+    case 6: incident_e<T, 2, false><<<blocks, threads, 0, stream>>> (p); break;
+    default: incident_e<T, 2, true><<<blocks, threads, 0, stream>>> (p); break;
+  }
+  return cudaGetLastError ();
+}
+template cudaError_t launch_incident<float> (bool, const StepParams<float> &, bool, bool, cudaStream_t);
+template cudaError_t launch_incident<double> (bool, const StepParams<double> &, bool, bool, cudaStream_t);
+
+cudaError_t launch_tick (long long *step, cudaStream_t stream)
+{
+  tick_kernel<<<1, 1, 0, stream>>> (step);
+  return cudaGetLastError ();
+}
+
+cudaError_t launch_reorder (bool to_device, void *dev, void *staged, int cellBytes, int ia, int ib, int ny, int nzb,
+                            int pitch, long long ps, int kofs, int kmin, int kmax, cudaStream_t stream)
+{
+  switch (cellBytes)
+  {
+    case 4: return reorder_t<uint32_t> (to_device, dev, staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax, stream);
+    case 8: return reorder_t<unsigned long long> (to_device, dev, staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax, stream);
+    case 16: return reorder_t<int4> (to_device, dev, staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t launch_repitch (bool to_device, void *dev, void *staged, int cellBytes, int nx, long long nrows, int pitch,
+                            cudaStream_t stream)
+{
+  switch (cellBytes)
+  {
+    case 4: return repitch_t<uint32_t> (to_device, dev, staged, nx, nrows, pitch, stream);
+    case 8: return repitch_t<unsigned long long> (to_device, dev, staged, nx, nrows, pitch, stream);
+    case 16: return repitch_t<int4> (to_device, dev, staged, nx, nrows, pitch, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t launch_fill (void *dev, long long count, int cellBytes, const void *pattern16, cudaStream_t stream)
+{
+  const int threads = 256;
+  long long want = (count + threads - 1) / threads;
+  const int blocks = (int) (want < 148 * 16 ? (want > 0 ? want : 1) : 148 * 16);
+  switch (cellBytes)
+  {
+    case 4: fill_kernel<uint32_t><<<blocks, threads, 0, stream>>> ((uint32_t *) dev, count, *(const uint32_t *) pattern16); break;
+    case 8: fill_kernel<unsigned long long><<<blocks, threads, 0, stream>>> ((unsigned long long *) dev, count, *(const unsigned long long *) pattern16); break;
+    case 16: fill_kernel<int4><<<blocks, threads, 0, stream>>> ((int4 *) dev, count, *(const int4 *) pattern16); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError ();
+}
+
+template <typename T>
+cudaError_t launch_eps_sphere (T *eps, int mx, int my, int nzm, int kz0, int pitchM, long long psM, T cx, T cy, T cz,
+                               T radius, T eps_in, cudaStream_t stream)
+{
+  dim3 block (128);
+  dim3 grid ((mx + 127) / 128, my, nzm < 64 ? nzm : 64);
+  eps_sphere_kernel<T><<<grid, block, 0, stream>>> (eps, mx, my, nzm, kz0, pitchM, psM, cx, cy, cz, radius, eps_in);
+  return cudaGetLastError ();
+}
+template cudaError_t launch_eps_sphere<float> (float *, int, int, int, int, int, long long, float, float, float, float, float, cudaStream_t);
+template cudaError_t launch_eps_sphere<double> (double *, int, int, int, int, int, long long, double, double, double, double, double, cudaStream_t);
+
+int sumsq_partial_count () { return SUMSQ_CTAS; }
+
+template <typename T>
+cudaError_t launch_sumsq (const T *base, int nscal, long long nrows, long long pitch_scal, double *partials, double *out,
+                          cudaStream_t stream)
+{
+  sumsq_partial<T><<<SUMSQ_CTAS, SUMSQ_THREADS, 0, stream>>> (base, nscal, nrows, pitch_scal, partials);
+  cudaError_t e = cudaGetLastError ();
+  if (e != cudaSuccess) return e;
+  sumsq_final<<<1, SUMSQ_THREADS, 0, stream>>> (partials, SUMSQ_CTAS, out);
+  return cudaGetLastError ();
+}
+template cudaError_t launch_sumsq<float> (const float *, int, long long, long long, double *, double *, cudaStream_t);
+template cudaError_t launch_sumsq<double> (const double *, int, long long, long long, double *, double *, cudaStream_t);
+
+} /* namespace fdtd */

@@ -1,0 +1,151 @@
+/*
+ * Device-side parameter block and small helpers shared by the kernels of fdtd3d_b200.
+ *
+ * Device data layout (DESIGN.md "Data layout in HBM"):
+ *   - x is the fastest axis, then y, then z, so that a z-plane (the unit the slab halo exchange moves)
+ *     is contiguous and a warp reads 512 contiguous bytes of one x-row with 128-bit accesses.  The
+ *     reference's host order is z-fastest (Source/Grid/Grid.cpp:138); the transposition happens in the
+ *     upload / download kernels, outside the time loop.
+ *   - a "cell" is one FieldValue: NC = 1 (real) or 2 (interleaved re,im) scalars of T.
+ *   - field arrays: (nzl + 2) planes x Ny rows x pitch cells; plane p holds local z = p - 1, so plane 0
+ *     is the low halo (z = -1) and plane nzl+1 the high halo; rows are padded to 128 bytes.
+ *   - material arrays (eps, mu; real T): (nzl + 3) planes x (Ny+1) rows x pitchM values, plane p holds
+ *     local material z = p - 1.
+ */
+#ifndef FDTD_DEVICE_CUH
+#define FDTD_DEVICE_CUH
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace fdtd
+{
+
+enum { KIND_AT = 0, KIND_BTW = 1 };
+
+/*
+ * UPML coefficient tables along one axis for one sampling kind (SURVEY.md §7 "Coefficients"):
+ * s = sigma[n] (AT: all material samples of the component share index n on this axis) or
+ * (sigma[n] + sigma[n+1]) / 2 (BTW: the samples straddle n and n+1).  Built on the host with the
+ * reference's own expressions (Scheme3D.cpp:310-311, 401-403), so they are the reference's values:
+ *   ca   = (2 eps0 - s dt) / (2 eps0 + s dt)            Ca of either sweep
+ *   cbd  = (2 eps0 dt / dx) / (2 eps0 + s dt)           Cb of the D/B sweep
+ *   p    = 2 eps0 + s dt                                numerator of Cb / divisor of Cb, Cc (sweep 3)
+ *   m    = 2 eps0 - s dt                                numerator of Cc
+ *   invp = 1 / p                                        fast mode only
+ */
+template <typename T>
+struct CoefTab
+{
+  const T *ca, *cbd, *p, *m, *invp;
+};
+
+template <typename T>
+struct StepParams
+{
+  /* fields: Ex Ey Ez Hx Hy Hz Dx Dy Dz Bx By Bz (scalar pointer; cell stride NC) */
+  T *f[12];
+  const T *eps, *mu;
+  CoefTab<T> tab[3][2]; /* [axis][kind] */
+  T *einc, *hinc;       /* 1-D incident line, cells */
+  const T *src;         /* source samples for the steps of the current run, one cell per step */
+  long long *step;      /* device step counter: index into src of the step being computed */
+  long long ninc;       /* cells in einc / hinc */
+
+  int nx, ny;           /* global x/y size */
+  int nzl;              /* planes owned by this rank */
+  int kz0;              /* global z of local plane 0 */
+  int nzg;              /* global z size */
+  int pitch, pitchM;    /* row pitch of field arrays (cells) and material arrays (values) */
+  long long ps, psM;    /* plane strides (cells / values) */
+  int kchunk;           /* planes marched by one CTA */
+
+  int L[3], R[3];       /* TF/SF box: leftBorderTotalField, rightBorderTotalField */
+  int srcpos[3];        /* point source cell (global) */
+
+  T dt, dx, eps0, mu0;
+  T dt_dx;              /* dt / dx (fast mode) */
+  T inc_ce, inc_ch;     /* dt / (relV eps0 dx), dt / (relV mu0 dx): Scheme3D.cpp:39,76 */
+
+  /* incident-wave sampling, Scheme3D.cpp:100-123: zero coordinate (FPValue), direction cosines as
+   * the doubles sin/cos return, projections of YeeGridLayout.cpp:811-845 as FPValue */
+  T zero_inc[3];
+  double s1, c1, s2, c2;
+  T proj_e[3], proj_h[3]; /* proj_h[2] carries the leading minus of getHzFromIncidentH */
+  double cphi, sphi;      /* TMz: cos / sin of incidentWaveAngle */
+};
+
+/* 16-byte vector of W scalars */
+template <typename T, int W>
+struct alignas (16) Vec
+{
+  T v[W];
+};
+
+template <typename T, int W>
+__device__ __forceinline__ Vec<T, W> ldv (const T *p)
+{
+  static_assert (sizeof (T) * W == 16 || sizeof (T) * W == 8, "vector width");
+  Vec<T, W> r;
+  if (sizeof (T) * W == 16)
+    *reinterpret_cast<int4 *> (&r) = __ldg (reinterpret_cast<const int4 *> (p));
+  else
+    *reinterpret_cast<int2 *> (&r) = __ldg (reinterpret_cast<const int2 *> (p));
+  return r;
+}
+
+/* plain (coherent) 16-byte load for arrays this kernel also writes */
+template <typename T, int W>
+__device__ __forceinline__ Vec<T, W> ldv_rw (const T *p)
+{
+  Vec<T, W> r;
+  *reinterpret_cast<int4 *> (&r) = *reinterpret_cast<const int4 *> (p);
+  return r;
+}
+
+template <typename T, int W>
+__device__ __forceinline__ void stv (T *p, const Vec<T, W> &r)
+{
+  *reinterpret_cast<int4 *> (p) = *reinterpret_cast<const int4 *> (&r);
+}
+
+template <typename T> __device__ __forceinline__ T fma_t (T a, T b, T c);
+template <> __device__ __forceinline__ float fma_t<float> (float a, float b, float c) { return __fmaf_rn (a, b, c); }
+template <> __device__ __forceinline__ double fma_t<double> (double a, double b, double c) { return __fma_rn (a, b, c); }
+
+template <typename T> __device__ __forceinline__ T rcp_t (T a);
+template <> __device__ __forceinline__ float rcp_t<float> (float a) { return __frcp_rn (a); }
+template <> __device__ __forceinline__ double rcp_t<double> (double a) { return __drcp_rn (a); }
+
+/*
+ * Projected incident field at the real coordinate of a component's grid position
+ * (Scheme3D::approximateIncidentWave, Scheme3D.cpp:100-123 + YeeGridLayout.cpp:811-845).
+ * gpos = global integer position; off = the component's Yee offset (YeeGridLayout.h:416-424);
+ * ddiff = 0 for E, 0.5 for H; F = einc / hinc; coef = projection.  Rare path (TF/SF faces only).
+ */
+template <typename T, int NC>
+__device__ __noinline__ void incident_sample (const StepParams<T> &p, const T *F, T ddiff, T coef,
+                                              int gi, int gj, int gk, T offx, T offy, T offz, T *out)
+{
+  T x = ((T) gi + offx) - p.zero_inc[0];
+  T y = ((T) gj + offy) - p.zero_inc[1];
+  T z = ((T) gk + offz) - p.zero_inc[2];
+  /* evaluated in double and rounded once, as the reference does for float builds (sin/cos are the
+   * C double functions there); for T = double this is the reference's expression verbatim */
+  double dd = (double) x * p.s1 * p.c2 + (double) y * p.s1 * p.s2 + (double) z * p.c1 - (double) ddiff;
+  T d = (T) dd;
+  unsigned long long n = (unsigned long long) d;
+  T c1 = (T) n;
+  T prop2 = d - c1;
+  T prop1 = (T) 1 - prop2;
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
+  {
+    T v = prop1 * F[n * NC + c] + prop2 * F[(n + 1) * NC + c];
+    out[c] = v * coef;
+  }
+}
+
+} /* namespace fdtd */
+
+#endif /* FDTD_DEVICE_CUH */

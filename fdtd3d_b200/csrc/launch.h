@@ -1,0 +1,66 @@
+/*
+ * Host-callable launch wrappers of the kernel translation units (kernels3d.cu, kernels2d.cu, aux_kernels.cu).
+ * Every wrapper launches exactly one kernel on `stream` and returns cudaGetLastError().
+ */
+#ifndef FDTD_LAUNCH_H
+#define FDTD_LAUNCH_H
+
+#include <cuda_runtime.h>
+#include "fdtd_device.cuh"
+
+namespace fdtd
+{
+
+/* 3D half steps over local planes [kb, ke) (kernels3d.cu) */
+template <typename T>
+cudaError_t launch_phase_3d (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact,
+                             int kb, int ke, cudaStream_t stream);
+
+/* 2D TMz half steps (kernels2d.cu) */
+template <typename T>
+cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact,
+                              cudaStream_t stream);
+
+/* 1-D incident line: E update + source sample at cell 0, H update (aux_kernels.cu);
+ * Scheme3D::performPlaneWaveESteps / HSteps, Scheme3D.cpp:24-82 */
+template <typename T>
+cudaError_t launch_incident (bool e_phase, const StepParams<T> &p, bool cplx, bool exact, cudaStream_t stream);
+
+/* step counter += 1 (one thread) */
+cudaError_t launch_tick (long long *step, cudaStream_t stream);
+
+/*
+ * Layout conversion between a staged host-order block and the device layout.
+ * host-order block: cells (i in [ia, ib), j in [0, ny), k in [0, nzb)) stored as ((i-ia)*ny + j)*nzb + k
+ * (reference order restricted to an i-range of a buffer that covers global planes [z0, z0+nzb));
+ * device: ((k + kofs)*ny + j)*pitch + i, `cellBytes` bytes per cell.  to_device: scatter into the device
+ * layout; otherwise gather from it.  Planes with k + kofs outside [kmin, kmax) are skipped.
+ */
+cudaError_t launch_reorder (bool to_device, void *dev, void *staged, int cellBytes, int ia, int ib, int ny, int nzb,
+                            int pitch, long long ps, int kofs, int kmin, int kmax, cudaStream_t stream);
+
+/* native-order (x fastest, unpadded) <-> device layout, rows [0, nrows) of nx cells */
+cudaError_t launch_repitch (bool to_device, void *dev, void *staged, int cellBytes, int nx, long long nrows, int pitch,
+                            cudaStream_t stream);
+
+/* fill `count` cells of `cellBytes` (4, 8 or 16) with a 16-byte pattern */
+cudaError_t launch_fill (void *dev, long long count, int cellBytes, const void *pattern16, cudaStream_t stream);
+
+/* Approximation::approximateSphere over the material grid (Approximation.cpp:303-331) */
+template <typename T>
+cudaError_t launch_eps_sphere (T *eps, int mx, int my, int nzm, int kz0, int pitchM, long long psM, T cx, T cy, T cz,
+                               T radius, T eps_in, cudaStream_t stream);
+
+/*
+ * sum of squares of `nscal` scalars per row over rows of a pitched array, accumulated in double.
+ * Two kernels: per-CTA partial sums into `partials` (scratch, >= sumsq_partial_count() doubles), then a
+ * single-CTA reduction into *out.
+ */
+int sumsq_partial_count ();
+template <typename T>
+cudaError_t launch_sumsq (const T *base, int nscal, long long nrows, long long pitch_scal, double *partials,
+                          double *out, cudaStream_t stream);
+
+} /* namespace fdtd */
+
+#endif /* FDTD_LAUNCH_H */

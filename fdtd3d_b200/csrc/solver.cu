@@ -1,0 +1,922 @@
+/*
+ * Host side of the C ABI declared in include/fdtd3d_b200.h: device-resident solver state, UPML
+ * coefficient tables, the time loop (kernel launches + z-slab halo exchange) and host<->device
+ * transfers.  There is no CPU compute path: every entry point that needs a device fails with
+ * FDTD_NO_DEVICE if there is none.
+ *
+ * Reference being replaced: Source/Cuda/CudaInterface.cu (cudaExecute3DSteps :356-932,
+ * cudaExecute2DTMzSteps :20-339, cudaInit :934, cudaInfo :939-959) and, for the exchange,
+ * Source/Grid/ParallelGrid.cpp:1817-1823 (share) -- see DESIGN.md.
+ */
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/fdtd3d_b200.h"
+#include "fdtd_device.cuh"
+#include "launch.h"
+#include "nccl_dl.h"
+
+namespace fdtd
+{
+
+static thread_local std::string g_last_error;
+
+static int fail (int code, const char *fmt, ...)
+{
+  char buf[1024];
+  va_list ap;
+  va_start (ap, fmt);
+  vsnprintf (buf, sizeof (buf), fmt, ap);
+  va_end (ap);
+  g_last_error = buf;
+  return code;
+}
+
+#define CUDA_TRY(expr) \
+  do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return fail (FDTD_ERROR, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString (e_), __FILE__, __LINE__); } while (0)
+
+#define NCCL_TRY(expr) \
+  do { int r_ = (expr); if (r_ != 0) return fail (FDTD_COMM_ERROR, "%s failed: %s (%s:%d)", #expr, nccl->GetErrorString (r_), __FILE__, __LINE__); } while (0)
+
+static inline long long round_up (long long x, long long m) { return (x + m - 1) / m * m; }
+
+/* Physics/PhysicsConst.h:9-13: constants stored as FPValue */
+template <typename T> struct PC
+{
+  static T c () { return (T) 2.99792458e+8; }
+  static T eps0 () { return (T) 0.0000000000088541878176203892; }
+  static T mu0 () { return (T) 0.0000012566370614359173; }
+  static T pi () { return (T) M_PI; }
+};
+
+} /* namespace fdtd */
+
+using namespace fdtd;
+
+struct fdtd_solver
+{
+  fdtd_config cfg;
+  int nc;            /* scalars per cell */
+  int fp;            /* sizeof FPValue */
+  int cell;          /* bytes per cell */
+  int nx, ny, nzg;   /* global sizes (nzg = 1 in 2D) */
+  int nzl, kz0;      /* local planes and their global offset */
+  int nzm;           /* local material planes (nzl+1 in 3D, 1 in 2D) */
+  int pitch, pitchM;
+  long long ps, psM;
+  long long field_cells, mat_vals; /* allocation sizes */
+  long long ninc;
+
+  void *f[12];
+  void *eps, *mu;
+  void *einc, *hinc;
+  void *tab_mem;     /* all coefficient tables, one allocation */
+  size_t tab_stride; /* bytes between tables */
+  void *src;         /* source samples */
+  long long src_capacity;
+  long long *step;
+  void *staging;     /* layout-conversion scratch */
+  size_t staging_bytes;
+  double *red_partials, *red_out; /* reduction scratch */
+
+  std::vector<double> sigma[3]; /* profiles as given (FPValue-valued) */
+
+  cudaStream_t s_compute, s_comm;
+  cudaEvent_t ev_start, ev_stop, ev_eb, ev_ex, ev_hb, ev_hx;
+  NcclComm comm;
+
+  bool profiling;
+  std::vector<cudaEvent_t> prof_ev; /* 4 per step: E begin/end, H begin/end */
+  long long prof_steps;
+  float prof_e_ms, prof_h_ms;
+
+  long long t;          /* next time step index */
+  long long launches;
+  float last_ms;
+  bool run_pending;
+};
+
+namespace fdtd
+{
+
+static const int N_TABLES = 3 * 2 * 5;
+
+template <typename T>
+static StepParams<T> make_params (const fdtd_solver *s)
+{
+  StepParams<T> p;
+  memset (&p, 0, sizeof (p));
+  const fdtd_config &c = s->cfg;
+  for (int i = 0; i < 12; ++i) p.f[i] = (T *) s->f[i];
+  p.eps = (const T *) s->eps;
+  p.mu = (const T *) s->mu;
+  for (int a = 0; a < 3; ++a)
+    for (int k = 0; k < 2; ++k)
+    {
+      const char *base = (const char *) s->tab_mem + (size_t) ((a * 2 + k) * 5) * s->tab_stride;
+      p.tab[a][k].ca = (const T *) (base + 0 * s->tab_stride);
+      p.tab[a][k].cbd = (const T *) (base + 1 * s->tab_stride);
+      p.tab[a][k].p = (const T *) (base + 2 * s->tab_stride);
+      p.tab[a][k].m = (const T *) (base + 3 * s->tab_stride);
+      p.tab[a][k].invp = (const T *) (base + 4 * s->tab_stride);
+    }
+  p.einc = (T *) s->einc;
+  p.hinc = (T *) s->hinc;
+  p.src = (const T *) s->src;
+  p.step = s->step;
+  p.ninc = s->ninc;
+  p.nx = s->nx; p.ny = s->ny; p.nzl = s->nzl; p.kz0 = s->kz0; p.nzg = s->nzg;
+  p.pitch = s->pitch; p.pitchM = s->pitchM; p.ps = s->ps; p.psM = s->psM;
+  p.kchunk = c.dims == 3 ? 32 : 16;
+  for (int a = 0; a < 3; ++a)
+  {
+    p.L[a] = (int) c.tfsf_size[a];
+    p.R[a] = (int) (c.size[a] - c.tfsf_size[a]);
+    p.srcpos[a] = (int) c.source_pos[a];
+  }
+  const T dt = (T) c.dt, dx = (T) c.dx, relv = (T) c.rel_phase_velocity;
+  p.dt = dt; p.dx = dx; p.eps0 = PC<T>::eps0 (); p.mu0 = PC<T>::mu0 ();
+  p.dt_dx = dt / dx;
+  /* Scheme3D.cpp:39,76: gridTimeStep / (relPhaseVelocity * Eps0 * gridStep) */
+  p.inc_ce = dt / (relv * PC<T>::eps0 () * dx);
+  p.inc_ch = dt / (relv * PC<T>::mu0 () * dx);
+  const T a1 = (T) c.angle_teta, a2 = (T) c.angle_phi, a3 = (T) c.angle_psi;
+  /* YeeGridLayout.h:438-440 */
+  p.zero_inc[0] = (T) ((unsigned long long) c.tfsf_size[0] - 2.5 * sin ((double) a1) * cos ((double) a2));
+  p.zero_inc[1] = (T) ((unsigned long long) c.tfsf_size[1] - 2.5 * sin ((double) a1) * sin ((double) a2));
+  p.zero_inc[2] = (T) ((unsigned long long) c.tfsf_size[2] - 2.5 * cos ((double) a1));
+  p.s1 = sin ((double) a1); p.c1 = cos ((double) a1);
+  p.s2 = sin ((double) a2); p.c2 = cos ((double) a2);
+  const double s3 = sin ((double) a3), c3 = cos ((double) a3);
+  /* YeeGridLayout.cpp:811-845 */
+  p.proj_e[0] = (T) (c3 * p.s2 - s3 * p.c1 * p.c2);
+  p.proj_e[1] = (T) (-c3 * p.c2 - s3 * p.c1 * p.s2);
+  p.proj_e[2] = (T) (s3 * p.s1);
+  p.proj_h[0] = (T) (s3 * p.s2 + c3 * p.c1 * p.c2);
+  p.proj_h[1] = (T) (-s3 * p.c2 + c3 * p.c1 * p.s2);
+  p.proj_h[2] = -(T) (c3 * p.s1);
+  p.cphi = p.c2; p.sphi = p.s2;
+  return p;
+}
+
+/* UPML coefficient tables from the 1-D sigma profiles (fdtd_device.cuh, struct CoefTab), with the
+ * reference's expressions Scheme3D.cpp:310-311, 401-403 evaluated in FPValue arithmetic. */
+template <typename T>
+static int build_tables (fdtd_solver *s)
+{
+  const fdtd_config &c = s->cfg;
+  const size_t len = s->tab_stride / sizeof (T);
+  std::vector<T> host ((size_t) N_TABLES * len);
+  const T eps0 = PC<T>::eps0 ();
+  const T dt = (T) c.dt, dx = (T) c.dx;
+  for (int a = 0; a < 3; ++a)
+  {
+    const std::vector<double> &sg = s->sigma[a];
+    const long long n = (long long) sg.size (); /* N_a + 1 */
+    for (int kind = 0; kind < 2; ++kind)
+    {
+      T *ca = &host[(size_t) ((a * 2 + kind) * 5 + 0) * len];
+      T *cbd = &host[(size_t) ((a * 2 + kind) * 5 + 1) * len];
+      T *pp = &host[(size_t) ((a * 2 + kind) * 5 + 2) * len];
+      T *mm = &host[(size_t) ((a * 2 + kind) * 5 + 3) * len];
+      T *ip = &host[(size_t) ((a * 2 + kind) * 5 + 4) * len];
+      for (size_t i = 0; i < len; ++i)
+      {
+        T sig = 0;
+        if ((long long) i < n)
+        {
+          if (kind == KIND_AT) sig = (T) sg[i];
+          else
+          {
+            /* Approximation.cpp:15-19: (val1 + val2) / 2.0 */
+            T v1 = (T) sg[i], v2 = (long long) i + 1 < n ? (T) sg[i + 1] : (T) sg[i];
+            sig = (v1 + v2) / 2.0;
+          }
+        }
+        T k = 1;
+        ca[i] = (2 * eps0 * k - sig * dt) / (2 * eps0 * k + sig * dt);
+        cbd[i] = (2 * eps0 * dt / dx) / (2 * eps0 * k + sig * dt);
+        pp[i] = 2 * eps0 * k + sig * dt;
+        mm[i] = 2 * eps0 * k - sig * dt;
+        ip[i] = (T) 1 / pp[i];
+      }
+    }
+  }
+  CUDA_TRY (cudaMemcpyAsync (s->tab_mem, host.data (), host.size () * sizeof (T), cudaMemcpyHostToDevice, s->s_compute));
+  CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+  return FDTD_OK;
+}
+
+static int build_tables_any (fdtd_solver *s)
+{
+  return s->fp == 4 ? build_tables<float> (s) : build_tables<double> (s);
+}
+
+/* source samples for steps [t, t+n): sin (gridTimeStep * t * 2 * Pi * sourceFrequency), complex builds
+ * (sin, cos) -- Scheme3D.cpp:47-52, 2016-2021 -- evaluated on the host with the C double sin/cos as
+ * the reference does, so the waveform is the reference's bit for bit. */
+template <typename T>
+static int upload_source (fdtd_solver *s, long long n)
+{
+  const fdtd_config &c = s->cfg;
+  if (n > s->src_capacity)
+  {
+    if (s->src) cudaFree (s->src);
+    s->src = NULL;
+    s->src_capacity = 0;
+    CUDA_TRY (cudaMalloc (&s->src, (size_t) n * s->cell));
+    s->src_capacity = n;
+  }
+  std::vector<T> host ((size_t) n * s->nc);
+  const T dt = (T) c.dt, freq = (T) c.source_frequency;
+  for (long long i = 0; i < n; ++i)
+  {
+    const int t = (int) (s->t + i);
+    const T arg = dt * t * 2 * PC<T>::pi () * freq;
+    host[(size_t) i * s->nc] = (T) ::sin ((double) arg);
+    if (s->nc == 2) host[(size_t) i * 2 + 1] = (T) ::cos ((double) arg);
+  }
+  CUDA_TRY (cudaMemcpyAsync (s->src, host.data (), host.size () * sizeof (T), cudaMemcpyHostToDevice, s->s_compute));
+  CUDA_TRY (cudaStreamSynchronize (s->s_compute)); /* host vector goes out of scope */
+  return FDTD_OK;
+}
+
+/* ------------------------------------------------------------------ halo exchange */
+
+/* H phase -> E phase: top owned plane of Hx, Hy goes to the upper neighbour's low halo;
+ * E phase -> H phase: bottom owned plane of Ex, Ey goes to the lower neighbour's high halo. */
+static int exchange (fdtd_solver *s, bool h_fields)
+{
+  const char *why = NULL;
+  const NcclApi *nccl = nccl_api (&why);
+  if (!nccl || !s->comm) return fail (FDTD_COMM_ERROR, "halo exchange without a communicator (%s)", why ? why : "");
+  const size_t plane_bytes = (size_t) s->ps * s->cell;
+  const int r = s->cfg.rank, n = s->cfg.nranks;
+  NCCL_TRY (nccl->GroupStart ());
+  if (h_fields)
+  {
+    for (int f = FDTD_HX; f <= FDTD_HY; ++f)
+    {
+      char *base = (char *) s->f[f];
+      if (r + 1 < n) NCCL_TRY (nccl->Send (base + (size_t) s->nzl * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
+      if (r > 0) NCCL_TRY (nccl->Recv (base, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
+    }
+  }
+  else
+  {
+    for (int f = FDTD_EX; f <= FDTD_EY; ++f)
+    {
+      char *base = (char *) s->f[f];
+      if (r > 0) NCCL_TRY (nccl->Send (base + plane_bytes, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
+      if (r + 1 < n) NCCL_TRY (nccl->Recv (base + (size_t) (s->nzl + 1) * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
+    }
+  }
+  NCCL_TRY (nccl->GroupEnd ());
+  return FDTD_OK;
+}
+
+/* ------------------------------------------------------------------ time loop */
+
+template <typename T>
+static int enqueue_steps (fdtd_solver *s, long long nsteps)
+{
+  const fdtd_config &c = s->cfg;
+  const StepParams<T> p = make_params<T> (s);
+  const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode != 0;
+  const bool multi = c.nranks > 1;
+  cudaStream_t S = s->s_compute, C = s->s_comm;
+  const bool prof = s->profiling && !multi;
+  s->prof_steps = 0;
+  if (prof)
+  {
+    while ((long long) s->prof_ev.size () < 4 * nsteps)
+    {
+      cudaEvent_t e;
+      CUDA_TRY (cudaEventCreate (&e));
+      s->prof_ev.push_back (e);
+    }
+    s->prof_steps = nsteps;
+  }
+
+  if (multi)
+  {
+    /* make the low H halo valid for the first E half step */
+    CUDA_TRY (cudaEventRecord (s->ev_hb, S));
+    CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
+    int rc = exchange (s, true);
+    if (rc) return rc;
+    CUDA_TRY (cudaEventRecord (s->ev_hx, C));
+  }
+
+  for (long long n = 0; n < nsteps; ++n)
+  {
+    /* Scheme3D::performNSteps, Scheme3D.cpp:1986-2069 (SchemeTMz.cpp:1336-1427) */
+    if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, exact, S)); s->launches++; }
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
+    if (c.dims == 2)
+    {
+      CUDA_TRY (launch_phase_tmz<T> (true, p, cplx, pml, tfsf, exact, S)); s->launches++;
+    }
+    else if (!multi)
+    {
+      CUDA_TRY (launch_phase_3d<T> (true, p, cplx, pml, tfsf, exact, 0, s->nzl, S)); s->launches++;
+    }
+    else
+    {
+      CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
+      CUDA_TRY (launch_phase_3d<T> (true, p, cplx, pml, tfsf, exact, 0, 1, S)); s->launches++;
+      CUDA_TRY (cudaEventRecord (s->ev_eb, S));
+      CUDA_TRY (cudaStreamWaitEvent (C, s->ev_eb, 0));
+      int rc = exchange (s, false);
+      if (rc) return rc;
+      CUDA_TRY (cudaEventRecord (s->ev_ex, C));
+      if (s->nzl > 1) { CUDA_TRY (launch_phase_3d<T> (true, p, cplx, pml, tfsf, exact, 1, s->nzl, S)); s->launches++; }
+    }
+
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
+    if (tfsf) { CUDA_TRY (launch_incident<T> (false, p, cplx, exact, S)); s->launches++; }
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
+    if (c.dims == 2)
+    {
+      CUDA_TRY (launch_phase_tmz<T> (false, p, cplx, pml, tfsf, exact, S)); s->launches++;
+    }
+    else if (!multi)
+    {
+      CUDA_TRY (launch_phase_3d<T> (false, p, cplx, pml, tfsf, exact, 0, s->nzl, S)); s->launches++;
+    }
+    else
+    {
+      CUDA_TRY (cudaStreamWaitEvent (S, s->ev_ex, 0));
+      CUDA_TRY (launch_phase_3d<T> (false, p, cplx, pml, tfsf, exact, s->nzl - 1, s->nzl, S)); s->launches++;
+      CUDA_TRY (cudaEventRecord (s->ev_hb, S));
+      CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
+      int rc = exchange (s, true);
+      if (rc) return rc;
+      CUDA_TRY (cudaEventRecord (s->ev_hx, C));
+      if (s->nzl > 1) { CUDA_TRY (launch_phase_3d<T> (false, p, cplx, pml, tfsf, exact, 0, s->nzl - 1, S)); s->launches++; }
+    }
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
+    CUDA_TRY (launch_tick (s->step, S)); s->launches++;
+  }
+  if (multi) CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
+  return FDTD_OK;
+}
+
+static int run_async (fdtd_solver *s, long long nsteps)
+{
+  if (nsteps < 0) return fail (FDTD_INVALID_ARGUMENT, "nsteps < 0");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  if (s->run_pending)
+  {
+    CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+    s->run_pending = false;
+  }
+  if (nsteps == 0) { s->last_ms = 0; return FDTD_OK; }
+  int rc = s->fp == 4 ? upload_source<float> (s, nsteps) : upload_source<double> (s, nsteps);
+  if (rc) return rc;
+  CUDA_TRY (cudaMemsetAsync (s->step, 0, sizeof (long long), s->s_compute));
+  CUDA_TRY (cudaEventRecord (s->ev_start, s->s_compute));
+  rc = s->fp == 4 ? enqueue_steps<float> (s, nsteps) : enqueue_steps<double> (s, nsteps);
+  if (rc) return rc;
+  CUDA_TRY (cudaEventRecord (s->ev_stop, s->s_compute));
+  s->t += nsteps;
+  s->run_pending = true;
+  return FDTD_OK;
+}
+
+static int sync_run (fdtd_solver *s)
+{
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+  if (s->run_pending)
+  {
+    CUDA_TRY (cudaEventElapsedTime (&s->last_ms, s->ev_start, s->ev_stop));
+    s->run_pending = false;
+    s->prof_e_ms = s->prof_h_ms = 0;
+    for (long long n = 0; n < s->prof_steps; ++n)
+    {
+      float a = 0, b = 0;
+      CUDA_TRY (cudaEventElapsedTime (&a, s->prof_ev[4 * n + 0], s->prof_ev[4 * n + 1]));
+      CUDA_TRY (cudaEventElapsedTime (&b, s->prof_ev[4 * n + 2], s->prof_ev[4 * n + 3]));
+      s->prof_e_ms += a;
+      s->prof_h_ms += b;
+    }
+  }
+  return FDTD_OK;
+}
+
+/* ------------------------------------------------------------------ transfers */
+
+struct FieldInfo
+{
+  void *dev;
+  int cell;          /* bytes per cell */
+  int nx, ny;        /* logical row length and rows per plane */
+  int nzl_planes;    /* owned planes */
+  int nzg_planes;    /* global planes */
+  int pitch;
+  long long ps;
+  bool is_inc;
+};
+
+static int field_info (fdtd_solver *s, int field, FieldInfo *fi)
+{
+  memset (fi, 0, sizeof (*fi));
+  const fdtd_config &c = s->cfg;
+  if (field >= FDTD_EX && field <= FDTD_BZ)
+  {
+    if (!s->f[field]) return fail (FDTD_INVALID_ARGUMENT, "field %d is not part of this configuration", field);
+    fi->dev = s->f[field]; fi->cell = s->cell; fi->nx = s->nx; fi->ny = s->ny;
+    fi->nzl_planes = s->nzl; fi->nzg_planes = s->nzg; fi->pitch = s->pitch; fi->ps = s->ps;
+    return FDTD_OK;
+  }
+  if (field == FDTD_EPS || field == FDTD_MU)
+  {
+    fi->dev = field == FDTD_EPS ? s->eps : s->mu; fi->cell = s->fp; fi->nx = s->nx + 1; fi->ny = s->ny + 1;
+    fi->nzl_planes = s->nzm; fi->nzg_planes = c.dims == 3 ? s->nzg + 1 : 1; fi->pitch = s->pitchM; fi->ps = s->psM;
+    return FDTD_OK;
+  }
+  if (field == FDTD_EINC || field == FDTD_HINC)
+  {
+    if (!s->einc) return fail (FDTD_INVALID_ARGUMENT, "incident line requested without use_tfsf");
+    fi->dev = field == FDTD_EINC ? s->einc : s->hinc; fi->cell = s->cell; fi->is_inc = true;
+    return FDTD_OK;
+  }
+  return fail (FDTD_INVALID_ARGUMENT, "unknown field id %d", field);
+}
+
+static int transfer (fdtd_solver *s, int field, void *host, int order, long long z0, long long nz, bool to_device)
+{
+  if (!host) return fail (FDTD_INVALID_ARGUMENT, "NULL host pointer");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  int rc = sync_run (s);
+  if (rc) return rc;
+  FieldInfo fi;
+  rc = field_info (s, field, &fi);
+  if (rc) return rc;
+  cudaStream_t S = s->s_compute;
+  if (fi.is_inc)
+  {
+    const size_t bytes = (size_t) s->ninc * s->cell;
+    if (to_device) CUDA_TRY (cudaMemcpyAsync (fi.dev, host, bytes, cudaMemcpyHostToDevice, S));
+    else CUDA_TRY (cudaMemcpyAsync (host, fi.dev, bytes, cudaMemcpyDeviceToHost, S));
+    CUDA_TRY (cudaStreamSynchronize (S));
+    return FDTD_OK;
+  }
+  if (s->cfg.dims == 2) { z0 = 0; nz = 1; }
+  if (z0 < 0 || nz <= 0 || z0 + nz > fi.nzg_planes)
+    return fail (FDTD_INVALID_ARGUMENT, "plane range [%lld, %lld) outside [0, %d)", z0, z0 + nz, fi.nzg_planes);
+  /* device plane index of buffer plane k: (z0 + k - kz0) + 1; owned planes are [1, nzl_planes + 1) */
+  const int kofs = (int) (z0 - s->kz0) + 1;
+  const int kmin = 1, kmax = fi.nzl_planes + 1;
+  char *h = (char *) host;
+  if (order == FDTD_ORDER_REFERENCE)
+  {
+    /* chunks of i-rows of the k-fastest host block */
+    const size_t row_bytes = (size_t) fi.ny * nz * fi.cell;
+    long long rows_per_chunk = (long long) (s->staging_bytes / row_bytes);
+    if (rows_per_chunk < 1) return fail (FDTD_INVALID_ARGUMENT, "one i-row (%zu bytes) exceeds the staging buffer", row_bytes);
+    for (long long ia = 0; ia < fi.nx; ia += rows_per_chunk)
+    {
+      const long long ib = ia + rows_per_chunk < fi.nx ? ia + rows_per_chunk : fi.nx;
+      const size_t bytes = (size_t) (ib - ia) * row_bytes;
+      if (to_device)
+      {
+        CUDA_TRY (cudaMemcpyAsync (s->staging, h + (size_t) ia * row_bytes, bytes, cudaMemcpyHostToDevice, S));
+        CUDA_TRY (launch_reorder (true, fi.dev, s->staging, fi.cell, (int) ia, (int) ib, fi.ny, (int) nz, fi.pitch, fi.ps, kofs, kmin, kmax, S));
+      }
+      else
+      {
+        CUDA_TRY (launch_reorder (false, fi.dev, s->staging, fi.cell, (int) ia, (int) ib, fi.ny, (int) nz, fi.pitch, fi.ps, kofs, kmin, kmax, S));
+        CUDA_TRY (cudaMemcpyAsync (h + (size_t) ia * row_bytes, s->staging, bytes, cudaMemcpyDeviceToHost, S));
+      }
+      s->launches++;
+      CUDA_TRY (cudaStreamSynchronize (S));
+    }
+  }
+  else if (order == FDTD_ORDER_NATIVE)
+  {
+    /* x-fastest host block: plane by plane, rows of nx cells */
+    for (long long k = 0; k < nz; ++k)
+    {
+      const int kd = (int) k + kofs;
+      if (kd < kmin || kd >= kmax) continue;
+      char *hp = h + (size_t) k * fi.ny * fi.nx * fi.cell;
+      char *dp = (char *) fi.dev + (size_t) kd * fi.ps * fi.cell;
+      if (to_device)
+        CUDA_TRY (cudaMemcpy2DAsync (dp, (size_t) fi.pitch * fi.cell, hp, (size_t) fi.nx * fi.cell, (size_t) fi.nx * fi.cell, fi.ny, cudaMemcpyHostToDevice, S));
+      else
+        CUDA_TRY (cudaMemcpy2DAsync (hp, (size_t) fi.nx * fi.cell, dp, (size_t) fi.pitch * fi.cell, (size_t) fi.nx * fi.cell, fi.ny, cudaMemcpyDeviceToHost, S));
+    }
+    CUDA_TRY (cudaStreamSynchronize (S));
+  }
+  else
+    return fail (FDTD_INVALID_ARGUMENT, "unknown order %d", order);
+  return FDTD_OK;
+}
+
+static int validate (const fdtd_config *c)
+{
+  if (!c) return fail (FDTD_INVALID_ARGUMENT, "NULL config");
+  if (c->abi_version != FDTD3D_B200_ABI_VERSION) return fail (FDTD_INVALID_ARGUMENT, "abi_version %d, library is %d", c->abi_version, FDTD3D_B200_ABI_VERSION);
+  if (c->dims != 2 && c->dims != 3) return fail (FDTD_INVALID_ARGUMENT, "dims must be 2 (TMz) or 3");
+  if (c->value_type != 4 && c->value_type != 8) return fail (FDTD_INVALID_ARGUMENT, "value_type must be 4 (float) or 8 (double); long double has no device type");
+  for (int a = 0; a < c->dims; ++a)
+  {
+    if (c->size[a] < 2 || c->size[a] > (1 << 20)) return fail (FDTD_INVALID_ARGUMENT, "size[%d] = %lld out of range", a, (long long) c->size[a]);
+    if (c->use_tfsf && (c->tfsf_size[a] < 1 || 2 * c->tfsf_size[a] >= c->size[a]))
+      return fail (FDTD_INVALID_ARGUMENT, "tfsf_size[%d] = %lld does not leave a total-field region", a, (long long) c->tfsf_size[a]);
+    if (!c->use_tfsf && (c->source_pos[a] < 0 || c->source_pos[a] >= c->size[a]))
+      return fail (FDTD_INVALID_ARGUMENT, "source_pos[%d] = %lld outside the grid", a, (long long) c->source_pos[a]);
+  }
+  if (c->dims == 2 && c->size[2] != 1) return fail (FDTD_INVALID_ARGUMENT, "size[2] must be 1 for dims == 2");
+  if (!(c->dx > 0) || !(c->dt > 0)) return fail (FDTD_INVALID_ARGUMENT, "dx and dt must be positive");
+  if (c->use_tfsf && !(c->rel_phase_velocity > 0)) return fail (FDTD_INVALID_ARGUMENT, "rel_phase_velocity must be positive");
+  if (c->nranks < 1 || c->rank < 0 || c->rank >= c->nranks) return fail (FDTD_INVALID_ARGUMENT, "bad rank %d of %d", c->rank, c->nranks);
+  if (c->nranks > 1 && c->dims != 3) return fail (FDTD_INVALID_ARGUMENT, "z-slab decomposition needs dims == 3");
+  if (c->nranks > 1 && c->size[2] / c->nranks < 1) return fail (FDTD_INVALID_ARGUMENT, "fewer z planes than ranks");
+  return FDTD_OK;
+}
+
+} /* namespace fdtd */
+
+/* ==================================================================== C ABI */
+
+extern "C"
+{
+
+const char *fdtd_last_error (void) { return g_last_error.c_str (); }
+
+int fdtd_device_info (int device, char *buf, int64_t buflen)
+{
+  if (!buf || buflen <= 0) return fail (FDTD_INVALID_ARGUMENT, "NULL buffer");
+  int n = 0;
+  if (cudaGetDeviceCount (&n) != cudaSuccess || n == 0) return fail (FDTD_NO_DEVICE, "no CUDA device");
+  cudaDeviceProp prop;
+  CUDA_TRY (cudaGetDeviceProperties (&prop, device));
+  int memclk = 0, buswidth = 0;
+  cudaDeviceGetAttribute (&memclk, cudaDevAttrMemoryClockRate, device);
+  cudaDeviceGetAttribute (&buswidth, cudaDevAttrGlobalMemoryBusWidth, device);
+  /* same "theoretical bandwidth" formula as cudaInfo, CudaInterface.cu:955-957 */
+  snprintf (buf, (size_t) buflen, "%s: sm_%d%d, %d SMs, %.1f GiB, L2 %.0f MiB, theoretical bandwidth %.0f GB/s",
+            prop.name, prop.major, prop.minor, prop.multiProcessorCount, prop.totalGlobalMem / 1073741824.0,
+            prop.l2CacheSize / 1048576.0, 2.0 * memclk * (buswidth / 8) / 1.0e6);
+  return FDTD_OK;
+}
+
+int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
+{
+  if (!out) return fail (FDTD_INVALID_ARGUMENT, "NULL output handle");
+  *out = NULL;
+  int rc = validate (cfg);
+  if (rc) return rc;
+  int ndev = 0;
+  if (cudaGetDeviceCount (&ndev) != cudaSuccess || ndev == 0)
+    return fail (FDTD_NO_DEVICE, "no CUDA device available: fdtd3d_b200 has no CPU fallback");
+  if (cfg->device < 0 || cfg->device >= ndev) return fail (FDTD_INVALID_ARGUMENT, "device %d of %d", cfg->device, ndev);
+  CUDA_TRY (cudaSetDevice (cfg->device));
+
+  fdtd_solver *s = new fdtd_solver ();
+  s->cfg = *cfg;
+  s->nc = cfg->complex_values ? 2 : 1;
+  s->fp = cfg->value_type;
+  s->cell = s->fp * s->nc;
+  s->nx = (int) cfg->size[0]; s->ny = (int) cfg->size[1]; s->nzg = cfg->dims == 3 ? (int) cfg->size[2] : 1;
+  if (cfg->dims == 2) { s->cfg.size[2] = 1; s->cfg.tfsf_size[2] = 0; s->cfg.pml_size[2] = 0; s->cfg.source_pos[2] = 0; }
+  /* slab partition: core = Nz / n, last rank takes the remainder (ParallelYeeGridLayout.cpp:24-36) */
+  const int core = s->nzg / cfg->nranks;
+  s->kz0 = cfg->rank * core;
+  s->nzl = cfg->rank == cfg->nranks - 1 ? s->nzg - s->kz0 : core;
+  s->nzm = cfg->dims == 3 ? s->nzl + 1 : 1;
+  s->pitch = (int) round_up (s->nx, 128 / s->cell);
+  s->pitchM = (int) round_up (s->nx + 1, 128 / s->fp);
+  s->ps = (long long) s->pitch * s->ny;
+  s->psM = (long long) s->pitchM * (s->ny + 1);
+  s->field_cells = s->ps * (s->nzl + 2);
+  s->mat_vals = s->psM * (s->nzm + 2);
+  s->ninc = cfg->use_tfsf ? 100LL * (s->nx + s->ny + (cfg->dims == 3 ? s->nzg : 0)) : 0;
+  s->t = cfg->time_step_start;
+  for (int a = 0; a < 3; ++a) s->sigma[a].assign ((size_t) (a < cfg->dims ? cfg->size[a] : 1) + 1, 0.0);
+
+#define CREATE_TRY(expr) \
+  do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail (FDTD_ERROR, "%s failed: %s", #expr, cudaGetErrorString (e_)); fdtd_destroy (s); return FDTD_ERROR; } } while (0)
+
+  CREATE_TRY (cudaStreamCreateWithFlags (&s->s_compute, cudaStreamNonBlocking));
+  CREATE_TRY (cudaStreamCreateWithFlags (&s->s_comm, cudaStreamNonBlocking));
+  CREATE_TRY (cudaEventCreate (&s->ev_start));
+  CREATE_TRY (cudaEventCreate (&s->ev_stop));
+  CREATE_TRY (cudaEventCreateWithFlags (&s->ev_eb, cudaEventDisableTiming));
+  CREATE_TRY (cudaEventCreateWithFlags (&s->ev_ex, cudaEventDisableTiming));
+  CREATE_TRY (cudaEventCreateWithFlags (&s->ev_hb, cudaEventDisableTiming));
+  CREATE_TRY (cudaEventCreateWithFlags (&s->ev_hx, cudaEventDisableTiming));
+
+  const bool is3 = cfg->dims == 3;
+  for (int f = 0; f < 12; ++f)
+  {
+    const int comp = f % 3;
+    const bool aux = f >= FDTD_DX;
+    bool present = is3 ? true : ((f < FDTD_HX || (f >= FDTD_DX && f < FDTD_BX)) ? comp == 2 : comp < 2); /* TMz: Ez, Hx, Hy */
+    if (aux && !cfg->use_pml) present = false;
+    if (!present) continue;
+    CREATE_TRY (cudaMalloc (&s->f[f], (size_t) s->field_cells * s->cell));
+    CREATE_TRY (cudaMemsetAsync (s->f[f], 0, (size_t) s->field_cells * s->cell, s->s_compute));
+  }
+  CREATE_TRY (cudaMalloc (&s->eps, (size_t) s->mat_vals * s->fp));
+  CREATE_TRY (cudaMalloc (&s->mu, (size_t) s->mat_vals * s->fp));
+  if (cfg->use_tfsf)
+  {
+    CREATE_TRY (cudaMalloc (&s->einc, (size_t) s->ninc * s->cell));
+    CREATE_TRY (cudaMalloc (&s->hinc, (size_t) s->ninc * s->cell));
+    CREATE_TRY (cudaMemsetAsync (s->einc, 0, (size_t) s->ninc * s->cell, s->s_compute));
+    CREATE_TRY (cudaMemsetAsync (s->hinc, 0, (size_t) s->ninc * s->cell, s->s_compute));
+  }
+  long long tlen = 0;
+  for (int a = 0; a < 3; ++a) { long long l = round_up ((long long) s->sigma[a].size (), 128 / s->fp) + 128 / s->fp; if (l > tlen) tlen = l; }
+  if (tlen < s->pitchM + 128 / s->fp) tlen = s->pitchM + 128 / s->fp;
+  s->tab_stride = (size_t) tlen * s->fp;
+  CREATE_TRY (cudaMalloc (&s->tab_mem, (size_t) N_TABLES * s->tab_stride));
+  CREATE_TRY (cudaMalloc ((void **) &s->step, sizeof (long long)));
+  CREATE_TRY (cudaMemsetAsync (s->step, 0, sizeof (long long), s->s_compute));
+  s->staging_bytes = (size_t) 64 << 20;
+  {
+    /* one i-row of the largest field must fit */
+    const size_t need = (size_t) (s->ny + 1) * (s->nzg + 1) * (s->cell > s->fp ? s->cell : s->fp);
+    if (need > s->staging_bytes) s->staging_bytes = need;
+  }
+  CREATE_TRY (cudaMalloc (&s->staging, s->staging_bytes));
+  CREATE_TRY (cudaMalloc ((void **) &s->red_partials, sizeof (double) * (size_t) sumsq_partial_count ()));
+  CREATE_TRY (cudaMalloc ((void **) &s->red_out, sizeof (double)));
+#undef CREATE_TRY
+
+  *out = s;
+  if ((rc = fdtd_fill (s, FDTD_EPS, 1.0, 0.0)) || (rc = fdtd_fill (s, FDTD_MU, 1.0, 0.0)) || (rc = build_tables_any (s)))
+  {
+    fdtd_destroy (s);
+    *out = NULL;
+    return rc;
+  }
+  return FDTD_OK;
+}
+
+int fdtd_destroy (fdtd_handle s)
+{
+  if (!s) return FDTD_OK;
+  cudaSetDevice (s->cfg.device);
+  if (s->s_compute) cudaStreamSynchronize (s->s_compute);
+  if (s->s_comm) cudaStreamSynchronize (s->s_comm);
+  if (s->comm)
+  {
+    const NcclApi *nccl = nccl_api (NULL);
+    if (nccl) nccl->CommDestroy (s->comm);
+  }
+  for (int f = 0; f < 12; ++f) if (s->f[f]) cudaFree (s->f[f]);
+  void *ptrs[] = { s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->step, s->staging, s->red_partials, s->red_out };
+  for (void *p : ptrs) if (p) cudaFree (p);
+  cudaEvent_t evs[] = { s->ev_start, s->ev_stop, s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx };
+  for (cudaEvent_t e : evs) if (e) cudaEventDestroy (e);
+  for (cudaEvent_t e : s->prof_ev) cudaEventDestroy (e);
+  if (s->s_compute) cudaStreamDestroy (s->s_compute);
+  if (s->s_comm) cudaStreamDestroy (s->s_comm);
+  delete s;
+  return FDTD_OK;
+}
+
+int fdtd_set_sigma (fdtd_handle s, int axis, const void *profile, int64_t count)
+{
+  if (!s || !profile) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  if (axis < 0 || axis >= s->cfg.dims) return fail (FDTD_INVALID_ARGUMENT, "axis %d", axis);
+  if (count != (int64_t) s->sigma[axis].size ()) return fail (FDTD_INVALID_ARGUMENT, "sigma profile along axis %d needs %zu values, got %lld", axis, s->sigma[axis].size (), (long long) count);
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  int rc = sync_run (s);
+  if (rc) return rc;
+  for (int64_t i = 0; i < count; ++i)
+    s->sigma[axis][(size_t) i] = s->fp == 4 ? (double) ((const float *) profile)[i] : ((const double *) profile)[i];
+  return build_tables_any (s);
+}
+
+int fdtd_upload (fdtd_handle s, int field, const void *host, int order, int64_t z0, int64_t nz)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  return transfer (s, field, (void *) host, order, z0, nz, true);
+}
+
+int fdtd_download (fdtd_handle s, int field, void *host, int order, int64_t z0, int64_t nz)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  return transfer (s, field, host, order, z0, nz, false);
+}
+
+int fdtd_fill (fdtd_handle s, int field, double re, double im)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  int rc = sync_run (s);
+  if (rc) return rc;
+  FieldInfo fi;
+  rc = field_info (s, field, &fi);
+  if (rc) return rc;
+  const bool material = field == FDTD_EPS || field == FDTD_MU;
+  long long count = fi.is_inc ? s->ninc : (material ? s->mat_vals : s->field_cells);
+  alignas (16) char pat[16];
+  memset (pat, 0, sizeof (pat));
+  if (s->fp == 4)
+  {
+    float v[2] = { (float) re, (float) im };
+    memcpy (pat, v, material || s->nc == 1 ? 4 : 8);
+  }
+  else
+  {
+    double v[2] = { re, im };
+    memcpy (pat, v, material || s->nc == 1 ? 8 : 16);
+  }
+  CUDA_TRY (launch_fill (fi.dev, count, fi.cell, pat, s->s_compute));
+  s->launches++;
+  CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+  return FDTD_OK;
+}
+
+int fdtd_init_eps_sphere (fdtd_handle s, double cx, double cy, double cz, double radius, double eps_inside)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  if (s->cfg.dims != 3) return fail (FDTD_INVALID_ARGUMENT, "the eps sphere is a Scheme3D feature");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  int rc = sync_run (s);
+  if (rc) return rc;
+  if (s->fp == 4)
+    CUDA_TRY (launch_eps_sphere<float> ((float *) s->eps, s->nx + 1, s->ny + 1, s->nzm, s->kz0, s->pitchM, s->psM, (float) cx, (float) cy, (float) cz, (float) radius, (float) eps_inside, s->s_compute));
+  else
+    CUDA_TRY (launch_eps_sphere<double> ((double *) s->eps, s->nx + 1, s->ny + 1, s->nzm, s->kz0, s->pitchM, s->psM, cx, cy, cz, radius, eps_inside, s->s_compute));
+  s->launches++;
+  CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+  return FDTD_OK;
+}
+
+int fdtd_run_async (fdtd_handle s, int64_t nsteps)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  return run_async (s, nsteps);
+}
+
+int fdtd_sync (fdtd_handle s)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  return sync_run (s);
+}
+
+int fdtd_run (fdtd_handle s, int64_t nsteps)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  int rc = run_async (s, nsteps);
+  if (rc) return rc;
+  return sync_run (s);
+}
+
+int fdtd_last_run_ms (fdtd_handle s, float *ms)
+{
+  if (!s || !ms) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  *ms = s->last_ms;
+  return FDTD_OK;
+}
+
+int fdtd_set_profiling (fdtd_handle s, int enable)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  int rc = sync_run (s);
+  if (rc) return rc;
+  s->profiling = enable != 0;
+  if (!s->profiling) s->prof_steps = 0;
+  return FDTD_OK;
+}
+
+int fdtd_phase_times (fdtd_handle s, float *e_ms, float *h_ms, int64_t *steps)
+{
+  if (!s || !e_ms || !h_ms || !steps) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  int rc = sync_run (s);
+  if (rc) return rc;
+  *e_ms = s->prof_e_ms; *h_ms = s->prof_h_ms; *steps = s->prof_steps;
+  return FDTD_OK;
+}
+
+int fdtd_launch_count (fdtd_handle s, int64_t *count)
+{
+  if (!s || !count) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  *count = s->launches;
+  return FDTD_OK;
+}
+
+int fdtd_get_time_step (fdtd_handle s, int64_t *t)
+{
+  if (!s || !t) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  *t = s->t;
+  return FDTD_OK;
+}
+
+int fdtd_field_sumsq (fdtd_handle s, int field, double *out)
+{
+  if (!s || !out) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  int rc = sync_run (s);
+  if (rc) return rc;
+  FieldInfo fi;
+  rc = field_info (s, field, &fi);
+  if (rc) return rc;
+  const bool material = field == FDTD_EPS || field == FDTD_MU;
+  const int scal_per_cell = material ? 1 : s->nc;
+  cudaStream_t S = s->s_compute;
+  if (fi.is_inc)
+  {
+    if (s->fp == 4) CUDA_TRY (launch_sumsq<float> ((const float *) fi.dev, (int) (s->ninc * s->nc), 1, 0, s->red_partials, s->red_out, S));
+    else CUDA_TRY (launch_sumsq<double> ((const double *) fi.dev, (int) (s->ninc * s->nc), 1, 0, s->red_partials, s->red_out, S));
+  }
+  else
+  {
+    /* owned planes are contiguous rows: plane 1 .. nzl_planes */
+    const long long nrows = (long long) fi.ny * fi.nzl_planes;
+    const char *base = (const char *) fi.dev + (size_t) fi.ps * fi.cell;
+    if (s->fp == 4) CUDA_TRY (launch_sumsq<float> ((const float *) base, fi.nx * scal_per_cell, nrows, (long long) fi.pitch * scal_per_cell, s->red_partials, s->red_out, S));
+    else CUDA_TRY (launch_sumsq<double> ((const double *) base, fi.nx * scal_per_cell, nrows, (long long) fi.pitch * scal_per_cell, s->red_partials, s->red_out, S));
+  }
+  s->launches += 2;
+  CUDA_TRY (cudaMemcpyAsync (out, s->red_out, sizeof (double), cudaMemcpyDeviceToHost, S));
+  CUDA_TRY (cudaStreamSynchronize (S));
+  return FDTD_OK;
+}
+
+int fdtd_comm_unique_id (void *id128)
+{
+  if (!id128) return fail (FDTD_INVALID_ARGUMENT, "NULL id buffer");
+  const char *why = NULL;
+  const NcclApi *nccl = nccl_api (&why);
+  if (!nccl) return fail (FDTD_COMM_ERROR, "NCCL unavailable: %s", why);
+  NcclUniqueId id;
+  NCCL_TRY (nccl->GetUniqueId (&id));
+  memcpy (id128, &id, sizeof (id));
+  return FDTD_OK;
+}
+
+int fdtd_comm_init (fdtd_handle s, const void *id128)
+{
+  if (!s || !id128) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  if (s->cfg.nranks < 2) return FDTD_OK;
+  const char *why = NULL;
+  const NcclApi *nccl = nccl_api (&why);
+  if (!nccl) return fail (FDTD_COMM_ERROR, "NCCL unavailable: %s", why);
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  NcclUniqueId id;
+  memcpy (&id, id128, sizeof (id));
+  NCCL_TRY (nccl->CommInitRank (&s->comm, s->cfg.nranks, id, s->cfg.rank));
+  return FDTD_OK;
+}
+
+int fdtd_execute_steps (int *status, const fdtd_config *cfg, fdtd_host_arrays *arr, int64_t total_steps)
+{
+  if (status) *status = FDTD_ERROR;
+  if (!arr) return fail (FDTD_INVALID_ARGUMENT, "NULL arrays");
+  fdtd_handle h = NULL;
+  int rc = fdtd_create (cfg, &h);
+  if (rc) return rc;
+  const int64_t nzf = cfg->dims == 3 ? cfg->size[2] : 1;
+  const int64_t nzm = cfg->dims == 3 ? cfg->size[2] + 1 : 1;
+  const int64_t kz0 = h->kz0, nzl = h->nzl;
+  /* host arrays hold the whole grid; each rank moves its own slab */
+  (void) kz0; (void) nzl;
+  do
+  {
+    for (int a = 0; a < cfg->dims && !rc; ++a)
+      if (arr->sigma[a]) rc = fdtd_set_sigma (h, a, arr->sigma[a], cfg->size[a] + 1);
+    if (rc) break;
+    if (arr->eps && (rc = fdtd_upload (h, FDTD_EPS, arr->eps, FDTD_ORDER_REFERENCE, 0, nzm))) break;
+    if (arr->mu && (rc = fdtd_upload (h, FDTD_MU, arr->mu, FDTD_ORDER_REFERENCE, 0, nzm))) break;
+    for (int f = 0; f < 12 && !rc; ++f)
+      if (arr->field[f] && h->f[f]) rc = fdtd_upload (h, f, arr->field[f], FDTD_ORDER_REFERENCE, 0, nzf);
+    if (rc) break;
+    if (cfg->use_tfsf)
+    {
+      if (arr->einc && (rc = fdtd_upload (h, FDTD_EINC, arr->einc, FDTD_ORDER_REFERENCE, 0, 1))) break;
+      if (arr->hinc && (rc = fdtd_upload (h, FDTD_HINC, arr->hinc, FDTD_ORDER_REFERENCE, 0, 1))) break;
+    }
+    if ((rc = fdtd_run (h, total_steps))) break;
+    for (int f = 0; f < 12 && !rc; ++f)
+      if (arr->field[f] && h->f[f]) rc = fdtd_download (h, f, arr->field[f], FDTD_ORDER_REFERENCE, 0, nzf);
+    if (rc) break;
+    if (cfg->use_tfsf)
+    {
+      if (arr->einc && (rc = fdtd_download (h, FDTD_EINC, arr->einc, FDTD_ORDER_REFERENCE, 0, 1))) break;
+      if (arr->hinc && (rc = fdtd_download (h, FDTD_HINC, arr->hinc, FDTD_ORDER_REFERENCE, 0, 1))) break;
+    }
+  } while (0);
+  std::string keep = g_last_error;
+  fdtd_destroy (h);
+  if (rc) { g_last_error = keep; return rc; }
+  if (status) *status = FDTD_OK;
+  return FDTD_OK;
+}
+
+} /* extern "C" */

@@ -113,6 +113,17 @@ const char *fdtd_last_error (void);
  * (name, SM count, memory, theoretical bandwidth) into buf. */
 int fdtd_device_info (int device, char *buf, int64_t buflen);
 
+/* Host-only helpers (no device needed) that derive the time step's scalar inputs the way the reference
+ * does.  fdtd_init_scheme: from cfg->dims, value_type, size, dx and the CLI-style wavelength / angles in
+ * degrees (--wavelength, --angle-teta/phi/psi) fills dx (rounded to FPValue), dt, source_frequency,
+ * rel_phase_velocity, the three angles in radians and the reference's point-source position --
+ * Scheme3D::initScheme (Source/Scheme/Scheme3D.cpp:3387-3402), SchemeTMz::initScheme
+ * (Source/Scheme/SchemeTMz.cpp:1948-1956, 35-49) and Source/main.cpp:79-85,148.
+ * fdtd_pml_sigma_profile: the 1-D conductivity profile Scheme3D::initGrids writes along `axis`
+ * (Source/Scheme/Scheme3D.cpp:3656-3818), size[axis]+1 FPValues, to be passed to fdtd_set_sigma. */
+int fdtd_init_scheme (fdtd_config *cfg, double wavelength, double teta_deg, double phi_deg, double psi_deg);
+int fdtd_pml_sigma_profile (const fdtd_config *cfg, int axis, void *out, int64_t count);
+
 /* Allocates the device-resident state of one Scheme (all fields zero, eps = mu = 1, sigma = 0).
  * Stands in for the cudaMalloc block of cudaExecute3DSteps (Source/Cuda/CudaInterface.cu:420-470),
  * but the handle keeps the memory between calls so the timed loop has no allocation or copy. */
@@ -150,6 +161,14 @@ int fdtd_sync (fdtd_handle h);
 /* Device time of the last completed fdtd_run / fdtd_run_async+fdtd_sync, from CUDA events on the
  * solver's stream (milliseconds). */
 int fdtd_last_run_ms (fdtd_handle h, float *ms);
+
+/* Per-kernel timing for the roofline report: when enabled, the two half-step kernels of every step of a
+ * single-rank run are bracketed by CUDA events on the solver's stream (capacity: the steps of one run).
+ * fdtd_phase_times returns, for the last completed run, the summed device time of the E-phase and H-phase
+ * kernels (milliseconds) and the number of steps they cover.  The reference's only timing is gettimeofday
+ * around performSteps (Source/main.cpp:153-158). */
+int fdtd_set_profiling (fdtd_handle h, int enable);
+int fdtd_phase_times (fdtd_handle h, float *e_ms, float *h_ms, int64_t *steps);
 
 /* Number of kernels of this library launched by this handle since creation (bench.py's gpu_launches). */
 int fdtd_launch_count (fdtd_handle h, int64_t *count);

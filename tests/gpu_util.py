@@ -1,0 +1,69 @@
+"""Helpers shared by the GPU parity tests: run the CUDA path through the C ABI on given inputs."""
+import numpy as np
+
+import fdtd3d_b200 as F
+import oracle_lib as O
+
+
+def run_gpu(cfg, nsteps, inputs=None, fields=None, order=F.ORDER_REFERENCE, chunks=None):
+    """Mirror of oracle_lib.run(): same inputs, same output dict, computed by libfdtd3d_b200."""
+    inputs = inputs or {}
+    fields = fields or {}
+    with F.Solver(cfg) as s:
+        for a in range(cfg.dims):
+            key = "Sigma" + "XYZ"[a]
+            if key in inputs:
+                s.set_sigma(a, inputs[key])
+        for key in ("Eps", "Mu"):
+            if key in inputs:
+                s.upload(key, inputs[key])
+        for name in O.field_names(cfg):
+            if name in fields:
+                s.upload(name, fields[name])
+        if cfg.use_tfsf:
+            for name in ("EInc", "HInc"):
+                if name in fields:
+                    s.upload(name, fields[name])
+        if chunks:
+            for n in chunks:
+                s.run(n)
+        else:
+            s.run(nsteps)
+        out = {name: s.download(name) for name in O.field_names(cfg)}
+        if cfg.use_tfsf:
+            out["EInc"] = s.download("EInc")
+            out["HInc"] = s.download("HInc")
+        out["_launches"] = s.launch_count
+    return out
+
+
+def rel_err(a, b):
+    """max |a-b| / max |b| (absolute floor = the field's own scale, SURVEY.md §8c note)."""
+    scale = np.abs(b).max()
+    if scale == 0:
+        return float(np.abs(a).max())
+    return float(np.abs(a - b).max() / scale)
+
+
+def random_inputs(cfg, seed):
+    """Random eps/mu in [1,4], sigma profiles from the oracle, random small initial fields."""
+    rng = np.random.default_rng(seed)
+    rd, fd = O.real_dtype(cfg), O.field_dtype(cfg)
+    mz = cfg.size[2] + 1 if cfg.dims == 3 else 1
+    nm = (cfg.size[0] + 1) * (cfg.size[1] + 1) * mz
+    inputs = {"Eps": rng.uniform(1.0, 4.0, nm).astype(rd), "Mu": rng.uniform(1.0, 2.0, nm).astype(rd)}
+    for a in range(cfg.dims):
+        inputs["Sigma" + "XYZ"[a]] = O.sigma_profile(cfg, a) if cfg.use_pml else np.zeros(cfg.size[a] + 1, rd)
+    n = O.n_cells(cfg)
+    fields = {}
+    for name in O.field_names(cfg):
+        scale = 1.0 if name[0] in "ED" else 2.6e-3
+        if name[0] == "D":
+            scale = 8.85e-12
+        if name[0] == "B":
+            scale = 3.3e-9
+        v = rng.standard_normal(n)
+        if cfg.complex_values:
+            v = v + 1j * rng.standard_normal(n)
+        fields[name] = (v * scale).astype(fd)
+    return inputs, fields

@@ -1,0 +1,182 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against
+
+  (1) dumps of the unmodified reference solver (tests/golden/), and
+  (2) the pinned Tier-2 oracle on seeded random inputs, ragged sizes and edge cases.
+
+Bar (BASELINE.json north_star): index/halo bookkeeping bit-exact; field values within max relative
+error 1e-12 (double) / 1e-5 (float).  exact mode (reference operand order, IEEE division, no FMA
+contraction: -fmad=false) is held to BIT-EXACT equality with the reference in double; fast mode
+(reciprocal tables + explicit FMA) to the stated tolerances.
+"""
+import numpy as np
+import pytest
+
+import fdtd3d_b200 as F
+import golden_cases as G
+import oracle_lib as O
+from gpu_util import random_inputs, rel_err, run_gpu
+
+pytestmark = pytest.mark.gpu
+
+TOL = {8: 1e-12, 4: 1e-5}
+
+
+def _keys(cfg):
+    return O.field_names(cfg) + (["EInc", "HInc"] if cfg.use_tfsf else [])
+
+
+@pytest.mark.parametrize("name", G.case_names())
+def test_exact_mode_matches_reference_dump(name):
+    meta, data = G.load(name)
+    cfg = G.config_from_meta(meta, exact_mode=1)
+    out = run_gpu(cfg, meta["steps"], G.inputs_from_golden(cfg, data))
+    assert out["_launches"] > 0
+    for key in _keys(cfg):
+        if cfg.value_type == 8:
+            assert np.array_equal(out[key], data[key]), "%s not bit-exact: rel err %g" % (key, rel_err(out[key], data[key]))
+        else:
+            assert rel_err(out[key], data[key]) <= TOL[4], key
+
+
+@pytest.mark.parametrize("name", G.case_names())
+def test_fast_mode_within_tolerance_of_reference_dump(name):
+    meta, data = G.load(name)
+    cfg = G.config_from_meta(meta, exact_mode=0)
+    out = run_gpu(cfg, meta["steps"], G.inputs_from_golden(cfg, data))
+    for key in _keys(cfg):
+        assert rel_err(out[key], data[key]) <= TOL[cfg.value_type], "%s: %g" % (key, rel_err(out[key], data[key]))
+
+
+RANDOM_CASES = [
+    # dims, size, pml, tfsf, use_pml, use_tfsf, value_type, complex, steps, angles
+    (3, (37, 21, 19), 4, 6, True, True, 8, False, 12, (90, 0, 90)),
+    (3, (18, 35, 23), 4, 6, True, True, 8, False, 12, (50, 70, 20)),
+    (3, (33, 17, 40), 4, 6, True, False, 8, False, 10, (90, 0, 90)),
+    (3, (20, 20, 20), 3, 5, False, True, 8, False, 10, (90, 90, 0)),
+    (3, (16, 19, 17), 3, 5, False, False, 8, True, 10, (90, 0, 90)),
+    (3, (17, 18, 19), 3, 5, True, True, 8, True, 10, (30, 60, 45)),
+    (3, (35, 22, 18), 4, 6, True, True, 4, False, 12, (90, 0, 90)),
+    (3, (21, 22, 23), 4, 6, True, True, 4, True, 10, (90, 0, 90)),
+    (3, (5, 4, 3), 1, 1, True, False, 8, False, 6, (90, 0, 90)),
+    (2, (75, 40), 5, 8, True, False, 8, False, 20, (90, 0, 90)),
+    (2, (131, 77), 6, 9, True, True, 8, False, 20, (90, 0, 90)),
+    (2, (90, 33), 5, 8, False, True, 8, True, 20, (90, 0, 90)),
+    (2, (200, 45), 5, 8, True, True, 4, False, 20, (90, 0, 90)),
+    (2, (100, 50), 5, 8, True, False, 4, True, 20, (90, 0, 90)),
+]
+
+
+@pytest.mark.parametrize("case", RANDOM_CASES, ids=lambda c: "%dd-%s-p%dt%d-vt%d%s" % (c[0], "x".join(map(str, c[1])), c[4], c[5], c[6], "c" if c[7] else ""))
+@pytest.mark.parametrize("exact", [1, 0])
+def test_random_inputs_against_oracle(case, exact):
+    dims, size, pml, tfsf, use_pml, use_tfsf, vt, cplx, steps, ang = case
+    src = (size[0] // 2, size[1] // 2, size[2] // 2) if dims == 3 else (min(70, size[0] - 2), size[1] // 2, 0)
+    cfg = O.make_config(dims=dims, size=size, pml=pml, tfsf=tfsf, use_pml=use_pml, use_tfsf=use_tfsf, value_type=vt,
+                        complex_values=cplx, theta=ang[0], phi=ang[1], psi=ang[2], exact_mode=exact, source_pos=src)
+    inputs, fields = random_inputs(cfg, seed=1234 + steps)
+    ref = O.run(cfg, steps, inputs, fields)
+    out = run_gpu(cfg, steps, inputs, fields)
+    for key in _keys(cfg):
+        if exact and vt == 8:
+            assert np.array_equal(out[key], ref[key]), "%s not bit-exact: rel err %g" % (key, rel_err(out[key], ref[key]))
+        else:
+            assert rel_err(out[key], ref[key]) <= TOL[vt], "%s: %g" % (key, rel_err(out[key], ref[key]))
+
+
+def test_chunked_runs_equal_one_run():
+    """performNSteps (startStep, n): running 7 + 1 + 12 steps is the same as 20 steps (time index carries over)."""
+    cfg = O.make_config(size=(24, 20, 22), pml=4, tfsf=6, use_pml=True, use_tfsf=False, exact_mode=1)
+    inputs, fields = random_inputs(cfg, seed=7)
+    a = run_gpu(cfg, 20, inputs, fields)
+    b = run_gpu(cfg, 20, inputs, fields, chunks=[7, 1, 12])
+    for key in _keys(cfg):
+        assert np.array_equal(a[key], b[key]), key
+
+
+def test_compute_ranges_leave_border_cells_untouched():
+    """Cells outside the compute boxes of YeeGridLayout.h:131-182 keep their initial value bit for bit."""
+    cfg = O.make_config(size=(12, 11, 10), pml=2, tfsf=3, use_pml=True, use_tfsf=False, exact_mode=1)
+    inputs, fields = random_inputs(cfg, seed=3)
+    out = run_gpu(cfg, 3, inputs, fields)
+    N = (12, 11, 10)
+    lo = {"Ex": (0, 1, 1), "Ey": (1, 0, 1), "Ez": (1, 1, 0), "Hx": (1, 0, 0), "Hy": (0, 1, 0), "Hz": (0, 0, 1)}
+    hi = {"Ex": (1, 0, 0), "Ey": (0, 1, 0), "Ez": (0, 0, 1), "Hx": (0, 1, 1), "Hy": (1, 0, 1), "Hz": (1, 1, 0)}
+    for name in lo:
+        for aux in (name, {"E": "D", "H": "B"}[name[0]] + name[1]):
+            a, b = out[aux].reshape(N), fields[aux].reshape(N)
+            mask = np.ones(N, bool)
+            sl = tuple(slice(lo[name][d], N[d] - hi[name][d]) for d in range(3))
+            mask[sl] = False
+            if name == "Ez" and aux == "Ez":
+                mask[6, 5, 5] = False  # the point source cell
+            assert np.array_equal(a[mask], b[mask]), aux
+            assert not np.array_equal(a[sl], b[sl]), aux
+
+
+@pytest.mark.parametrize("vt,cplx", [(8, False), (8, True), (4, False), (4, True)])
+def test_upload_download_round_trip(vt, cplx):
+    cfg = O.make_config(size=(19, 13, 11), pml=2, tfsf=3, use_pml=True, use_tfsf=True, value_type=vt, complex_values=cplx)
+    rng = np.random.default_rng(5)
+    with F.Solver(cfg) as s:
+        for name in ["Ex", "Hz", "Dy", "Bz", "Eps", "Mu", "EInc"]:
+            shape = s.field_shape(name)
+            fid = F.FIELD_IDS[name]
+            dt = O.real_dtype(cfg) if name in ("Eps", "Mu") else O.field_dtype(cfg)
+            a = rng.standard_normal(int(np.prod(shape))).astype(dt)
+            s.upload(name, a)
+            assert np.array_equal(s.download(name), a), name
+            if len(shape) == 3:
+                # native order is the transpose of reference order
+                nat = s.download(name, order=F.ORDER_NATIVE)
+                assert np.array_equal(nat.reshape(shape[::-1]), a.reshape(shape).transpose(2, 1, 0)), name
+                # partial plane range, both directions
+                part = s.download(name, z0=3, nz=4)
+                assert np.array_equal(part.reshape(shape[0], shape[1], 4), a.reshape(shape)[:, :, 3:7]), name
+                b = rng.standard_normal(shape[0] * shape[1] * 2).astype(dt)
+                s.upload(name, b, z0=5, nz=2)
+                full = a.reshape(shape).copy()
+                full[:, :, 5:7] = b.reshape(shape[0], shape[1], 2)
+                assert np.array_equal(s.download(name).reshape(shape), full), name
+                s.upload(name, np.ascontiguousarray(full.transpose(2, 1, 0)), order=F.ORDER_NATIVE)
+                assert np.array_equal(s.download(name).reshape(shape), full), name
+                sq = float((np.abs(full.astype(np.complex128 if cplx else np.float64)) ** 2).sum())
+                assert abs(s.sumsq(name) - sq) <= 1e-12 * sq, name
+
+
+def test_device_eps_sphere_matches_reference_init():
+    """fdtd_init_eps_sphere == Approximation::approximateSphere as run by Scheme3D::initGrids, bit for bit."""
+    for vt in (8, 4):
+        cfg = O.make_config(size=(47, 52, 45), value_type=vt)
+        with F.Solver(cfg) as s:
+            s.init_eps_sphere()
+            assert np.array_equal(s.download("Eps"), O.eps_sphere(cfg))
+
+
+def test_one_shot_execute_steps():
+    """fdtd_execute_steps, the drop-in for cudaExecute3DSteps / cudaExecute2DTMzSteps."""
+    for dims, size in ((3, (22, 20, 18)), (2, (80, 30))):
+        cfg = O.make_config(dims=dims, size=size, pml=4, tfsf=6, use_pml=True, use_tfsf=True, exact_mode=1)
+        inputs, fields = random_inputs(cfg, seed=11)
+        ref = O.run(cfg, 9, inputs, fields)
+        arrays = {k: v.copy() for k, v in fields.items()}
+        arrays.update(inputs)
+        n_inc = O.inc_len(cfg)
+        arrays["EInc"] = np.zeros(n_inc, O.field_dtype(cfg))
+        arrays["HInc"] = np.zeros(n_inc, O.field_dtype(cfg))
+        assert F.execute_steps(cfg, arrays, 9) == F.OK
+        for key in _keys(cfg):
+            assert np.array_equal(arrays[key], ref[key]), key
+
+
+def test_errors_are_reported_not_fatal():
+    cfg = O.make_config(size=(16, 16, 16), pml=3, tfsf=4)
+    with F.Solver(cfg) as s:
+        with pytest.raises(F.FdtdError) as e:
+            s.set_sigma(0, np.zeros(5))
+        assert e.value.code == F.INVALID_ARGUMENT
+        with pytest.raises(F.FdtdError):
+            s.download("Ex", z0=10, nz=20)
+    bad = O.make_config(size=(16, 16, 16), pml=3, tfsf=4)
+    bad.tfsf_size[0] = 8
+    with pytest.raises(F.FdtdError):
+        F.Solver(bad)
