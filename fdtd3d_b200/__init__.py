@@ -15,7 +15,8 @@ from ._capi import (ABI_VERSION, Config, HostArrays, FIELD_IDS, FIELD_NAMES, ORD
                     OK, ERROR, INVALID_ARGUMENT, NO_DEVICE, COMM_ERROR)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfdtd3d_b200.so")
+# FDTD3D_B200_LIB selects another build of the same library (kernel tuning experiments, tools/)
+LIB_PATH = os.environ.get("FDTD3D_B200_LIB") or os.path.join(_HERE, "libfdtd3d_b200.so")
 
 _lib = None
 

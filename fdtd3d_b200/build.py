@@ -14,8 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libfdtd3d_b200.so")
-SOURCES = ["kernels3d.cu", "kernels2d.cu", "aux_kernels.cu", "solver.cu", "scheme_init.cpp"]
-HEADERS = ["fdtd_device.cuh", "launch.h", "nccl_dl.h", os.path.join("..", "..", "include", "fdtd3d_b200.h")]
+SOURCES = ["kernels3d_tma.cu", "kernels3d.cu", "kernels2d.cu", "aux_kernels.cu", "solver.cu", "scheme_init.cpp"]
+HEADERS = ["fdtd_device.cuh", "kernels3d_common.cuh", "launch.h", "nccl_dl.h", os.path.join("..", "..", "include", "fdtd3d_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
@@ -27,7 +27,21 @@ def _newer(src, dst):
     return not os.path.exists(dst) or os.path.getmtime(src) > os.path.getmtime(dst)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, defines=(), lib=None, build_dir=None):
+    """defines: extra -D flags (kernel tuning knobs); lib / build_dir: where a variant build goes."""
+    global BUILD, LIB
+    saved = (BUILD, LIB)
+    if lib:
+        LIB = lib
+    if build_dir:
+        BUILD = build_dir
+    try:
+        return _build(force, verbose, list(defines))
+    finally:
+        BUILD, LIB = saved
+
+
+def _build(force, verbose, defines):
     os.makedirs(BUILD, exist_ok=True)
     hdr_paths = [os.path.normpath(os.path.join(CSRC, h)) for h in HEADERS] + [os.path.abspath(__file__)]
     jobs = []
@@ -39,7 +53,7 @@ def build(force=False, verbose=False):
 
     def compile_one(job):
         sp, obj = job
-        cmd = [NVCC] + NVCC_FLAGS + ["-c", sp, "-o", obj]
+        cmd = [NVCC] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-c", sp, "-o", obj]
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         with open(obj + ".log", "w") as f:
             f.write(" ".join(cmd) + "\n" + r.stdout)

@@ -75,38 +75,43 @@ struct StepParams
   double cphi, sphi;      /* TMz: cos / sin of incidentWaveAngle */
 };
 
-/* 16-byte vector of W scalars */
+/* vector of W scalars moved with one 4-, 8- or 16-byte access */
 template <typename T, int W>
-struct alignas (16) Vec
+struct alignas (sizeof (T) * W) Vec
 {
   T v[W];
 };
 
+template <int BYTES> struct RawVec;
+template <> struct RawVec<4> { typedef int type; };
+template <> struct RawVec<8> { typedef int2 type; };
+template <> struct RawVec<16> { typedef int4 type; };
+
+/* read-only path (arrays this kernel does not write) */
 template <typename T, int W>
 __device__ __forceinline__ Vec<T, W> ldv (const T *p)
 {
-  static_assert (sizeof (T) * W == 16 || sizeof (T) * W == 8, "vector width");
+  typedef typename RawVec<sizeof (T) * W>::type R;
   Vec<T, W> r;
-  if (sizeof (T) * W == 16)
-    *reinterpret_cast<int4 *> (&r) = __ldg (reinterpret_cast<const int4 *> (p));
-  else
-    *reinterpret_cast<int2 *> (&r) = __ldg (reinterpret_cast<const int2 *> (p));
+  *reinterpret_cast<R *> (&r) = __ldg (reinterpret_cast<const R *> (p));
   return r;
 }
 
-/* plain (coherent) 16-byte load for arrays this kernel also writes */
+/* plain (coherent) load for arrays this kernel also writes */
 template <typename T, int W>
 __device__ __forceinline__ Vec<T, W> ldv_rw (const T *p)
 {
+  typedef typename RawVec<sizeof (T) * W>::type R;
   Vec<T, W> r;
-  *reinterpret_cast<int4 *> (&r) = *reinterpret_cast<const int4 *> (p);
+  *reinterpret_cast<R *> (&r) = *reinterpret_cast<const R *> (p);
   return r;
 }
 
 template <typename T, int W>
 __device__ __forceinline__ void stv (T *p, const Vec<T, W> &r)
 {
-  *reinterpret_cast<int4 *> (p) = *reinterpret_cast<const int4 *> (&r);
+  typedef typename RawVec<sizeof (T) * W>::type R;
+  *reinterpret_cast<R *> (p) = *reinterpret_cast<const R *> (&r);
 }
 
 template <typename T> __device__ __forceinline__ T fma_t (T a, T b, T c);

@@ -1,0 +1,768 @@
+/*
+ * 3D Yee leapfrog half-step kernels for sm_100a, TMA-staged version (the production path).
+ *
+ * Same arithmetic and fusion as kernels3d.cu (see there for the reference citations of each formula):
+ * one pass per half step updates the three components, their auxiliary D/B fields, E-from-D / H-from-B,
+ * the TF/SF correction and the point source, in place.  What differs is how the data reaches the SM.
+ *
+ * The direct version keeps every in-flight byte in registers (19 x 16-byte loads per thread, > 200
+ * registers, one 8-warp CTA per SM) and tops out at about two thirds of the HBM roofline because too few
+ * bytes are in flight (profiles/r1_direct_*).  Here a CTA owns an (x, y) tile of 32*V x 8 cells and marches
+ * along z; for each plane ONE elected thread issues one TMA box copy (cp.async.bulk.tensor.3d) per array
+ * into a 4-deep ring of shared-memory stages (about 42 KB each), each stage completing on its own
+ * mbarrier.  The boxes of the arrays whose neighbours the stencil needs carry a one-vector x halo and / or
+ * a one-row y halo, so the y and x neighbours are read from shared memory and no value is fetched twice by
+ * a CTA; the z neighbour is carried in registers from plane to plane.  Three stages (~125 KB per SM) are
+ * in flight while one is being consumed, independent of register pressure.  Out-of-range parts of a box
+ * (grid edges) are zero-filled by the TMA unit; results are written back with coalesced 128-bit stores.
+ *
+ * Tile geometry (V = cells per 16 bytes = 16 / sizeof(FieldValue)):
+ *   thread (tx, ty) owns cells [i0t + tx*V, +V) of row j0t + ty;  TXC = 32*V cells = 512 bytes per row.
+ *   E phase stage for plane k:  Hz  (TXC+V) x 9 from (i0t-V, j0t-1)   Hy  (TXC+V) x 8 from (i0t-V, j0t)
+ *                               Hx  TXC x 9 from (i0t, j0t-1)         D*, E*  TXC x 8
+ *                               eps (TXC+HM) x 9 of material plane k+1 from (i0t, j0t)
+ *   H phase stage for plane k:  Ex  TXC x 9 of plane k+1              Ey  (TXC+V) x 8 of plane k+1
+ *                               Ez  (TXC+V) x 9 of plane k            B*, H*  TXC x 8
+ *                               mu  (TXC+HM) x 9 of material plane k+1
+ */
+#include <cuda.h>
+
+#include <string>
+
+#include "fdtd_device.cuh"
+#include "kernels3d_common.cuh"
+#include "launch.h"
+
+namespace fdtd
+{
+
+namespace
+{
+
+using namespace k3d;
+
+constexpr int TY = 8;
+constexpr int NTHREADS = 32 * TY;
+constexpr int N_MAPS = 10;
+
+struct TmaSet
+{
+  CUtensorMap m[N_MAPS];
+};
+
+__host__ __device__ constexpr int align128 (int x) { return (x + 127) & ~127; }
+
+template <typename T, int NC, bool PML>
+struct Tile
+{
+  static constexpr int CELL = NC * (int) sizeof (T);
+  static constexpr int V = 16 / CELL;                 /* cells per thread = x halo cells */
+  static constexpr int TXC = 32 * V;                  /* tile cells along x */
+  static constexpr int HM = 16 / (int) sizeof (T);    /* material halo values */
+  static constexpr int ROW = TXC * CELL;              /* 512 bytes */
+  static constexpr int ROW_H = (TXC + V) * CELL;      /* row with x halo: 528 bytes */
+  static constexpr int ROW_M = (TXC + HM) * (int) sizeof (T);
+  static constexpr int N_OWN = PML ? 6 : 3;
+  /* box bytes */
+  static constexpr int SZ_A = ROW_H * (TY + 1);       /* x and y halo */
+  static constexpr int SZ_B = ROW_H * TY;             /* x halo */
+  static constexpr int SZ_C = ROW * (TY + 1);         /* y halo */
+  static constexpr int SZ_OWN = ROW * TY;
+  static constexpr int SZ_M = ROW_M * (TY + 1);
+  static constexpr int OWN_STRIDE = (SZ_OWN + 127) & ~127; /* between the own-cell tiles of a stage */
+  /* stage layout */
+  static constexpr int OFF_A = 0;
+  static constexpr int OFF_B = OFF_A + align128 (SZ_A);
+  static constexpr int OFF_C = OFF_B + align128 (SZ_B);
+  static constexpr int OFF_OWN = OFF_C + align128 (SZ_C);
+  static constexpr int OFF_M = OFF_OWN + N_OWN * align128 (SZ_OWN);
+  static constexpr int STAGE = OFF_M + align128 (SZ_M);
+  static constexpr int TX_BYTES = SZ_A + SZ_B + SZ_C + N_OWN * SZ_OWN + SZ_M;
+  static constexpr int STAGES = (4 * STAGE <= 200 * 1024) ? 4 : 3;
+  static constexpr int SMEM = STAGES * STAGE + 128;
+};
+
+/* ------------------------------------------------------------------ PTX wrappers */
+
+__device__ __forceinline__ unsigned smem_u32 (const void *p) { return (unsigned) __cvta_generic_to_shared (p); }
+
+__device__ __forceinline__ void mbar_init (unsigned long long *bar, int count)
+{
+  asm volatile ("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32 (bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx (unsigned long long *bar, unsigned bytes)
+{
+  asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32 (bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait (unsigned long long *bar, unsigned parity)
+{
+  unsigned ok;
+  asm volatile ("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(ok) : "r"(smem_u32 (bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+/* bounded wait: a mis-programmed pipeline traps (reported as a CUDA error) instead of hanging the GPU */
+__device__ __forceinline__ void mbar_wait (unsigned long long *bar, unsigned parity)
+{
+  unsigned tries = 0;
+  while (!mbar_try_wait (bar, parity))
+  {
+    if (++tries > (1u << 26)) __trap ();
+  }
+}
+__device__ __forceinline__ void tma_load_3d (void *dst, const CUtensorMap *map, unsigned long long *bar, int x, int y, int z)
+{
+  asm volatile ("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                ::"r"(smem_u32 (dst)), "l"(map), "r"(smem_u32 (bar)), "r"(x), "r"(y), "r"(z) : "memory");
+}
+
+template <typename T, int W>
+__device__ __forceinline__ Vec<T, W> lds (const unsigned char *p)
+{
+  typedef typename RawVec<sizeof (T) * W>::type R;
+  Vec<T, W> r;
+  *reinterpret_cast<R *> (&r) = *reinterpret_cast<const R *> (p);
+  return r;
+}
+
+/* ------------------------------------------------------------------ E half step */
+
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
+__global__ void __launch_bounds__ (NTHREADS, 1)
+e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
+{
+  typedef Tile<T, NC, PML> L;
+  constexpr int V = L::V, W = V * NC, S = L::STAGES;
+  typedef Vec<T, W> FVec;
+  typedef Vec<T, V> MVec;
+
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ __align__ (8) unsigned long long full[S];
+  unsigned char *smem = reinterpret_cast<unsigned char *> ((reinterpret_cast<uintptr_t> (smem_raw) + 127) & ~(uintptr_t) 127);
+
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const bool leader = tx == 0 && ty == 0;
+  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * TY;
+  const int i0 = i0t + tx * V, j = j0t + ty;
+  const bool active = i0 < p.nx && j < p.ny;
+  const int k0 = kb + blockIdx.z * p.kchunk;
+  const int k1 = min (k0 + p.kchunk, ke);
+  if (k0 >= k1) return; /* uniform over the CTA */
+
+  /* maps: 0 Hz (A), 1 Hy (B), 2 Hx (C), 3..8 Ex Ey Ez [Dx Dy Dz], 9 eps (M) */
+  auto issue = [&] (int slot, int k)
+  {
+    unsigned char *base = smem + slot * L::STAGE;
+    unsigned long long *bar = &full[slot];
+    mbar_expect_tx (bar, L::TX_BYTES);
+    tma_load_3d (base + L::OFF_A, &maps.m[0], bar, (i0t - V) * NC, j0t - 1, k + 1);
+    tma_load_3d (base + L::OFF_B, &maps.m[1], bar, (i0t - V) * NC, j0t, k + 1);
+    tma_load_3d (base + L::OFF_C, &maps.m[2], bar, i0t * NC, j0t - 1, k + 1);
+#pragma unroll
+    for (int a = 0; a < L::N_OWN; ++a)
+      tma_load_3d (base + L::OFF_OWN + a * L::OWN_STRIDE, &maps.m[3 + a], bar, i0t * NC, j0t, k + 1);
+    tma_load_3d (base + L::OFF_M, &maps.m[9], bar, i0t, j0t, k + 2);
+  };
+
+  if (leader)
+  {
+    for (int s = 0; s < S; ++s) mbar_init (&full[s], 1);
+    asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads ();
+  if (leader)
+  {
+    for (int s = 0; s < S && k0 + s < k1; ++s) issue (s, k0 + s);
+  }
+
+  long long o = (((long long) (k0 + 1) * p.ny + j) * p.pitch + i0) * NC;
+  const long long pl = p.ps * NC;
+  const long long om = ((long long) (k0 + 1) * (p.ny + 1) + j) * p.pitchM + i0;
+
+  T *Ex = p.f[0], *Ey = p.f[1], *Ez = p.f[2];
+  T *Dx = p.f[6], *Dy = p.f[7], *Dz = p.f[8];
+
+  const bool jlo = j >= 1, jhi = j < p.ny - 1;
+
+  T ca_y_at = 0, cbd_y_at = 0, p_y_btw = 0, m_y_btw = 0, q_y_at = 0;
+  MVec p_x_btw = {}, m_x_btw = {}, ca_x_at = {}, cbd_x_at = {}, q_x_at = {};
+  FVec hx_km = {}, hy_km = {};
+  MVec eps_c = {}, eps_jp = {};
+  T eps_ip = 0;
+  if (active)
+  {
+    if (PML)
+    {
+      ca_y_at = p.tab[1][KIND_AT].ca[j];
+      cbd_y_at = p.tab[1][KIND_AT].cbd[j];
+      p_y_btw = p.tab[1][KIND_BTW].p[j];
+      m_y_btw = p.tab[1][KIND_BTW].m[j];
+      q_y_at = EXACT ? p.tab[1][KIND_AT].p[j] : p.tab[1][KIND_AT].invp[j];
+      p_x_btw = ldv<T, V> (p.tab[0][KIND_BTW].p + i0);
+      m_x_btw = ldv<T, V> (p.tab[0][KIND_BTW].m + i0);
+      ca_x_at = ldv<T, V> (p.tab[0][KIND_AT].ca + i0);
+      cbd_x_at = ldv<T, V> (p.tab[0][KIND_AT].cbd + i0);
+      q_x_at = ldv<T, V> ((EXACT ? p.tab[0][KIND_AT].p : p.tab[0][KIND_AT].invp) + i0);
+    }
+    /* z-carried values for the first plane of the chunk, straight from global memory */
+    hx_km = ldv<T, W> (p.f[3] + o - pl);
+    hy_km = ldv<T, W> (p.f[4] + o - pl);
+    eps_c = ldv<T, V> (p.eps + om);
+    eps_jp = ldv<T, V> (p.eps + om + p.pitchM);
+    eps_ip = __ldg (p.eps + om + V);
+  }
+
+  long long step = 0;
+  if (!TFSF) step = *p.step;
+
+  /* per-thread byte offsets inside a stage */
+  const int xo = tx * 16;
+  const unsigned char *sA_own = smem + L::OFF_A + (ty + 1) * L::ROW_H + 16 + xo; /* Hz[j]   */
+  const unsigned char *sA_jm = smem + L::OFF_A + ty * L::ROW_H + 16 + xo;        /* Hz[j-1] */
+  const unsigned char *sB_own = smem + L::OFF_B + ty * L::ROW_H + 16 + xo;       /* Hy[j]   */
+  const unsigned char *sC_own = smem + L::OFF_C + (ty + 1) * L::ROW + xo;        /* Hx[j]   */
+  const unsigned char *sC_jm = smem + L::OFF_C + ty * L::ROW + xo;               /* Hx[j-1] */
+  const unsigned char *sOwn = smem + L::OFF_OWN + ty * L::ROW + xo;
+  const unsigned char *sM = smem + L::OFF_M + ty * L::ROW_M + tx * V * (int) sizeof (T);
+
+  for (int k = k0; k < k1; ++k, o += pl)
+  {
+    const int n = k - k0;
+    const int slot = n % S;
+    const int so = slot * L::STAGE;
+    mbar_wait (&full[slot], (n / S) & 1);
+
+    const int gk = p.kz0 + k;
+    const bool klo = gk >= 1, khi = gk < p.nzg - 1;
+
+    const FVec hz = lds<T, W> (sA_own + so), hz_jm = lds<T, W> (sA_jm + so);
+    const FVec hy = lds<T, W> (sB_own + so);
+    const FVec hx = lds<T, W> (sC_own + so), hx_jm = lds<T, W> (sC_jm + so);
+    T hz_im[NC], hy_im[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c)
+    {
+      hz_im[c] = *reinterpret_cast<const T *> (sA_own + so - L::CELL + c * sizeof (T));
+      hy_im[c] = *reinterpret_cast<const T *> (sB_own + so - L::CELL + c * sizeof (T));
+    }
+    FVec ex = lds<T, W> (sOwn + so + 0 * L::OWN_STRIDE);
+    FVec ey = lds<T, W> (sOwn + so + 1 * L::OWN_STRIDE);
+    FVec ez = lds<T, W> (sOwn + so + 2 * L::OWN_STRIDE);
+    FVec dx, dy, dz;
+    if (PML)
+    {
+      dx = lds<T, W> (sOwn + so + 3 * L::OWN_STRIDE);
+      dy = lds<T, W> (sOwn + so + 4 * L::OWN_STRIDE);
+      dz = lds<T, W> (sOwn + so + 5 * L::OWN_STRIDE);
+    }
+    const MVec eps_kp = lds<T, V> (sM + so);
+    const MVec eps_jp_next = lds<T, V> (sM + so + L::ROW_M);
+    const T eps_ip_next = *reinterpret_cast<const T *> (sM + so + V * sizeof (T));
+
+    if (active)
+    {
+      T ca_z_at = 0, cbd_z_at = 0, q_z_at = 0, p_z_btw = 0, m_z_btw = 0;
+      if (PML)
+      {
+        ca_z_at = p.tab[2][KIND_AT].ca[gk];
+        cbd_z_at = p.tab[2][KIND_AT].cbd[gk];
+        q_z_at = EXACT ? p.tab[2][KIND_AT].p[gk] : p.tab[2][KIND_AT].invp[gk];
+        p_z_btw = p.tab[2][KIND_BTW].p[gk];
+        m_z_btw = p.tab[2][KIND_BTW].m[gk];
+      }
+
+#pragma unroll
+      for (int v = 0; v < V; ++v)
+      {
+        const int i = i0 + v;
+        const bool ilo = i >= 1, ihi = i < p.nx - 1;
+        const bool do_ex = ihi && jlo && klo;
+        const bool do_ey = ilo && jhi && klo;
+        const bool do_ez = ilo && jlo && khi;
+
+        T cex[NC], cey[NC], cez[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+        {
+          const int s = v * NC + c;
+          const T hz_m = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
+          const T hy_m = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
+          cex[c] = hz.v[s] - hz_jm.v[s] - hy.v[s] + hy_km.v[s];
+          cey[c] = hx.v[s] - hx_km.v[s] - hz.v[s] + hz_m;
+          cez[c] = hy.v[s] - hy_m - hx.v[s] + hx_jm.v[s];
+        }
+
+        if (TFSF)
+        {
+          const int fx = tfsf_e_faces (p, 0, i, j, gk), fy = tfsf_e_faces (p, 1, i, j, gk), fz = tfsf_e_faces (p, 2, i, j, gk);
+          if (fx | fy | fz)
+          {
+#pragma unroll
+            for (int c = 0; c < NC; ++c)
+            {
+              const int s = v * NC + c;
+              const T hz_m = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
+              const T hy_m = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
+              if (fx) cex[c] = tfsf_curl<T, NC, true> (p, 0, fx, c, i, j, gk, hz.v[s], hz_jm.v[s], hy.v[s], hy_km.v[s]);
+              if (fy) cey[c] = tfsf_curl<T, NC, true> (p, 1, fy, c, i, j, gk, hx.v[s], hx_km.v[s], hz.v[s], hz_m);
+              if (fz) cez[c] = tfsf_curl<T, NC, true> (p, 2, fz, c, i, j, gk, hy.v[s], hy_m, hx.v[s], hx_jm.v[s]);
+            }
+          }
+        }
+
+        const T e_c = eps_c.v[v];
+        const T e_xp = v + 1 < V ? eps_c.v[v + 1 < V ? v + 1 : v] : eps_ip;
+        const T mod_x = ((e_c + e_xp) / (T) 2) * p.eps0;
+        const T mod_y = ((e_c + eps_jp.v[v]) / (T) 2) * p.eps0;
+        const T mod_z = ((e_c + eps_kp.v[v]) / (T) 2) * p.eps0;
+
+        if (PML)
+        {
+          T cbx, ccx, cby, ccy, cbz, ccz;
+          sweep3_coefs<T, EXACT> (p_x_btw.v[v], m_x_btw.v[v], q_z_at, mod_x, cbx, ccx);
+          sweep3_coefs<T, EXACT> (p_y_btw, m_y_btw, q_x_at.v[v], mod_y, cby, ccy);
+          sweep3_coefs<T, EXACT> (p_z_btw, m_z_btw, q_y_at, mod_z, cbz, ccz);
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_ex) upml_cell<T, EXACT> (dx.v[s], ex.v[s], cex[c], ca_y_at, cbd_y_at, ca_z_at, cbx, ccx);
+            if (do_ey) upml_cell<T, EXACT> (dy.v[s], ey.v[s], cey[c], ca_z_at, cbd_z_at, ca_x_at.v[v], cby, ccy);
+            if (do_ez) upml_cell<T, EXACT> (dz.v[s], ez.v[s], cez[c], ca_x_at.v[v], cbd_x_at.v[v], ca_y_at, cbz, ccz);
+          }
+        }
+        else
+        {
+          const T cbx = plain_coef<T, EXACT> (mod_x, p);
+          const T cby = plain_coef<T, EXACT> (mod_y, p);
+          const T cbz = plain_coef<T, EXACT> (mod_z, p);
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_ex) ex.v[s] = plain_cell<T, NC, EXACT> (ex.v[s], cex[c], cbx);
+            if (do_ey) ey.v[s] = plain_cell<T, NC, EXACT> (ey.v[s], cey[c], cby);
+            if (do_ez) ez.v[s] = plain_cell<T, NC, EXACT> (ez.v[s], cez[c], cbz);
+          }
+        }
+
+        if (!TFSF)
+        {
+          if (gk == p.srcpos[2] && j == p.srcpos[1] && i == p.srcpos[0])
+          {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) ez.v[v * NC + c] = p.src[step * NC + c];
+          }
+        }
+      }
+
+      stv<T, W> (Ex + o, ex); stv<T, W> (Ey + o, ey); stv<T, W> (Ez + o, ez);
+      if (PML)
+      {
+        stv<T, W> (Dx + o, dx); stv<T, W> (Dy + o, dy); stv<T, W> (Dz + o, dz);
+      }
+    }
+
+    hx_km = hx; hy_km = hy;
+    eps_c = eps_kp; eps_jp = eps_jp_next; eps_ip = eps_ip_next;
+
+    /* every thread has read the stage: hand the slot back to the TMA unit for plane k + S */
+    __syncthreads ();
+    if (leader && k + S < k1) issue (slot, k + S);
+  }
+}
+
+/* ------------------------------------------------------------------ H half step */
+
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
+__global__ void __launch_bounds__ (NTHREADS, 1)
+h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
+{
+  typedef Tile<T, NC, PML> L;
+  constexpr int V = L::V, W = V * NC, S = L::STAGES;
+  typedef Vec<T, W> FVec;
+  typedef Vec<T, V> MVec;
+
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ __align__ (8) unsigned long long full[S];
+  unsigned char *smem = reinterpret_cast<unsigned char *> ((reinterpret_cast<uintptr_t> (smem_raw) + 127) & ~(uintptr_t) 127);
+
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const bool leader = tx == 0 && ty == 0;
+  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * TY;
+  const int i0 = i0t + tx * V, j = j0t + ty;
+  const bool active = i0 < p.nx && j < p.ny;
+  const int k0 = kb + blockIdx.z * p.kchunk;
+  const int k1 = min (k0 + p.kchunk, ke);
+  if (k0 >= k1) return;
+
+  /* maps: 0 Ez (A: x+y halo, plane k), 1 Ey (B: x halo, plane k+1), 2 Ex (C: y halo, plane k+1),
+   *       3..8 Hx Hy Hz [Bx By Bz], 9 mu (M, material plane k+1) */
+  auto issue = [&] (int slot, int k)
+  {
+    unsigned char *base = smem + slot * L::STAGE;
+    unsigned long long *bar = &full[slot];
+    mbar_expect_tx (bar, L::TX_BYTES);
+    tma_load_3d (base + L::OFF_A, &maps.m[0], bar, i0t * NC, j0t, k + 1);
+    tma_load_3d (base + L::OFF_B, &maps.m[1], bar, i0t * NC, j0t, k + 2);
+    tma_load_3d (base + L::OFF_C, &maps.m[2], bar, i0t * NC, j0t, k + 2);
+#pragma unroll
+    for (int a = 0; a < L::N_OWN; ++a)
+      tma_load_3d (base + L::OFF_OWN + a * L::OWN_STRIDE, &maps.m[3 + a], bar, i0t * NC, j0t, k + 1);
+    tma_load_3d (base + L::OFF_M, &maps.m[9], bar, i0t, j0t, k + 2);
+  };
+
+  if (leader)
+  {
+    for (int s = 0; s < S; ++s) mbar_init (&full[s], 1);
+    asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads ();
+  if (leader)
+  {
+    for (int s = 0; s < S && k0 + s < k1; ++s) issue (s, k0 + s);
+  }
+
+  long long o = (((long long) (k0 + 1) * p.ny + j) * p.pitch + i0) * NC;
+  const long long row = (long long) p.pitch * NC;
+  const long long pl = p.ps * NC;
+  const long long om = ((long long) (k0 + 1) * (p.ny + 1) + j) * p.pitchM + i0;
+
+  T *Hx = p.f[3], *Hy = p.f[4], *Hz = p.f[5];
+  T *Bx = p.f[9], *By = p.f[10], *Bz = p.f[11];
+
+  const bool jlo = j >= 1, jhi = j < p.ny - 1;
+
+  T ca_y_btw = 0, cbd_y_btw = 0, p_y_at = 0, m_y_at = 0, q_y_btw = 0;
+  MVec p_x_at = {}, m_x_at = {}, ca_x_btw = {}, cbd_x_btw = {}, q_x_btw = {};
+  FVec ex = {}, ex_jp = {}, ey = {};
+  T ey_ip[NC] = {};
+  MVec mu_c = {}, mu_jp = {};
+  T mu_ip = 0, mu_ip_jp = 0;
+  if (active)
+  {
+    if (PML)
+    {
+      ca_y_btw = p.tab[1][KIND_BTW].ca[j];
+      cbd_y_btw = p.tab[1][KIND_BTW].cbd[j];
+      p_y_at = p.tab[1][KIND_AT].p[j];
+      m_y_at = p.tab[1][KIND_AT].m[j];
+      q_y_btw = EXACT ? p.tab[1][KIND_BTW].p[j] : p.tab[1][KIND_BTW].invp[j];
+      p_x_at = ldv<T, V> (p.tab[0][KIND_AT].p + i0);
+      m_x_at = ldv<T, V> (p.tab[0][KIND_AT].m + i0);
+      ca_x_btw = ldv<T, V> (p.tab[0][KIND_BTW].ca + i0);
+      cbd_x_btw = ldv<T, V> (p.tab[0][KIND_BTW].cbd + i0);
+      q_x_btw = ldv<T, V> ((EXACT ? p.tab[0][KIND_BTW].p : p.tab[0][KIND_BTW].invp) + i0);
+    }
+    /* z-carried values of plane k0, straight from global memory */
+    ex = ldv<T, W> (p.f[0] + o);
+    ex_jp = ldv<T, W> (p.f[0] + o + row);
+    ey = ldv<T, W> (p.f[1] + o);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) ey_ip[c] = __ldg (p.f[1] + o + W + c);
+    mu_c = ldv<T, V> (p.mu + om);
+    mu_jp = ldv<T, V> (p.mu + om + p.pitchM);
+    mu_ip = __ldg (p.mu + om + V);
+    mu_ip_jp = __ldg (p.mu + om + p.pitchM + V);
+  }
+
+  const int xo = tx * 16;
+  const unsigned char *sA_own = smem + L::OFF_A + ty * L::ROW_H + xo;       /* Ez[j]      */
+  const unsigned char *sA_jp = smem + L::OFF_A + (ty + 1) * L::ROW_H + xo;  /* Ez[j+1]    */
+  const unsigned char *sB_own = smem + L::OFF_B + ty * L::ROW_H + xo;       /* Ey[k+1]    */
+  const unsigned char *sC_own = smem + L::OFF_C + ty * L::ROW + xo;         /* Ex[k+1]    */
+  const unsigned char *sC_jp = smem + L::OFF_C + (ty + 1) * L::ROW + xo;    /* Ex[k+1][j+1] */
+  const unsigned char *sOwn = smem + L::OFF_OWN + ty * L::ROW + xo;
+  const unsigned char *sM = smem + L::OFF_M + ty * L::ROW_M + tx * V * (int) sizeof (T);
+
+  for (int k = k0; k < k1; ++k, o += pl)
+  {
+    const int n = k - k0;
+    const int slot = n % S;
+    const int so = slot * L::STAGE;
+    mbar_wait (&full[slot], (n / S) & 1);
+
+    const int gk = p.kz0 + k;
+    const bool klo = gk >= 1, khi = gk < p.nzg - 1;
+
+    const FVec ez = lds<T, W> (sA_own + so), ez_jp = lds<T, W> (sA_jp + so);
+    const FVec ey_kp = lds<T, W> (sB_own + so);
+    const FVec ex_kp = lds<T, W> (sC_own + so), ex_kp_jp = lds<T, W> (sC_jp + so);
+    T ez_ip[NC], ey_kp_ip[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c)
+    {
+      ez_ip[c] = *reinterpret_cast<const T *> (sA_own + so + 16 + c * sizeof (T));
+      ey_kp_ip[c] = *reinterpret_cast<const T *> (sB_own + so + 16 + c * sizeof (T));
+    }
+    FVec hx = lds<T, W> (sOwn + so + 0 * L::OWN_STRIDE);
+    FVec hy = lds<T, W> (sOwn + so + 1 * L::OWN_STRIDE);
+    FVec hz = lds<T, W> (sOwn + so + 2 * L::OWN_STRIDE);
+    FVec bx, by, bz;
+    if (PML)
+    {
+      bx = lds<T, W> (sOwn + so + 3 * L::OWN_STRIDE);
+      by = lds<T, W> (sOwn + so + 4 * L::OWN_STRIDE);
+      bz = lds<T, W> (sOwn + so + 5 * L::OWN_STRIDE);
+    }
+    const MVec mu_kp = lds<T, V> (sM + so), mu_jp_kp = lds<T, V> (sM + so + L::ROW_M);
+    const T mu_ip_kp = *reinterpret_cast<const T *> (sM + so + V * sizeof (T));
+    const T mu_ip_jp_kp = *reinterpret_cast<const T *> (sM + so + L::ROW_M + V * sizeof (T));
+
+    if (active)
+    {
+      T ca_z_btw = 0, cbd_z_btw = 0, q_z_btw = 0, p_z_at = 0, m_z_at = 0;
+      if (PML)
+      {
+        ca_z_btw = p.tab[2][KIND_BTW].ca[gk];
+        cbd_z_btw = p.tab[2][KIND_BTW].cbd[gk];
+        q_z_btw = EXACT ? p.tab[2][KIND_BTW].p[gk] : p.tab[2][KIND_BTW].invp[gk];
+        p_z_at = p.tab[2][KIND_AT].p[gk];
+        m_z_at = p.tab[2][KIND_AT].m[gk];
+      }
+
+#pragma unroll
+      for (int v = 0; v < V; ++v)
+      {
+        const int i = i0 + v;
+        const bool ilo = i >= 1, ihi = i < p.nx - 1;
+        const bool do_hx = ilo && jhi && khi;
+        const bool do_hy = ihi && jlo && khi;
+        const bool do_hz = ihi && jhi && klo;
+
+        T chx[NC], chy[NC], chz[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+        {
+          const int s = v * NC + c;
+          const T ez_p = v + 1 < V ? ez.v[v + 1 < V ? s + NC : s] : ez_ip[c];
+          const T ey_p = v + 1 < V ? ey.v[v + 1 < V ? s + NC : s] : ey_ip[c];
+          chx[c] = ey_kp.v[s] - ey.v[s] - ez_jp.v[s] + ez.v[s];
+          chy[c] = ez_p - ez.v[s] - ex_kp.v[s] + ex.v[s];
+          chz[c] = ex_jp.v[s] - ex.v[s] - ey_p + ey.v[s];
+        }
+
+        if (TFSF)
+        {
+          const int fx = tfsf_h_faces (p, 0, i, j, gk), fy = tfsf_h_faces (p, 1, i, j, gk), fz = tfsf_h_faces (p, 2, i, j, gk);
+          if (fx | fy | fz)
+          {
+#pragma unroll
+            for (int c = 0; c < NC; ++c)
+            {
+              const int s = v * NC + c;
+              const T ez_p = v + 1 < V ? ez.v[v + 1 < V ? s + NC : s] : ez_ip[c];
+              const T ey_p = v + 1 < V ? ey.v[v + 1 < V ? s + NC : s] : ey_ip[c];
+              if (fx) chx[c] = tfsf_curl<T, NC, false> (p, 0, fx, c, i, j, gk, ey_kp.v[s], ey.v[s], ez_jp.v[s], ez.v[s]);
+              if (fy) chy[c] = tfsf_curl<T, NC, false> (p, 1, fy, c, i, j, gk, ez_p, ez.v[s], ex_kp.v[s], ex.v[s]);
+              if (fz) chz[c] = tfsf_curl<T, NC, false> (p, 2, fz, c, i, j, gk, ex_jp.v[s], ex.v[s], ey_p, ey.v[s]);
+            }
+          }
+        }
+
+        const T m000 = mu_c.v[v], m001 = mu_kp.v[v], m010 = mu_jp.v[v], m011 = mu_jp_kp.v[v];
+        const T m100 = v + 1 < V ? mu_c.v[v + 1 < V ? v + 1 : v] : mu_ip;
+        const T m101 = v + 1 < V ? mu_kp.v[v + 1 < V ? v + 1 : v] : mu_ip_kp;
+        const T m110 = v + 1 < V ? mu_jp.v[v + 1 < V ? v + 1 : v] : mu_ip_jp;
+        const T two = (T) 2;
+        const T mod_x = (((m000 + m001) / two + (m010 + m011) / two) / two) * p.mu0;
+        const T mod_y = (((m000 + m001) / two + (m100 + m101) / two) / two) * p.mu0;
+        const T mod_z = (((m000 + m010) / two + (m100 + m110) / two) / two) * p.mu0;
+
+        if (PML)
+        {
+          T cbx, ccx, cby, ccy, cbz, ccz;
+          sweep3_coefs<T, EXACT> (p_x_at.v[v], m_x_at.v[v], q_z_btw, mod_x, cbx, ccx);
+          sweep3_coefs<T, EXACT> (p_y_at, m_y_at, q_x_btw.v[v], mod_y, cby, ccy);
+          sweep3_coefs<T, EXACT> (p_z_at, m_z_at, q_y_btw, mod_z, cbz, ccz);
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_hx) upml_cell<T, EXACT> (bx.v[s], hx.v[s], chx[c], ca_y_btw, cbd_y_btw, ca_z_btw, cbx, ccx);
+            if (do_hy) upml_cell<T, EXACT> (by.v[s], hy.v[s], chy[c], ca_z_btw, cbd_z_btw, ca_x_btw.v[v], cby, ccy);
+            if (do_hz) upml_cell<T, EXACT> (bz.v[s], hz.v[s], chz[c], ca_x_btw.v[v], cbd_x_btw.v[v], ca_y_btw, cbz, ccz);
+          }
+        }
+        else
+        {
+          const T cbx = plain_coef<T, EXACT> (mod_x, p);
+          const T cby = plain_coef<T, EXACT> (mod_y, p);
+          const T cbz = plain_coef<T, EXACT> (mod_z, p);
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_hx) hx.v[s] = plain_cell<T, NC, EXACT> (hx.v[s], chx[c], cbx);
+            if (do_hy) hy.v[s] = plain_cell<T, NC, EXACT> (hy.v[s], chy[c], cby);
+            if (do_hz) hz.v[s] = plain_cell<T, NC, EXACT> (hz.v[s], chz[c], cbz);
+          }
+        }
+      }
+
+      stv<T, W> (Hx + o, hx); stv<T, W> (Hy + o, hy); stv<T, W> (Hz + o, hz);
+      if (PML)
+      {
+        stv<T, W> (Bx + o, bx); stv<T, W> (By + o, by); stv<T, W> (Bz + o, bz);
+      }
+    }
+
+    ex = ex_kp; ex_jp = ex_kp_jp; ey = ey_kp;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) ey_ip[c] = ey_kp_ip[c];
+    mu_c = mu_kp; mu_jp = mu_jp_kp; mu_ip = mu_ip_kp; mu_ip_jp = mu_ip_jp_kp;
+
+    __syncthreads ();
+    if (leader && k + S < k1) issue (slot, k + S);
+  }
+}
+
+/* ------------------------------------------------------------------ dispatch */
+
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
+cudaError_t launch_t (bool e_phase, const StepParams<T> &p, const TmaSet &maps, int kb, int ke, cudaStream_t stream)
+{
+  typedef Tile<T, NC, PML> L;
+  if (ke <= kb) return cudaSuccess;
+  dim3 block (32, TY);
+  dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + TY - 1) / TY, (ke - kb + p.kchunk - 1) / p.kchunk);
+  static bool attr_e = false, attr_h = false;
+  if (e_phase)
+  {
+    if (!attr_e)
+    {
+      cudaError_t e = cudaFuncSetAttribute (e_phase_3d_tma<T, NC, PML, TFSF, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM);
+      if (e != cudaSuccess) return e;
+      attr_e = true;
+    }
+    e_phase_3d_tma<T, NC, PML, TFSF, EXACT><<<grid, block, L::SMEM, stream>>> (p, maps, kb, ke);
+  }
+  else
+  {
+    if (!attr_h)
+    {
+      cudaError_t e = cudaFuncSetAttribute (h_phase_3d_tma<T, NC, PML, TFSF, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM);
+      if (e != cudaSuccess) return e;
+      attr_h = true;
+    }
+    h_phase_3d_tma<T, NC, PML, TFSF, EXACT><<<grid, block, L::SMEM, stream>>> (p, maps, kb, ke);
+  }
+  return cudaGetLastError ();
+}
+
+template <typename T, int NC>
+cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, const TmaSet &maps, bool pml, bool tfsf, bool exact, int kb,
+                       int ke, cudaStream_t s)
+{
+  const int key = (pml ? 4 : 0) | (tfsf ? 2 : 0) | (exact ? 1 : 0);
+  switch (key)
+  {
+    case 0: return launch_t<T, NC, false, false, false> (e_phase, p, maps, kb, ke, s);
+    case 1: return launch_t<T, NC, false, false, true> (e_phase, p, maps, kb, ke, s);
+    case 2: return launch_t<T, NC, false, true, false> (e_phase, p, maps, kb, ke, s);
+    case 3: return launch_t<T, NC, false, true, true> (e_phase, p, maps, kb, ke, s);
+    case 4: return launch_t<T, NC, true, false, false> (e_phase, p, maps, kb, ke, s);
+    case 5: return launch_t<T, NC, true, false, true> (e_phase, p, maps, kb, ke, s);
+    case 6: return launch_t<T, NC, true, true, false> (e_phase, p, maps, kb, ke, s);
+    default: return launch_t<T, NC, true, true, true> (e_phase, p, maps, kb, ke, s);
+  }
+}
+
+/* ------------------------------------------------------------------ tensor maps (host) */
+
+typedef CUresult (*EncodeTiledFn) (CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn (std::string *err)
+{
+  static EncodeTiledFn fn = NULL;
+  static bool tried = false;
+  if (!tried)
+  {
+    tried = true;
+    void *ptr = NULL;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint ("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q);
+    if (e == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (EncodeTiledFn) ptr;
+  }
+  if (!fn && err) *err = "cuTensorMapEncodeTiled is not available from the CUDA driver";
+  return fn;
+}
+
+/* 3-D tensor of `scalar_bytes` scalars: x extent xs scalars (row pitch), ny rows, nplanes planes; box bx x by x 1 */
+bool encode (CUtensorMap *out, void *base, int scalar_bytes, long long xs, long long ny, long long nplanes, int bx, int by,
+             std::string *err)
+{
+  EncodeTiledFn fn = encode_fn (err);
+  if (!fn) return false;
+  cuuint64_t gdim[3] = { (cuuint64_t) xs, (cuuint64_t) ny, (cuuint64_t) nplanes };
+  cuuint64_t gstride[2] = { (cuuint64_t) xs * scalar_bytes, (cuuint64_t) xs * ny * scalar_bytes };
+  cuuint32_t box[3] = { (cuuint32_t) bx, (cuuint32_t) by, 1 };
+  cuuint32_t estr[3] = { 1, 1, 1 };
+  CUresult r = fn (out, scalar_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, gdim,
+                   gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+  {
+    if (err) *err = "cuTensorMapEncodeTiled failed with CUresult " + std::to_string ((int) r);
+    return false;
+  }
+  return true;
+}
+
+template <typename T, int NC>
+bool prepare_t (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu, int pitch, int ny, int planes, int pitchM,
+                int planesM, std::string *err)
+{
+  typedef Tile<T, NC, true> L; /* box shapes do not depend on PML */
+  static_assert (sizeof (TmaSet) <= sizeof (out->e), "TmaMaps3D too small");
+  TmaSet *e = reinterpret_cast<TmaSet *> (out->e), *h = reinterpret_cast<TmaSet *> (out->h);
+  const int sb = (int) sizeof (T);
+  const long long xs = (long long) pitch * NC;
+  const int bxh = (L::TXC + L::V) * NC, bx = L::TXC * NC, bxm = L::TXC + L::HM;
+  bool ok = true;
+  /* E phase: Hz (A), Hy (B), Hx (C), Ex Ey Ez Dx Dy Dz, eps */
+  ok = ok && encode (&e->m[0], f[5], sb, xs, ny, planes, bxh, TY + 1, err);
+  ok = ok && encode (&e->m[1], f[4], sb, xs, ny, planes, bxh, TY, err);
+  ok = ok && encode (&e->m[2], f[3], sb, xs, ny, planes, bx, TY + 1, err);
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&e->m[3 + a], f[0 + a], sb, xs, ny, planes, bx, TY, err);
+  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&e->m[6 + a], f[6 + a], sb, xs, ny, planes, bx, TY, err);
+  ok = ok && encode (&e->m[9], eps, sb, pitchM, ny + 1, planesM, bxm, TY + 1, err);
+  /* H phase: Ez (A), Ey (B), Ex (C), Hx Hy Hz Bx By Bz, mu */
+  ok = ok && encode (&h->m[0], f[2], sb, xs, ny, planes, bxh, TY + 1, err);
+  ok = ok && encode (&h->m[1], f[1], sb, xs, ny, planes, bxh, TY, err);
+  ok = ok && encode (&h->m[2], f[0], sb, xs, ny, planes, bx, TY + 1, err);
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&h->m[3 + a], f[3 + a], sb, xs, ny, planes, bx, TY, err);
+  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&h->m[6 + a], f[9 + a], sb, xs, ny, planes, bx, TY, err);
+  ok = ok && encode (&h->m[9], mu, sb, pitchM, ny + 1, planesM, bxm, TY + 1, err);
+  out->valid = ok;
+  return ok;
+}
+
+} /* namespace */
+
+bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, void *const f[12], void *eps, void *mu, int pitch,
+                     int ny, int planes, int pitchM, int planesM, std::string *err)
+{
+  out->valid = false;
+  if (value_type == 4)
+    return nc == 2 ? prepare_t<float, 2> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err)
+                   : prepare_t<float, 1> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
+  return nc == 2 ? prepare_t<double, 2> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err)
+                 : prepare_t<double, 1> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
+}
+
+template <typename T>
+cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
+                                 bool exact, int kb, int ke, cudaStream_t stream)
+{
+  const TmaSet &set = *reinterpret_cast<const TmaSet *> (e_phase ? maps.e : maps.h);
+  if (cplx) return launch_nc<T, 2> (e_phase, p, set, pml, tfsf, exact, kb, ke, stream);
+  return launch_nc<T, 1> (e_phase, p, set, pml, tfsf, exact, kb, ke, stream);
+}
+
+template cudaError_t launch_phase_3d_tma<float> (bool, const StepParams<float> &, const TmaMaps3D &, bool, bool, bool, bool, int, int, cudaStream_t);
+template cudaError_t launch_phase_3d_tma<double> (bool, const StepParams<double> &, const TmaMaps3D &, bool, bool, bool, bool, int, int, cudaStream_t);
+
+} /* namespace fdtd */

@@ -6,6 +6,7 @@
 #define FDTD_LAUNCH_H
 
 #include <cuda_runtime.h>
+#include <string>
 #include "fdtd_device.cuh"
 
 namespace fdtd
@@ -15,6 +16,20 @@ namespace fdtd
 template <typename T>
 cudaError_t launch_phase_3d (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact,
                              int kb, int ke, cudaStream_t stream);
+
+/* TMA-staged 3D half steps (kernels3d_tma.cu).  TmaMaps3D holds the CUtensorMap descriptors (10 per phase,
+ * 128 bytes each) of one solver's arrays; tma_prepare_3d encodes them once the arrays are allocated. */
+struct TmaMaps3D
+{
+  alignas (64) unsigned char e[10 * 128];
+  alignas (64) unsigned char h[10 * 128];
+  bool valid;
+};
+bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, void *const f[12], void *eps, void *mu, int pitch,
+                     int ny, int planes, int pitchM, int planesM, std::string *err);
+template <typename T>
+cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
+                                 bool exact, int kb, int ke, cudaStream_t stream);
 
 /* 2D TMz half steps (kernels2d.cu) */
 template <typename T>

@@ -92,6 +92,10 @@ struct fdtd_solver
   cudaEvent_t ev_start, ev_stop, ev_eb, ev_ex, ev_hb, ev_hx;
   NcclComm comm;
 
+  TmaMaps3D tma;        /* tensor maps of the TMA-staged 3D kernels */
+  bool use_tma;
+  int kchunk;
+
   bool profiling;
   std::vector<cudaEvent_t> prof_ev; /* 4 per step: E begin/end, H begin/end */
   long long prof_steps;
@@ -134,7 +138,7 @@ static StepParams<T> make_params (const fdtd_solver *s)
   p.ninc = s->ninc;
   p.nx = s->nx; p.ny = s->ny; p.nzl = s->nzl; p.kz0 = s->kz0; p.nzg = s->nzg;
   p.pitch = s->pitch; p.pitchM = s->pitchM; p.ps = s->ps; p.psM = s->psM;
-  p.kchunk = c.dims == 3 ? 32 : 16;
+  p.kchunk = s->kchunk;
   for (int a = 0; a < 3; ++a)
   {
     p.L[a] = (int) c.tfsf_size[a];
@@ -285,6 +289,15 @@ static int exchange (fdtd_solver *s, bool h_fields)
 /* ------------------------------------------------------------------ time loop */
 
 template <typename T>
+static cudaError_t phase_3d (fdtd_solver *s, bool e_phase, const StepParams<T> &p, int kb, int ke, cudaStream_t S)
+{
+  const fdtd_config &c = s->cfg;
+  const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode != 0;
+  if (s->use_tma) return launch_phase_3d_tma<T> (e_phase, p, s->tma, cplx, pml, tfsf, exact, kb, ke, S);
+  return launch_phase_3d<T> (e_phase, p, cplx, pml, tfsf, exact, kb, ke, S);
+}
+
+template <typename T>
 static int enqueue_steps (fdtd_solver *s, long long nsteps)
 {
   const fdtd_config &c = s->cfg;
@@ -326,18 +339,18 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     }
     else if (!multi)
     {
-      CUDA_TRY (launch_phase_3d<T> (true, p, cplx, pml, tfsf, exact, 0, s->nzl, S)); s->launches++;
+      CUDA_TRY (phase_3d<T> (s, true, p, 0, s->nzl, S)); s->launches++;
     }
     else
     {
       CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
-      CUDA_TRY (launch_phase_3d<T> (true, p, cplx, pml, tfsf, exact, 0, 1, S)); s->launches++;
+      CUDA_TRY (phase_3d<T> (s, true, p, 0, 1, S)); s->launches++;
       CUDA_TRY (cudaEventRecord (s->ev_eb, S));
       CUDA_TRY (cudaStreamWaitEvent (C, s->ev_eb, 0));
       int rc = exchange (s, false);
       if (rc) return rc;
       CUDA_TRY (cudaEventRecord (s->ev_ex, C));
-      if (s->nzl > 1) { CUDA_TRY (launch_phase_3d<T> (true, p, cplx, pml, tfsf, exact, 1, s->nzl, S)); s->launches++; }
+      if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, true, p, 1, s->nzl, S)); s->launches++; }
     }
 
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
@@ -349,18 +362,18 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     }
     else if (!multi)
     {
-      CUDA_TRY (launch_phase_3d<T> (false, p, cplx, pml, tfsf, exact, 0, s->nzl, S)); s->launches++;
+      CUDA_TRY (phase_3d<T> (s, false, p, 0, s->nzl, S)); s->launches++;
     }
     else
     {
       CUDA_TRY (cudaStreamWaitEvent (S, s->ev_ex, 0));
-      CUDA_TRY (launch_phase_3d<T> (false, p, cplx, pml, tfsf, exact, s->nzl - 1, s->nzl, S)); s->launches++;
+      CUDA_TRY (phase_3d<T> (s, false, p, s->nzl - 1, s->nzl, S)); s->launches++;
       CUDA_TRY (cudaEventRecord (s->ev_hb, S));
       CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
       int rc = exchange (s, true);
       if (rc) return rc;
       CUDA_TRY (cudaEventRecord (s->ev_hx, C));
-      if (s->nzl > 1) { CUDA_TRY (launch_phase_3d<T> (false, p, cplx, pml, tfsf, exact, 0, s->nzl - 1, S)); s->launches++; }
+      if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, false, p, 0, s->nzl - 1, S)); s->launches++; }
     }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
     CUDA_TRY (launch_tick (s->step, S)); s->launches++;
@@ -654,6 +667,33 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   CREATE_TRY (cudaMalloc ((void **) &s->red_partials, sizeof (double) * (size_t) sumsq_partial_count ()));
   CREATE_TRY (cudaMalloc ((void **) &s->red_out, sizeof (double)));
 #undef CREATE_TRY
+
+  /* kernel selection and z-chunk per CTA: enough CTAs to fill 148 SMs twice, at most 64 planes each */
+  s->use_tma = false;
+  s->kchunk = 16;
+  if (is3)
+  {
+    const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
+    s->use_tma = !(sel && strcmp (sel, "direct") == 0);
+    const int txc = s->use_tma ? 32 * (16 / s->cell) : 32 * (16 / s->cell);
+    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + 7) / 8);
+    long long zsplit = (2 * 148 + tiles - 1) / tiles;
+    int kc = (int) (s->nzl / (zsplit > 0 ? zsplit : 1));
+    if (kc > 64) kc = 64;
+    if (kc < 4) kc = 4;
+    s->kchunk = kc;
+    if (s->use_tma)
+    {
+      std::string err;
+      if (!tma_prepare_3d (&s->tma, s->fp, s->nc, cfg->use_pml != 0, s->f, s->eps, s->mu, s->pitch, s->ny, s->nzl + 2, s->pitchM,
+                           s->nzm + 2, &err))
+      {
+        fail (FDTD_ERROR, "TMA descriptor set-up failed: %s", err.c_str ());
+        fdtd_destroy (s);
+        return FDTD_ERROR;
+      }
+    }
+  }
 
   *out = s;
   if ((rc = fdtd_fill (s, FDTD_EPS, 1.0, 0.0)) || (rc = fdtd_fill (s, FDTD_MU, 1.0, 0.0)) || (rc = build_tables_any (s)))
