@@ -181,6 +181,32 @@ int fdtd_get_time_step (fdtd_handle h, int64_t *t);
  * SURVEY.md §8c are quoted in this form). */
 int fdtd_field_sumsq (fdtd_handle h, int field, double *out);
 
+/*
+ * The same sum of squares for callers that cannot allocate device memory or have no solver handle.
+ * (No counterpart in the reference: it has no device-side reductions at all.)
+ *
+ * Computes sum(x[i]^2, i < count) over `count` float (value_type 4) or double (value_type 8) scalars at the
+ * device address dev_in and writes the double result to the device address dev_out; a complex field is its
+ * 2*N scalars.  Both pointers must belong to the device that is current in the calling thread.  The work is
+ * queued on `cuda_stream` (a cudaStream_t, NULL for the default stream) and the function returns without
+ * waiting: read *dev_out after that stream has been synchronised.
+ *
+ * It never calls cudaMalloc, cudaFree or any allocating routine.  Its scratch (one partial sum per thread
+ * block) is a fixed 256 KiB array inside the library image, which every GPU that loads the library keeps
+ * until the process ends.  Consequences a caller must know:
+ *   - count may not exceed FDTD_SUMSQ_NOALLOC_MAX_COUNT; a larger count is refused with
+ *     FDTD_INVALID_ARGUMENT and an explanation in errbuf (nothing is launched) -- split the array;
+ *   - all calls on one GPU share that array, so two calls whose kernels may overlap on the GPU (different
+ *     streams, or different host threads) race and return garbage: order them on one stream or with events.
+ *     Nothing in the array needs clearing between calls: each call rewrites every slot it later reads;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress) and loads
+ *     the kernels; make that first call outside, and before, any stream capture.
+ * errbuf (may be NULL) receives the message of a failure; the return value is an fdtd_status.
+ */
+#define FDTD_SUMSQ_NOALLOC_MAX_COUNT 268435456LL
+int fdtd_sumsq_noalloc (const void *dev_in, int value_type, int64_t count, double *dev_out, void *cuda_stream,
+                        char *errbuf, int64_t errbuf_len);
+
 /* Multi-GPU: NCCL communicator for the z-slab halo exchange (one rank per GPU).  Rank 0 calls
  * fdtd_comm_unique_id and distributes the 128 bytes out of band (torch.distributed, a file, ...);
  * then every rank calls fdtd_comm_init with the same id.  Replaces ParallelGridCore's MPI setup
