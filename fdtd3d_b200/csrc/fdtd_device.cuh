@@ -118,9 +118,21 @@ template <typename T> __device__ __forceinline__ T fma_t (T a, T b, T c);
 template <> __device__ __forceinline__ float fma_t<float> (float a, float b, float c) { return __fmaf_rn (a, b, c); }
 template <> __device__ __forceinline__ double fma_t<double> (double a, double b, double c) { return __fma_rn (a, b, c); }
 
+/* Reciprocal for fast mode (exact mode divides).  double: hardware seed (rcp.approx.ftz.f64, ~20 bits) plus two
+ * Newton steps -- branch-free, relative error about 1 ulp, no denormal / special-case handling (the argument is
+ * eps*eps0 or mu*mu0, about 1e-11 .. 1e-5).  float: the correctly rounded intrinsic (one MUFU + fix-up). */
 template <typename T> __device__ __forceinline__ T rcp_t (T a);
 template <> __device__ __forceinline__ float rcp_t<float> (float a) { return __frcp_rn (a); }
-template <> __device__ __forceinline__ double rcp_t<double> (double a) { return __drcp_rn (a); }
+template <> __device__ __forceinline__ double rcp_t<double> (double a)
+{
+  double r;
+  asm ("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
+  double e = __fma_rn (-a, r, 1.0);
+  r = __fma_rn (r, e, r);
+  e = __fma_rn (-a, r, 1.0);
+  r = __fma_rn (r, e, r);
+  return r;
+}
 
 /*
  * Projected incident field at the real coordinate of a component's grid position

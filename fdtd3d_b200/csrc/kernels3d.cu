@@ -66,6 +66,7 @@ e_phase_3d (const __grid_constant__ StepParams<T> p, int kb, int ke)
 
   /* compute-range masks that do not depend on k (YeeGridLayout.h:131-170) */
   const bool jlo = j >= 1, jhi = j < p.ny - 1;
+  const bool j_face = TFSF && tfsf_axis_hit (p, 1, j, true);
 
   /* per-thread UPML coefficients */
   T ca_y_at = 0, cbd_y_at = 0, p_y_btw = 0, m_y_btw = 0, q_y_at = 0;
@@ -96,6 +97,7 @@ e_phase_3d (const __grid_constant__ StepParams<T> p, int kb, int ke)
   {
     const int gk = p.kz0 + k;
     const bool klo = gk >= 1, khi = gk < p.nzg - 1;
+    const bool jk_face = j_face || (TFSF && tfsf_axis_hit (p, 2, gk, true));
 
     FVec hx = ldv<T, W> (Hx + o), hy = ldv<T, W> (Hy + o), hz = ldv<T, W> (Hz + o);
     FVec hz_jm = ldv<T, W> (Hz + o - row), hx_jm = ldv<T, W> (Hx + o - row);
@@ -151,7 +153,7 @@ e_phase_3d (const __grid_constant__ StepParams<T> p, int kb, int ke)
         cez[c] = hy.v[s] - hy_m - hx.v[s] + hx_jm.v[s];
       }
 
-      if (TFSF)
+      if (TFSF && (jk_face || tfsf_axis_hit (p, 0, i, true)))
       {
         /* cells on a TF/SF face (O(N^2) of them) redo their curl with corrected operands */
         const int fx = tfsf_e_faces (p, 0, i, j, gk), fy = tfsf_e_faces (p, 1, i, j, gk), fz = tfsf_e_faces (p, 2, i, j, gk);
@@ -263,6 +265,7 @@ h_phase_3d (const __grid_constant__ StepParams<T> p, int kb, int ke)
   T *Bx = p.f[9], *By = p.f[10], *Bz = p.f[11];
 
   const bool jlo = j >= 1, jhi = j < p.ny - 1;
+  const bool j_face = TFSF && tfsf_axis_hit (p, 1, j, false);
 
   T ca_y_btw = 0, cbd_y_btw = 0, p_y_at = 0, m_y_at = 0, q_y_btw = 0;
   MVec p_x_at, m_x_at, ca_x_btw, cbd_x_btw, q_x_btw;
@@ -289,6 +292,7 @@ h_phase_3d (const __grid_constant__ StepParams<T> p, int kb, int ke)
   {
     const int gk = p.kz0 + k;
     const bool klo = gk >= 1, khi = gk < p.nzg - 1;
+    const bool jk_face = j_face || (TFSF && tfsf_axis_hit (p, 2, gk, false));
 
     FVec ex_kp = ldv<T, W> (Ex + o + pl), ey_kp = ldv<T, W> (Ey + o + pl);
     FVec ez = ldv<T, W> (Ez + o);
@@ -343,7 +347,7 @@ h_phase_3d (const __grid_constant__ StepParams<T> p, int kb, int ke)
         chz[c] = ex_jp.v[s] - ex.v[s] - ey_p + ey.v[s];
       }
 
-      if (TFSF)
+      if (TFSF && (jk_face || tfsf_axis_hit (p, 0, i, false)))
       {
         const int fx = tfsf_h_faces (p, 0, i, j, gk), fy = tfsf_h_faces (p, 1, i, j, gk), fz = tfsf_h_faces (p, 2, i, j, gk);
         if (fx | fy | fz)

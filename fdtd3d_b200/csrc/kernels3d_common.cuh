@@ -129,6 +129,15 @@ __device__ __forceinline__ int tfsf_h_faces (const StepParams<T> &p, int a, int 
   return f;
 }
 
+/* Cheap necessary condition for a cell to lie on any TF/SF face of the E (or H) updates: on every face at
+ * least one coordinate equals L-1 or R (E) / L-1 or R-1 (H) along the face normal.  The j and k parts are
+ * hoisted by the callers (per thread / per plane); only the i part is evaluated per cell. */
+template <typename T>
+__device__ __forceinline__ bool tfsf_axis_hit (const StepParams<T> &p, int axis, int x, bool e_phase)
+{
+  return x == p.L[axis] - 1 || x == (e_phase ? p.R[axis] : p.R[axis] - 1);
+}
+
 /*
  * Curl of a face cell with the TF/SF correction applied to the operand that lies across the interface
  * (Scheme3D::calculate{Ex..Hz}TFSF, Scheme3D.cpp:138-208, 435-505, 732-802, 1029-1099, 1325-1395,

@@ -41,7 +41,18 @@ namespace
 
 using namespace k3d;
 
-constexpr int TY = 8;
+/* tuning knobs: rows per CTA tile, ring depth (0 = as many as fit in 200 KB, at most 4), CTAs per SM the
+ * register allocator must allow */
+#ifndef FDTD_TMA_TY
+#define FDTD_TMA_TY 8
+#endif
+#ifndef FDTD_TMA_STAGES
+#define FDTD_TMA_STAGES 0
+#endif
+#ifndef FDTD_TMA_MINB
+#define FDTD_TMA_MINB 1
+#endif
+constexpr int TY = FDTD_TMA_TY;
 constexpr int NTHREADS = 32 * TY;
 constexpr int N_MAPS = 10;
 
@@ -78,7 +89,7 @@ struct Tile
   static constexpr int OFF_M = OFF_OWN + N_OWN * align128 (SZ_OWN);
   static constexpr int STAGE = OFF_M + align128 (SZ_M);
   static constexpr int TX_BYTES = SZ_A + SZ_B + SZ_C + N_OWN * SZ_OWN + SZ_M;
-  static constexpr int STAGES = (4 * STAGE <= 200 * 1024) ? 4 : 3;
+  static constexpr int STAGES = FDTD_TMA_STAGES > 0 ? FDTD_TMA_STAGES : ((4 * STAGE <= 200 * 1024) ? 4 : ((3 * STAGE <= 200 * 1024) ? 3 : 2));
   static constexpr int SMEM = STAGES * STAGE + 128;
 };
 
@@ -128,7 +139,7 @@ __device__ __forceinline__ Vec<T, W> lds (const unsigned char *p)
 /* ------------------------------------------------------------------ E half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
-__global__ void __launch_bounds__ (NTHREADS, 1)
+__global__ void __launch_bounds__ (NTHREADS, FDTD_TMA_MINB)
 e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   typedef Tile<T, NC, PML> L;
@@ -183,6 +194,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   T *Dx = p.f[6], *Dy = p.f[7], *Dz = p.f[8];
 
   const bool jlo = j >= 1, jhi = j < p.ny - 1;
+  const bool j_face = TFSF && tfsf_axis_hit (p, 1, j, true);
 
   T ca_y_at = 0, cbd_y_at = 0, p_y_btw = 0, m_y_btw = 0, q_y_at = 0;
   MVec p_x_btw = {}, m_x_btw = {}, ca_x_at = {}, cbd_x_at = {}, q_x_at = {};
@@ -234,6 +246,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
     const int gk = p.kz0 + k;
     const bool klo = gk >= 1, khi = gk < p.nzg - 1;
+    const bool jk_face = j_face || (TFSF && tfsf_axis_hit (p, 2, gk, true));
 
     const FVec hz = lds<T, W> (sA_own + so), hz_jm = lds<T, W> (sA_jm + so);
     const FVec hy = lds<T, W> (sB_own + so);
@@ -292,7 +305,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
           cez[c] = hy.v[s] - hy_m - hx.v[s] + hx_jm.v[s];
         }
 
-        if (TFSF)
+        if (TFSF && (jk_face || tfsf_axis_hit (p, 0, i, true)))
         {
           const int fx = tfsf_e_faces (p, 0, i, j, gk), fy = tfsf_e_faces (p, 1, i, j, gk), fz = tfsf_e_faces (p, 2, i, j, gk);
           if (fx | fy | fz)
@@ -375,7 +388,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 /* ------------------------------------------------------------------ H half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
-__global__ void __launch_bounds__ (NTHREADS, 1)
+__global__ void __launch_bounds__ (NTHREADS, FDTD_TMA_MINB)
 h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   typedef Tile<T, NC, PML> L;
@@ -432,6 +445,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   T *Bx = p.f[9], *By = p.f[10], *Bz = p.f[11];
 
   const bool jlo = j >= 1, jhi = j < p.ny - 1;
+  const bool j_face = TFSF && tfsf_axis_hit (p, 1, j, false);
 
   T ca_y_btw = 0, cbd_y_btw = 0, p_y_at = 0, m_y_at = 0, q_y_btw = 0;
   MVec p_x_at = {}, m_x_at = {}, ca_x_btw = {}, cbd_x_btw = {}, q_x_btw = {};
@@ -484,6 +498,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
     const int gk = p.kz0 + k;
     const bool klo = gk >= 1, khi = gk < p.nzg - 1;
+    const bool jk_face = j_face || (TFSF && tfsf_axis_hit (p, 2, gk, false));
 
     const FVec ez = lds<T, W> (sA_own + so), ez_jp = lds<T, W> (sA_jp + so);
     const FVec ey_kp = lds<T, W> (sB_own + so);
@@ -542,7 +557,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
           chz[c] = ex_jp.v[s] - ex.v[s] - ey_p + ey.v[s];
         }
 
-        if (TFSF)
+        if (TFSF && (jk_face || tfsf_axis_hit (p, 0, i, false)))
         {
           const int fx = tfsf_h_faces (p, 0, i, j, gk), fy = tfsf_h_faces (p, 1, i, j, gk), fz = tfsf_h_faces (p, 2, i, j, gk);
           if (fx | fy | fz)

@@ -676,7 +676,7 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
     const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
     s->use_tma = !(sel && strcmp (sel, "direct") == 0);
     const int txc = s->use_tma ? 32 * (16 / s->cell) : 32 * (16 / s->cell);
-    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + 7) / 8);
+    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + 7) / 8); /* approximate: 8-row tiles */
     long long zsplit = (2 * 148 + tiles - 1) / tiles;
     int kc = (int) (s->nzl / (zsplit > 0 ? zsplit : 1));
     if (kc > 64) kc = 64;
