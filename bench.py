@@ -197,11 +197,8 @@ def main():
     s = F.Solver(cfg)
     if world > 1:
         # the 128-byte NCCL id travels over torch.distributed; the exchange itself is inside the library
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt.copy_(torch.frombuffer(bytearray(F.Solver.comm_unique_id()), dtype=torch.uint8))
-        dist.broadcast(idt, 0)
-        s.comm_init(bytes(idt.cpu().numpy().tobytes()))
+        from fdtd3d_b200 import multi
+        s.comm_init(multi.share_unique_id(dist, rank, "cuda"))
     for a in range(3):
         s.set_sigma(a, F.pml_sigma_profile(cfg, a))
     s.init_eps_sphere()  # Scheme3D.cpp:3437: centre (40.5,40.5,40.5), r = 20, eps = 2

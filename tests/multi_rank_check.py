@@ -1,0 +1,73 @@
+"""Launched by torchrun (one rank per GPU) from tests/test_gpu_multi.py: a z-slab sharded run in exact mode, every
+rank's slab compared bit for bit with the oracle's whole-grid result.  Exit code 0 = parity."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import fdtd3d_b200 as F  # noqa: E402
+from fdtd3d_b200 import multi  # noqa: E402
+import oracle_lib as O  # noqa: E402
+from gpu_util import random_inputs  # noqa: E402
+
+
+def main():
+    rank, world, local = multi.env_rank()
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    failures = 0
+    cases = [
+        # size (nz not divisible by world on purpose), pml, tfsf, use_pml, use_tfsf, value_type, complex, steps, angles
+        ((24, 20, 27), 4, 6, True, True, 8, False, 9, (90, 0, 90)),
+        ((21, 18, 26), 3, 5, True, True, 8, True, 7, (40, 50, 30)),
+        ((20, 22, 24), 4, 6, True, False, 8, False, 8, (90, 0, 90)),
+        ((18, 16, 22), 3, 5, False, True, 4, False, 8, (90, 0, 90)),
+    ]
+    for size, pml, tfsf, use_pml, use_tfsf, vt, cplx, steps, ang in cases:
+        kw = dict(size=size, pml=pml, tfsf=tfsf, use_pml=use_pml, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx,
+                  theta=ang[0], phi=ang[1], psi=ang[2], exact_mode=1)
+        cfg1 = O.make_config(**kw)
+        inputs, fields = random_inputs(cfg1, seed=99)
+        ref = O.run(cfg1, steps, inputs, fields)  # whole grid, on every rank's CPU
+        cfg = O.make_config(**kw)
+        cfg.rank, cfg.nranks, cfg.device = rank, world, local
+        z0, nzl = F.slab_range(size[2], rank, world)
+        with F.Solver(cfg) as s:
+            s.comm_init(multi.share_unique_id(dist, rank, "cuda"))
+            for a in range(3):
+                s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+            s.upload("Eps", inputs["Eps"])   # whole-grid arrays: planes a rank does not own are ignored
+            s.upload("Mu", inputs["Mu"])
+            for name in O.field_names(cfg):
+                s.upload(name, fields[name])
+            s.run(steps - 3)
+            s.run(3)                          # a second run exercises the halo refresh at run start
+            for name in O.field_names(cfg):
+                got = s.download(name, z0=z0, nz=nzl)
+                want = multi.slab_of_array(ref[name], size, z0, nzl)
+                exact = np.array_equal(got, want)
+                if vt == 8 and not exact or vt == 4 and np.abs(got - want).max() > 1e-5 * max(np.abs(want).max(), 1e-30):
+                    failures += 1
+                    print("rank %d case %s field %s: max |d| = %g" % (rank, size, name, np.abs(got - want).max()), flush=True)
+            if use_tfsf:
+                for name in ("EInc", "HInc"):
+                    if vt == 8 and not np.array_equal(s.download(name), ref[name]):
+                        failures += 1
+                        print("rank %d: %s differs" % (rank, name), flush=True)
+    t = torch.tensor([failures], device="cuda")
+    dist.all_reduce(t)
+    if rank == 0:
+        print("multi_rank_check: world %d, total failures %d" % (world, int(t.item())), flush=True)
+    dist.destroy_process_group()
+    return 1 if int(t.item()) else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
