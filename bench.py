@@ -35,6 +35,21 @@ NZ_PER_GPU = 512
 PML, TFSF = 10, 20
 DX, WAVELENGTH = 0.0005, 0.02
 
+# BASELINE.json configs; "c3" is the configuration the metric is quoted on (roofline headline) and the default.
+# nz: planes per GPU (weak scaling) unless "nz_total" is given (the grid is then split over the ranks).
+WORKLOADS = {
+    "c3": dict(dims=3, nx=512, ny=512, nz=512, vt=8, cplx=False, pml=True, tfsf=True, sphere=True,
+               label="3D 512x512x%(nz)d double real, UPML(10)+TF/SF(20) plane wave, eps sphere; BASELINE.json configs[2]"),
+    "c1": dict(dims=3, nx=80, ny=80, nz_total=80, vt=8, cplx=False, pml=True, tfsf=True, sphere=True,
+               label="3D 80x80x%(nz)d double real, UPML(10)+TF/SF(20), eps sphere; BASELINE.json configs[0] (README launch example)"),
+    "c2": dict(dims=2, nx=4096, ny=4096, nz_total=1, vt=4, cplx=False, pml=True, tfsf=False, sphere=False,
+               label="2D TMz 4096x4096 float real, UPML(10), point source at Ez(70, 2048); BASELINE.json configs[1]"),
+    "c4": dict(dims=3, nx=1024, ny=1024, nz_total=1024, vt=8, cplx=True, pml=True, tfsf=True, sphere=True,
+               label="3D 1024x1024x%(nz)d complex double, UPML(10)+TF/SF(20), z-slab sharded; BASELINE.json configs[3]"),
+    "c5": dict(dims=3, nx=1024, ny=1024, nz=512, vt=4, cplx=False, pml=True, tfsf=False, sphere=True,
+               label="3D 1024x1024x%(nz)d float real, UPML(10), point source; BASELINE.json configs[4] (weak scaling)"),
+}
+
 
 # ----------------------------------------------------------------------------- clocks
 
@@ -80,11 +95,16 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------- CPU legs (oracle = checker / baseline only)
 
-def cpu_oracle_baseline(n=256, steps=None, budget_s=15.0):
-    """The Tier-2 oracle (OpenMP port of the reference step) on a bounded n^3 sample of the workload."""
+def cpu_oracle_baseline(workload="c3", n=None, steps=None, budget_s=15.0):
+    """The Tier-2 oracle (OpenMP port of the reference step) on a bounded sub-grid sample of the workload."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as O
-    cfg = O.make_config(size=(n, n, n), pml=PML, tfsf=TFSF, use_pml=True, use_tfsf=True, dx=DX, wavelength=WAVELENGTH)
+    w = WORKLOADS[workload]
+    if n is None:
+        n = min(256, w["nx"]) if w["dims"] == 3 else min(2048, w["nx"])
+    size = (n, n, n)[:w["dims"]]
+    cfg = O.make_config(dims=w["dims"], size=size, pml=PML, tfsf=TFSF, use_pml=w["pml"], use_tfsf=w["tfsf"], value_type=w["vt"],
+                        complex_values=w["cplx"], dx=DX, wavelength=WAVELENGTH)
     inputs = O.reference_setup(cfg)
     cores = O.lib().oracle_max_threads()
     t0 = time.perf_counter()
@@ -95,8 +115,8 @@ def cpu_oracle_baseline(n=256, steps=None, budget_s=15.0):
     t0 = time.perf_counter()
     O.run(cfg, steps, inputs)
     dt = time.perf_counter() - t0
-    return {"value": n ** 3 * steps / dt / 1e6, "unit": METRIC, "cores": cores, "kind": "port",
-            "sample": "%d^3 sub-grid of the workload (same flags), %d steps, OpenMP oracle, alloc+init included" % (n, steps)}
+    return {"value": n ** w["dims"] * steps / dt / 1e6, "unit": METRIC, "cores": cores, "kind": "port",
+            "sample": "%s sub-grid of the workload (same flags), %d steps, OpenMP oracle, alloc+init included" % ("x".join([str(n)] * w["dims"]), steps)}
 
 
 def run_reference_arm(args):
@@ -123,7 +143,7 @@ def run_reference_arm(args):
         ms = secs / total * 1e3
         steps_run = total
     else:
-        cb = cpu_oracle_baseline(n=128, steps=max(2, min(steps, 20)))
+        cb = cpu_oracle_baseline("c3", n=128, steps=max(2, min(steps, 20)))
         value = cb["value"]
         ms = 128 ** 3 / (value * 1e6) * 1e3
         steps_run = steps
@@ -136,13 +156,24 @@ def run_reference_arm(args):
     return 0
 
 
-def workload_config(n_gpus):
-    return {"workload": "3D %dx%dx%d double real, UPML(10)+TF/SF(20) plane wave, eps sphere; BASELINE.json configs[2]%s"
-                        % (NX, NY, NZ_PER_GPU * n_gpus, "" if n_gpus == 1 else " extended to %d z-slabs of 512 planes" % n_gpus),
-            "size": [NX, NY, NZ_PER_GPU * n_gpus], "pml": PML, "tfsf": TFSF, "dx": DX, "wavelength": WAVELENGTH,
+def workload_nz(w, n_gpus):
+    return w["nz_total"] if "nz_total" in w else w["nz"] * n_gpus
+
+
+def workload_config(n_gpus, name="c3", exact=0):
+    w = WORKLOADS[name]
+    nz = workload_nz(w, n_gpus)
+    fv = w["vt"] * (2 if w["cplx"] else 1)
+    nfields = (12 if w["pml"] else 6) if w["dims"] == 3 else (6 if w["pml"] else 3)
+    gb = nfields * w["nx"] * w["ny"] * nz * fv / n_gpus / 1e9
+    return {"workload": w["label"] % {"nz": nz} + ("" if n_gpus == 1 else "; %d z-slabs" % n_gpus),
+            "name": name, "size": [w["nx"], w["ny"], nz][:w["dims"]], "pml": PML if w["pml"] else 0, "tfsf": TFSF if w["tfsf"] else 0,
+            "dx": DX, "wavelength": WAVELENGTH,
             "parallelism": "1 GPU" if n_gpus == 1 else "z-slab x%d, NCCL send/recv halo planes" % n_gpus,
-            "l2": "inputs larger than L2 (>= 15 GB of fields per GPU vs 126 MB L2); no flush needed",
-            "arithmetic": "fast mode (1-D reciprocal tables + explicit FMA; -fmad=false elsewhere), within 1e-12 of the reference"}
+            "l2": "inputs larger than L2 (%.1f GB of fields per GPU vs 126 MB L2); no flush" % gb if gb > 0.5 else
+                  "fields (%.2f GB) fit in L2: numbers are L2-resident, not an HBM roofline" % gb,
+            "arithmetic": "exact mode (reference operand order, IEEE division, no FMA contraction): bit-for-bit with the reference" if exact else
+                          "fast mode (1-D reciprocal tables + explicit FMA; -fmad=false elsewhere), within 1e-12 (double) / 1e-5 (float) of the reference"}
 
 
 # ----------------------------------------------------------------------------- our arm
@@ -156,7 +187,7 @@ def main():
     ap.add_argument("--exact", type=int, default=0, help="1: bench the exact-mode kernels instead")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--nz", type=int, default=NZ_PER_GPU, help=argparse.SUPPRESS)
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json config (default c3, the headline)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -190,20 +221,30 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    nz_total = args.nz * world
-    cfg = F.make_config(dims=3, size=(NX, NY, nz_total), pml=PML, tfsf=TFSF, use_pml=True, use_tfsf=True, value_type=8,
-                        complex_values=False, dx=DX, wavelength=WAVELENGTH, exact_mode=args.exact, device=local, rank=rank,
-                        nranks=world)
+    w = WORKLOADS[args.workload]
+    dims, nx, ny = w["dims"], w["nx"], w["ny"]
+    nz_total = workload_nz(w, world)
+    if dims == 2 and world > 1:
+        raise SystemExit("the 2D TMz workload runs on one GPU")
+    cfg = F.make_config(dims=dims, size=(nx, ny, nz_total)[:dims], pml=PML, tfsf=TFSF, use_pml=w["pml"], use_tfsf=w["tfsf"],
+                        value_type=w["vt"], complex_values=w["cplx"], dx=DX, wavelength=WAVELENGTH, exact_mode=args.exact,
+                        device=local, rank=rank, nranks=world)
     s = F.Solver(cfg)
     if world > 1:
         # the 128-byte NCCL id travels over torch.distributed; the exchange itself is inside the library
         from fdtd3d_b200 import multi
         s.comm_init(multi.share_unique_id(dist, rank, "cuda"))
-    for a in range(3):
-        s.set_sigma(a, F.pml_sigma_profile(cfg, a))
-    s.init_eps_sphere()  # Scheme3D.cpp:3437: centre (40.5,40.5,40.5), r = 20, eps = 2
-    cells = NX * NY * nz_total
+    if w["pml"]:
+        for a in range(dims):
+            s.set_sigma(a, F.pml_sigma_profile(cfg, a))
+    if w["sphere"]:
+        s.init_eps_sphere()  # Scheme3D.cpp:3437: centre (40.5,40.5,40.5), r = 20, eps = 2
+    cells = nx * ny * nz_total
     z0, nzl = F.slab_range(nz_total, rank, world)
+    fp = w["vt"]
+    fv = fp * (2 if w["cplx"] else 1)
+    rdt = torch.float64 if fp == 8 else torch.float32
+    fdt = {(8, False): torch.float64, (4, False): torch.float32, (8, True): torch.complex128, (4, True): torch.complex64}[(fp, w["cplx"])]
 
     # ---- device-resident throughput
     s.run(args.warmup)
@@ -226,8 +267,13 @@ def main():
     value = cells * args.steps / (ms * 1e-3) / 1e6
 
     # ---- roofline of the dominant kernel (single-rank run: per-kernel CUDA events inside the timed region)
-    fv = 8
-    bytes_per_cell_half_step = 15 * fv + 1 * 8  # 15 FieldValue + 1 FPValue per cell per half step
+    # SURVEY.md §8d, per cell per half step: 3D: (9 or 15) FieldValue + 1 FPValue; TMz E: (4 or 6) FV + FP, H: (5 or 9) FV + FP
+    if dims == 3:
+        bytes_e = bytes_h = (15 if w["pml"] else 9) * fv + fp
+        kn = ("e_phase_3d", "h_phase_3d")
+    else:
+        bytes_e, bytes_h = (6 if w["pml"] else 4) * fv + fp, (9 if w["pml"] else 5) * fv + fp
+        kn = ("ez_phase_tmz", "h_phase_tmz")
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -236,40 +282,43 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     roofline = None
     if psteps:
-        name, k_ms = ("h_phase_3d", h_ms / psteps) if h_ms >= e_ms else ("e_phase_3d", e_ms / psteps)
-        achieved = bytes_per_cell_half_step * (NX * NY * nzl) / (k_ms * 1e-3) / 1e9
+        name, k_ms, bytes_k = (kn[1], h_ms / psteps, bytes_h) if h_ms >= e_ms else (kn[0], e_ms / psteps, bytes_e)
+        achieved = bytes_k * (nx * ny * nzl) / (k_ms * 1e-3) / 1e9
         traffic = None
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
-            traffic = prof.get(name, {}).get("dram_bytes_per_launch")
+            traffic = prof.get(name, {}).get("dram_bytes_per_launch") if args.workload == "c3" and not args.exact else None
         except Exception:
             pass
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                     "kernel": name, "kernel_ms": k_ms, "e_phase_ms": e_ms / psteps, "h_phase_ms": h_ms / psteps,
-                    "algorithmic_bytes_per_launch": bytes_per_cell_half_step * NX * NY * nzl,
+                    "algorithmic_bytes_per_launch": bytes_k * nx * ny * nzl,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
-                    "whole_step_frac": (2 * bytes_per_cell_half_step * NX * NY * nzl / (ms / args.steps * 1e-3) / 1e9) / peak}
+                    "whole_step_frac": ((bytes_e + bytes_h) * nx * ny * nzl / (ms / args.steps * 1e-3) / 1e9) / peak}
     else:
-        whole = 2 * bytes_per_cell_half_step * NX * NY * nzl / (ms / args.steps * 1e-3) / 1e9
+        whole = (bytes_e + bytes_h) * nx * ny * nzl / (ms / args.steps * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": whole, "peak": peak, "unit": "GB/s", "frac": whole / peak, "traffic": None,
                     "kernel": "whole step per GPU (multi-rank run: boundary + interior launches overlap with the exchange)"}
 
     # ---- end to end through the C ABI with host buffers (upload + K steps + download in the timed region)
     e2e = None
     if not args.no_e2e:
-        names = ["Ex", "Ey", "Ez", "Hx", "Hy", "Hz", "Dx", "Dy", "Dz", "Bx", "By", "Bz"]
-        n_slab = NX * NY * nzl
-        host = torch.zeros(n_slab, dtype=torch.float64).pin_memory().numpy()  # all fields start at zero (no RNG)
-        eps_host = s.download("Eps", z0=z0, nz=nzl + 1)
+        names = ["Ex", "Ey", "Ez", "Hx", "Hy", "Hz"] if dims == 3 else ["Ez", "Hx", "Hy"]
+        if w["pml"]:
+            names += ["Dx", "Dy", "Dz", "Bx", "By", "Bz"] if dims == 3 else ["Dz", "Bx", "By"]
+        n_slab = nx * ny * nzl
+        nzm = nzl + 1 if dims == 3 else 1
+        host = torch.zeros(n_slab, dtype=fdt).pin_memory().numpy()  # all fields start at zero (no RNG)
+        eps_host = s.download("Eps", z0=z0, nz=nzm)
         eps_pin = torch.from_numpy(eps_host).pin_memory().numpy()
-        mu_pin = torch.ones(eps_host.size, dtype=torch.float64).pin_memory().numpy()
-        h2d = (len(names) * n_slab + 2 * eps_host.size) * 8
-        d2h = len(names) * n_slab * 8
+        mu_pin = torch.ones(eps_host.size, dtype=rdt).pin_memory().numpy()
+        h2d = len(names) * n_slab * fv + 2 * eps_host.size * fp
+        d2h = len(names) * n_slab * fv
         outs = host  # results land in the same pinned buffer, field after field
         barrier()
         t0 = time.perf_counter()
-        s.upload("Eps", eps_pin, z0=z0, nz=nzl + 1)
-        s.upload("Mu", mu_pin, z0=z0, nz=nzl + 1)
+        s.upload("Eps", eps_pin, z0=z0, nz=nzm)
+        s.upload("Mu", mu_pin, z0=z0, nz=nzm)
         for nme in names:
             s.upload(nme, host, z0=z0, nz=nzl)
         s.run(args.steps)
@@ -279,8 +328,8 @@ def main():
         t_e2e = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": cells * args.steps / t_e2e / 1e6, "unit": METRIC, "h2d_bytes_per_step": h2d * world / args.steps,
                "d2h_bytes_per_step": d2h * world / args.steps, "seconds": t_e2e,
-               "what": "per rank: upload eps, mu and 12 fields from pinned host memory in reference (z-fastest) order, %d steps, "
-                       "download 12 fields; host wall clock, max over ranks" % args.steps}
+               "what": "per rank: upload eps, mu and %d fields from pinned host memory in reference (z-fastest) order, %d steps, "
+                       "download %d fields; host wall clock, max over ranks" % (len(names), args.steps, len(names))}
         launches_e2e = s.launch_count
     s.close()
 
@@ -288,14 +337,15 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            cpu = cpu_oracle_baseline()
+            cpu = cpu_oracle_baseline(args.workload)
         except Exception as ex:  # the baseline must not take the GPU numbers down with it
             cpu = {"value": None, "unit": METRIC, "cores": None, "kind": "port", "sample": "failed: %r" % (ex,)}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic", "config": workload_config(world), "roofline": roofline,
+                "dtype": {8: "f64", 4: "f32"}[fp] + ("c" if w["cplx"] else ""), "data": "synthetic",
+                "config": workload_config(world, args.workload, args.exact), "roofline": roofline,
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "per_gpu_value": value / world, "host_wall_s": t_wall, "exact_mode": args.exact}
         print(json.dumps(line))

@@ -73,7 +73,26 @@ def _build(force, verbose, defines):
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stdout)
+    _build_cli(LIB)
     return LIB
+
+
+def _build_cli(lib):
+    """fdtd3d_b200/bin/fdtd3d: the solver binary with the reference's command line (host C++, links the C ABI)."""
+    host = os.path.join(HERE, "host")
+    srcs = [os.path.join(host, f) for f in ("main.cpp", "Settings.cpp", "Scheme.cpp")]
+    hdrs = [os.path.join(host, f) for f in ("Settings.h", "Scheme.h")]
+    exe = os.path.join(HERE, "bin", "fdtd3d")
+    if os.path.basename(lib) != "libfdtd3d_b200.so":
+        return
+    if os.path.exists(exe) and not any(_newer(f, exe) for f in srcs + hdrs + [lib]):
+        return
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    cmd = ["/usr/bin/g++", "-std=c++14", "-O2", "-ffp-contract=off", "-Wall"] + srcs + \
+          ["-L" + HERE, "-lfdtd3d_b200", "-Wl,-rpath,$ORIGIN/..", "-o", exe]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building the fdtd3d binary failed:\n" + r.stdout)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,156 @@
+#include "Scheme.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <vector>
+
+#include "Settings.h"
+
+YeeGridLayout::YeeGridLayout (int d, const long long s[3], const long long p[3], const long long t[3], double teta,
+                              double phi, double psi)
+  : tetaDeg (teta), phiDeg (phi), psiDeg (psi), dims (d)
+{
+  for (int a = 0; a < 3; ++a)
+  {
+    size[a] = a < d ? s[a] : 1;
+    pml[a] = a < d ? p[a] : 0;
+    tfsf[a] = a < d ? t[a] : 0;
+  }
+  /* YeeGridLayout.h:446-447: ASSERT (angle >= 0 && angle <= Pi / 2) for teta and phi */
+  if (teta < 0 || teta > 90.0 || phi < 0 || phi > 90.0)
+  {
+    printf ("ERROR: incident wave angles teta and phi must be within [0, 90] degrees.\n");
+    exit (EXIT_ERROR);
+  }
+}
+
+void DeviceScheme::fail (const char *what) const
+{
+  printf ("ERROR: %s: %s\n", what, fdtd_last_error ());
+  exit (EXIT_ERROR);
+}
+
+DeviceScheme::DeviceScheme (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType,
+                            bool complexValues, bool exactMode, int device)
+  : yeeLayout (layout), handle (NULL), totalStep (tStep), lastRunMs (0)
+{
+  memset (&cfg, 0, sizeof (cfg));
+  cfg.abi_version = FDTD3D_B200_ABI_VERSION;
+  cfg.dims = layout->dims;
+  cfg.value_type = valueType;
+  cfg.complex_values = complexValues;
+  cfg.use_pml = doUsePML;
+  cfg.use_tfsf = doUseTFSF;
+  cfg.exact_mode = exactMode;
+  cfg.device = device;
+  for (int a = 0; a < 3; ++a)
+  {
+    cfg.size[a] = layout->size[a];
+    cfg.pml_size[a] = layout->pml[a];
+    cfg.tfsf_size[a] = layout->tfsf[a];
+  }
+  cfg.nranks = 1;
+  /* Scheme3D.h:287-290: TF/SF needs a non-zero scattered zone, PML a non-zero PML size */
+  if (doUseTFSF && cfg.tfsf_size[0] == 0 && cfg.tfsf_size[1] == 0 && cfg.tfsf_size[2] == 0)
+  {
+    printf ("ERROR: --use-tfsf needs a non-zero TF/SF size.\n");
+    exit (EXIT_ERROR);
+  }
+  if (doUsePML && cfg.pml_size[0] == 0 && cfg.pml_size[1] == 0 && cfg.pml_size[2] == 0)
+  {
+    printf ("ERROR: --use-pml needs a non-zero PML size.\n");
+    exit (EXIT_ERROR);
+  }
+}
+
+DeviceScheme::~DeviceScheme ()
+{
+  if (handle) fdtd_destroy (handle);
+}
+
+void DeviceScheme::initScheme (double dx, double wavelength)
+{
+  cfg.dx = dx;
+  if (fdtd_init_scheme (&cfg, wavelength, yeeLayout->tetaDeg, yeeLayout->phiDeg, yeeLayout->psiDeg) != FDTD_OK)
+  {
+    printf ("ERROR: invalid scheme parameters (dx = %g, wavelength = %g).\n", dx, wavelength);
+    exit (EXIT_ERROR);
+  }
+}
+
+void DeviceScheme::initGrids ()
+{
+  if (fdtd_create (&cfg, &handle) != FDTD_OK) fail ("cannot create the device scheme");
+  if (cfg.use_pml)
+  {
+    for (int a = 0; a < cfg.dims; ++a)
+    {
+      std::vector<char> prof ((size_t) (cfg.size[a] + 1) * cfg.value_type);
+      if (fdtd_pml_sigma_profile (&cfg, a, prof.data (), cfg.size[a] + 1) != FDTD_OK)
+      {
+        printf ("ERROR: cannot build the PML profile along axis %d.\n", a);
+        exit (EXIT_ERROR);
+      }
+      if (fdtd_set_sigma (handle, a, prof.data (), cfg.size[a] + 1) != FDTD_OK) fail ("fdtd_set_sigma");
+    }
+  }
+  /* Scheme3D.cpp:3437: eps = smoothed sphere, centre (40.5, 40.5, 40.5), radius 20, eps 2 (hard-coded there);
+   * SchemeTMz.cpp:1966-2002: eps = 1.  mu = 1 in both (fdtd_create's default). */
+  if (cfg.dims == 3 && fdtd_init_eps_sphere (handle, 40.5, 40.5, 40.5, 20.0, 2.0) != FDTD_OK) fail ("fdtd_init_eps_sphere");
+}
+
+void DeviceScheme::performSteps ()
+{
+  if (!handle) initGrids ();
+  if (fdtd_run (handle, totalStep) != FDTD_OK) fail ("fdtd_run");
+  float ms = 0;
+  fdtd_last_run_ms (handle, &ms);
+  lastRunMs = ms;
+}
+
+void DeviceScheme::dumpDat (const std::string &dir)
+{
+  static const char *names3[] = { "Ex", "Ey", "Ez", "Hx", "Hy", "Hz", "Dx", "Dy", "Dz", "Bx", "By", "Bz" };
+  const long long cells = cfg.size[0] * cfg.size[1] * (cfg.dims == 3 ? cfg.size[2] : 1);
+  const size_t cell = (size_t) cfg.value_type * (cfg.complex_values ? 2 : 1);
+  std::vector<char> buf ((size_t) cells * cell);
+  int64_t t = 0;
+  fdtd_get_time_step (handle, &t);
+  for (int f = 0; f < 12; ++f)
+  {
+    const int comp = f % 3;
+    const bool e_like = f < FDTD_HX || (f >= FDTD_DX && f < FDTD_BX);
+    if (cfg.dims == 2 && (e_like ? comp != 2 : comp == 2)) continue;
+    if (f >= FDTD_DX && !cfg.use_pml) continue;
+    if (fdtd_download (handle, f, buf.data (), FDTD_ORDER_REFERENCE, 0, cfg.dims == 3 ? cfg.size[2] : 1) != FDTD_OK) fail ("fdtd_download");
+    const std::string path = dir + "/current[" + std::to_string ((long long) t) + "]_rank-0_" + names3[f] + ".dat";
+    std::ofstream file (path.c_str (), std::ios::out | std::ios::binary);
+    if (!file.is_open ())
+    {
+      printf ("ERROR: cannot write %s\n", path.c_str ());
+      exit (EXIT_ERROR);
+    }
+    file.write (buf.data (), (std::streamsize) buf.size ());
+  }
+}
+
+Scheme3D::Scheme3D (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
+                    bool exactMode, int device)
+  : DeviceScheme (layout, tStep, doUsePML, doUseTFSF, valueType, complexValues, exactMode, device)
+{
+}
+
+SchemeTMz::SchemeTMz (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
+                      bool exactMode, int device)
+  : DeviceScheme (layout, tStep, doUsePML, doUseTFSF, valueType, complexValues, exactMode, device)
+{
+  /* SchemeTMz.h:241-246: only phi = 0 and phi = 45 degrees are implemented for the TMz incident wave */
+  if (doUseTFSF && layout->phiDeg != 0.0 && layout->phiDeg != 45.0)
+  {
+    printf ("ERROR: the TMz scheme supports TF/SF only for --angle-phi 0 or 45.\n");
+    exit (EXIT_ERROR);
+  }
+}
