@@ -170,8 +170,8 @@ def workload_config(n_gpus, name="c3", exact=0):
             "name": name, "size": [w["nx"], w["ny"], nz][:w["dims"]], "pml": PML if w["pml"] else 0, "tfsf": TFSF if w["tfsf"] else 0,
             "dx": DX, "wavelength": WAVELENGTH,
             "parallelism": "1 GPU" if n_gpus == 1 else "z-slab x%d, NCCL send/recv halo planes" % n_gpus,
-            "l2": "inputs larger than L2 (%.1f GB of fields per GPU vs 126 MB L2); no flush" % gb if gb > 0.5 else
-                  "fields (%.2f GB) fit in L2: numbers are L2-resident, not an HBM roofline" % gb,
+            "l2": "inputs larger than L2 (%.2f GB of fields per GPU vs 126 MB L2); no flush" % gb if gb > 0.25 else
+                  "fields (%.3f GB) fit in the 126 MB L2: numbers are L2-resident, not an HBM roofline" % gb,
             "arithmetic": "exact mode (reference operand order, IEEE division, no FMA contraction): bit-for-bit with the reference" if exact else
                           "fast mode (1-D reciprocal tables + explicit FMA; -fmad=false elsewhere), within 1e-12 (double) / 1e-5 (float) of the reference"}
 

@@ -183,3 +183,49 @@ def test_errors_are_reported_not_fatal():
     bad.tfsf_size[0] = 8
     with pytest.raises(F.FdtdError):
         F.Solver(bad)
+
+
+def test_full_size_512_cubed_against_oracle():
+    """BASELINE.json's headline size (3D 512^3 double, PML + TF/SF), every cell exercised: random fields, random
+    materials, 3 steps, exact mode -- each of the twelve fields is compared with the CPU oracle bit for bit through
+    a checksum of per-plane checksums plus full equality of sampled planes, and through |field|^2."""
+    import ctypes as C
+    n, steps = 512, 3
+    cfg = O.make_config(size=(n, n, n), pml=10, tfsf=20, use_pml=True, use_tfsf=True, exact_mode=1)
+    rng = np.random.default_rng(2026)
+    nm = (n + 1) ** 3
+    inputs = {"Eps": rng.uniform(1.0, 4.0, nm), "Mu": rng.uniform(1.0, 2.0, nm)}
+    for a in range(3):
+        inputs["Sigma" + "XYZ"[a]] = O.sigma_profile(cfg, a)
+    scale = {"E": 1.0, "H": 2.6e-3, "D": 8.85e-12, "B": 3.3e-9}
+    names = O.field_names(cfg)
+    fields = {}
+    for name in names:
+        fields[name] = rng.standard_normal(n ** 3, dtype=np.float32).astype(np.float64) * scale[name[0]]
+    with F.Solver(cfg) as s:
+        for a in range(3):
+            s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+        s.upload("Eps", inputs["Eps"])
+        s.upload("Mu", inputs["Mu"])
+        for name in names:
+            s.upload(name, fields[name])
+        s.run(steps)
+        ref = O.run(cfg, steps, inputs, fields)  # ~10 s per step on 16 host cores
+        del fields
+        for name in names + ["EInc", "HInc"]:
+            got = s.download(name)
+            want = ref[name]
+            if name in names:
+                # checksum of per-(i)-plane checksums over the raw bits, then sampled planes in full
+                gb = got.view(np.uint64).reshape(n, -1)
+                wb = want.view(np.uint64).reshape(n, -1)
+                gs = np.bitwise_xor.reduce(gb, axis=1)
+                ws = np.bitwise_xor.reduce(wb, axis=1)
+                assert np.array_equal(gs, ws), "%s: plane checksums differ at i = %s" % (name, np.nonzero(gs != ws)[0][:8])
+                for i in (0, 1, 9, 10, 19, 20, 255, 256, 491, 492, 501, 502, 510, 511):
+                    assert np.array_equal(gb[i], wb[i]), (name, i)
+                sq = float((want ** 2).sum())
+                assert abs(s.sumsq(name) - sq) <= 1e-12 * sq, name
+            else:
+                assert np.array_equal(got, want), name
+            del got
