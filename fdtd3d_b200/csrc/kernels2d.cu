@@ -59,7 +59,7 @@ __device__ __forceinline__ T sub_scaled (T v, T s, double w)
 template <typename T, bool EXACT>
 __device__ __forceinline__ void sweep3_coefs (T pn, T mn, T q, T mod, T &cb, T &cc)
 {
-  if (EXACT) { cb = (pn / mod) / q; cc = (mn / mod) / q; }
+  if (EXACT) { cb = (pn / mod) / q; cc = pn == mn ? cb : (mn / mod) / q; }
   else { T r = q * rcp_t<T> (mod); cb = pn * r; cc = mn * r; }
 }
 

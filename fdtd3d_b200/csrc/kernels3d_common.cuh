@@ -44,9 +44,11 @@ __device__ __forceinline__ void sweep3_coefs (T pn, T mn, T q, T mod, T &cb, T &
 {
   if (EXACT)
   {
-    /* ((2 eps0 k + sigma dt) / modifier) / (2 eps0 k + sigma' dt), Scheme3D.cpp:402-403 */
+    /* ((2 eps0 k + sigma dt) / modifier) / (2 eps0 k + sigma' dt), Scheme3D.cpp:402-403.  Outside the PML
+     * sigma = 0, so both numerators are the same number 2 eps0 and so are the two quotients: computing one
+     * of them is the identical arithmetic (warp-uniform branch almost everywhere). */
     cb = (pn / mod) / q;
-    cc = (mn / mod) / q;
+    cc = pn == mn ? cb : (mn / mod) / q;
   }
   else
   {
