@@ -180,6 +180,10 @@ class Solver:
     def run(self, nsteps):
         _check(lib().fdtd_run(self._h, nsteps))
 
+    def subtract_incident(self):
+        """Total -> scattered field inside the TF/SF box, in place (the reference's --save-res post-processing)."""
+        _check(lib().fdtd_subtract_incident(self._h))
+
     def run_async(self, nsteps):
         _check(lib().fdtd_run_async(self._h, nsteps))
 

@@ -72,6 +72,7 @@ PROTOTYPES = {
     "fdtd_fill": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double]),
     "fdtd_init_eps_sphere": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double]),
     "fdtd_run": (C.c_int, [C.c_void_p, C.c_int64]),
+    "fdtd_subtract_incident": (C.c_int, [C.c_void_p]),
     "fdtd_run_async": (C.c_int, [C.c_void_p, C.c_int64]),
     "fdtd_sync": (C.c_int, [C.c_void_p]),
     "fdtd_last_run_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),

@@ -145,6 +145,39 @@ __global__ void eps_sphere_kernel (T *eps, int mx, int my, int nzm, int kz0, int
   }
 }
 
+/* ------------------------------------------------------------------ scattered field at save time */
+
+/* Scheme3D.cpp:2767-2921 (the block run before results are saved with --save-res): every cell of an E or H
+ * component whose real coordinate lies inside the TF/SF box [L, R] (inclusive) gets the projected incident field
+ * subtracted in place.  One thread per cell of one component; comp = 0..2 (E) or 3..5 (H). */
+template <typename T, int NC>
+__global__ void scattered_kernel (const __grid_constant__ StepParams<T> p, int comp)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  if (i >= p.nx) return;
+  const bool isE = comp < 3;
+  const int a = comp % 3;
+  const T off[3] = { isE ? (a == 0 ? (T) 1 : (T) 0.5) : (a == 0 ? (T) 0.5 : (T) 1),
+                     isE ? (a == 1 ? (T) 1 : (T) 0.5) : (a == 1 ? (T) 0.5 : (T) 1),
+                     isE ? (a == 2 ? (T) 1 : (T) 0.5) : (a == 2 ? (T) 0.5 : (T) 1) };
+  const T rx = (T) i + off[0], ry = (T) j + off[1];
+  if (rx < (T) p.L[0] || rx > (T) p.R[0] || ry < (T) p.L[1] || ry > (T) p.R[1]) return;
+  T *F = p.f[comp];
+  for (int kl = blockIdx.z; kl < p.nzl; kl += gridDim.z)
+  {
+    const int gk = p.kz0 + kl;
+    const T rz = (T) gk + off[2];
+    if (rz < (T) p.L[2] || rz > (T) p.R[2]) continue;
+    T inc[NC];
+    incident_sample<T, NC> (p, isE ? p.einc : p.hinc, isE ? (T) 0 : (T) 0.5, isE ? p.proj_e[a] : p.proj_h[a], i, j, gk,
+                            off[0], off[1], off[2], inc);
+    const long long o = (((long long) (kl + 1) * p.ny + j) * p.pitch + i) * NC;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) F[o + c] = F[o + c] - inc[c];
+  }
+}
+
 /* ------------------------------------------------------------------ reduction */
 
 constexpr int SUMSQ_CTAS = 1184; /* 148 SMs x 8 */
@@ -239,6 +272,18 @@ cudaError_t launch_incident (bool e_phase, const StepParams<T> &p, bool cplx, bo
 }
 template cudaError_t launch_incident<float> (bool, const StepParams<float> &, bool, bool, cudaStream_t);
 template cudaError_t launch_incident<double> (bool, const StepParams<double> &, bool, bool, cudaStream_t);
+
+template <typename T>
+cudaError_t launch_scattered (const StepParams<T> &p, bool cplx, int comp, cudaStream_t stream)
+{
+  dim3 block (128);
+  dim3 grid ((p.nx + 127) / 128, p.ny, p.nzl < 64 ? p.nzl : 64);
+  if (cplx) scattered_kernel<T, 2><<<grid, block, 0, stream>>> (p, comp);
+  else scattered_kernel<T, 1><<<grid, block, 0, stream>>> (p, comp);
+  return cudaGetLastError ();
+}
+template cudaError_t launch_scattered<float> (const StepParams<float> &, bool, int, cudaStream_t);
+template cudaError_t launch_scattered<double> (const StepParams<double> &, bool, int, cudaStream_t);
 
 cudaError_t launch_tick (long long *step, cudaStream_t stream)
 {

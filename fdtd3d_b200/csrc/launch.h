@@ -41,6 +41,11 @@ cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, b
 template <typename T>
 cudaError_t launch_incident (bool e_phase, const StepParams<T> &p, bool cplx, bool exact, cudaStream_t stream);
 
+/* total -> scattered field inside the TF/SF box for one component (0..2 = Ex..Ez, 3..5 = Hx..Hz), in place:
+ * the post-processing of Scheme3D.cpp:2767-2921 */
+template <typename T>
+cudaError_t launch_scattered (const StepParams<T> &p, bool cplx, int comp, cudaStream_t stream);
+
 /* step counter += 1 (one thread) */
 cudaError_t launch_tick (long long *step, cudaStream_t stream);
 

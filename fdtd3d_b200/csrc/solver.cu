@@ -798,6 +798,23 @@ int fdtd_init_eps_sphere (fdtd_handle s, double cx, double cy, double cz, double
   return FDTD_OK;
 }
 
+int fdtd_subtract_incident (fdtd_handle s)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  if (s->cfg.dims != 3 || !s->cfg.use_tfsf) return fail (FDTD_INVALID_ARGUMENT, "the scattered-field post-processing needs a 3D scheme with use_tfsf");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  int rc = sync_run (s);
+  if (rc) return rc;
+  for (int comp = 0; comp < 6; ++comp)
+  {
+    if (s->fp == 4) CUDA_TRY (launch_scattered<float> (make_params<float> (s), s->cfg.complex_values != 0, comp, s->s_compute));
+    else CUDA_TRY (launch_scattered<double> (make_params<double> (s), s->cfg.complex_values != 0, comp, s->s_compute));
+    s->launches++;
+  }
+  CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+  return FDTD_OK;
+}
+
 int fdtd_run_async (fdtd_handle s, int64_t nsteps)
 {
   if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");

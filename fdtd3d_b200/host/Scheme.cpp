@@ -111,22 +111,63 @@ void DeviceScheme::performSteps ()
   lastRunMs = ms;
 }
 
-void DeviceScheme::dumpDat (const std::string &dir)
+static const char *const kFieldNames[] = { "Ex", "Ey", "Ez", "Hx", "Hy", "Hz", "Dx", "Dy", "Dz", "Bx", "By", "Bz", "Eps", "Mu", "EInc", "HInc" };
+
+/* fields that exist for this configuration: E/H (+D/B with PML) of the scheme's components, incident lines with TF/SF */
+static bool fieldPresent (const fdtd_config &cfg, int f)
 {
-  static const char *names3[] = { "Ex", "Ey", "Ez", "Hx", "Hy", "Hz", "Dx", "Dy", "Dz", "Bx", "By", "Bz" };
+  if (f == FDTD_EINC || f == FDTD_HINC) return cfg.use_tfsf != 0;
+  if (f >= FDTD_EPS) return false;
+  const int comp = f % 3;
+  const bool e_like = f < FDTD_HX || (f >= FDTD_DX && f < FDTD_BX);
+  if (cfg.dims == 2 && (e_like ? comp != 2 : comp == 2)) return false;
+  if (f >= FDTD_DX && !cfg.use_pml) return false;
+  return true;
+}
+
+void DeviceScheme::loadDat (const std::string &dir, long long step)
+{
+  if (handle) { fdtd_destroy (handle); handle = NULL; }
+  cfg.time_step_start = step;
+  initGrids ();
   const long long cells = cfg.size[0] * cfg.size[1] * (cfg.dims == 3 ? cfg.size[2] : 1);
+  const long long ninc = 100LL * (cfg.size[0] + cfg.size[1] + (cfg.dims == 3 ? cfg.size[2] : 0));
   const size_t cell = (size_t) cfg.value_type * (cfg.complex_values ? 2 : 1);
-  std::vector<char> buf ((size_t) cells * cell);
+  for (int f = 0; f < FDTD_FIELD_COUNT; ++f)
+  {
+    if (!fieldPresent (cfg, f)) continue;
+    const size_t bytes = (size_t) (f >= FDTD_EINC ? ninc : cells) * cell;
+    std::vector<char> buf (bytes);
+    const std::string path = dir + "/current[" + std::to_string (step) + "]_rank-0_" + kFieldNames[f] + ".dat";
+    std::ifstream file (path.c_str (), std::ios::in | std::ios::binary);
+    if (!file.is_open () || !file.read (buf.data (), (std::streamsize) bytes))
+    {
+      printf ("ERROR: cannot read %zu bytes from %s\n", bytes, path.c_str ());
+      exit (EXIT_ERROR);
+    }
+    if (fdtd_upload (handle, f, buf.data (), FDTD_ORDER_REFERENCE, 0, cfg.dims == 3 ? cfg.size[2] : 1) != FDTD_OK) fail ("fdtd_upload");
+  }
+}
+
+void DeviceScheme::makeScatteredField ()
+{
+  if (cfg.dims != 3 || !cfg.use_tfsf) return;
+  if (fdtd_subtract_incident (handle) != FDTD_OK) fail ("fdtd_subtract_incident");
+}
+
+void DeviceScheme::dumpDat (const std::string &dir, const std::string &prefix)
+{
+  const long long cells = cfg.size[0] * cfg.size[1] * (cfg.dims == 3 ? cfg.size[2] : 1);
+  const long long ninc = 100LL * (cfg.size[0] + cfg.size[1] + (cfg.dims == 3 ? cfg.size[2] : 0));
+  const size_t cell = (size_t) cfg.value_type * (cfg.complex_values ? 2 : 1);
   int64_t t = 0;
   fdtd_get_time_step (handle, &t);
-  for (int f = 0; f < 12; ++f)
+  for (int f = 0; f < FDTD_FIELD_COUNT; ++f)
   {
-    const int comp = f % 3;
-    const bool e_like = f < FDTD_HX || (f >= FDTD_DX && f < FDTD_BX);
-    if (cfg.dims == 2 && (e_like ? comp != 2 : comp == 2)) continue;
-    if (f >= FDTD_DX && !cfg.use_pml) continue;
+    if (!fieldPresent (cfg, f)) continue;
+    std::vector<char> buf ((size_t) (f >= FDTD_EINC ? ninc : cells) * cell);
     if (fdtd_download (handle, f, buf.data (), FDTD_ORDER_REFERENCE, 0, cfg.dims == 3 ? cfg.size[2] : 1) != FDTD_OK) fail ("fdtd_download");
-    const std::string path = dir + "/current[" + std::to_string ((long long) t) + "]_rank-0_" + names3[f] + ".dat";
+    const std::string path = dir + "/current[" + std::to_string ((long long) t) + "]_rank-0_" + prefix + kFieldNames[f] + ".dat";
     std::ofstream file (path.c_str (), std::ios::out | std::ios::binary);
     if (!file.is_open ())
     {

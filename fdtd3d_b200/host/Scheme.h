@@ -55,7 +55,15 @@ public:
 
   /* DATDumper format (Source/File-Management/Dumper/DATDumper.h:84-118): raw FieldValue per cell in linear-index
    * order, file name current[<step>]_rank-<p>_<name>.dat (Source/File-Management/Commons.h:56-68) */
-  void dumpDat (const std::string &dir);
+  void dumpDat (const std::string &dir, const std::string &prefix = "");
+
+  /* resume: load every field (and the incident lines) from DAT dumps of step `step` and continue from there --
+   * the counterpart of DATLoader (Source/File-Management/Loader/DATLoader.h), which the reference never wires up */
+  void loadDat (const std::string &dir, long long step);
+
+  /* the post-processing Scheme3D::performNSteps applies before saving results (Scheme3D.cpp:2767-2921):
+   * total -> scattered field inside the TF/SF box, in place; no-op for 2D or without TF/SF */
+  void makeScatteredField ();
 
   const fdtd_config &config () const { return cfg; }
   double deviceMilliseconds () const { return lastRunMs; }

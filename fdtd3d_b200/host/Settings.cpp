@@ -20,7 +20,7 @@ Settings::Settings ()
     doUseMetamaterials (false), doUseAmplitudeMode (false), gridStep (0.0005), sourceWaveLength (0.02),
     doSaveRes (false), doSaveMaterials (false), doSaveIntermediateRes (false), intermediateSaveStep (100),
     doSaveScatteredFieldRes (false), doSaveScatteredFieldIntermediate (false),
-    valueType ("d"), complexValues (false), exactMode (false), fastMode (false), printSettings (false), cudaDevice (0)
+    valueType ("d"), complexValues (false), exactMode (false), fastMode (false), printSettings (false), cudaDevice (0), startStep (0)
 {
   buildTable ();
 }
@@ -97,6 +97,8 @@ void Settings::buildTable ()
   flag ("--fast", &fastMode, "[fdtd3d_b200] reciprocal tables and FMA (default)");
   integer ("--cuda-device", &cudaDevice, "[fdtd3d_b200] CUDA device ordinal");
   flag ("--print-settings", &printSettings, "[fdtd3d_b200] print the parsed settings and exit");
+  str ("--load-dat", &loadDatDir, "[fdtd3d_b200] directory with DAT dumps (current[<start-step>]_rank-0_<name>.dat) to resume from");
+  integer ("--start-step", &startStep, "[fdtd3d_b200] time step the loaded state belongs to; --time-steps more steps are run");
   str ("--dump-dat", &dumpDatDir, "[fdtd3d_b200] directory for DAT dumps of the final fields (DATDumper format)");
 }
 

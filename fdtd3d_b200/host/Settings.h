@@ -14,7 +14,8 @@
  *   - bool options can only be switched on.
  *
  * Additions (the reference fixes these at compile time, CMakeLists.txt:58-199): --value-type f|d,
- * --complex-values, --exact / --fast, --cuda-device, --print-settings, --dump-dat.
+ * --complex-values, --exact / --fast, --cuda-device, --print-settings, --dump-dat, --load-dat + --start-step
+ * (checkpoint / resume in DATDumper's format; the reference only has the unwired DATLoader class).
  */
 #ifndef FDTD3D_B200_HOST_SETTINGS_H
 #define FDTD3D_B200_HOST_SETTINGS_H
@@ -77,7 +78,8 @@ public:
   std::string valueType; /* "d" or "f" */
   bool complexValues, exactMode, fastMode, printSettings;
   long long cudaDevice;
-  std::string dumpDatDir;
+  std::string dumpDatDir, loadDatDir;
+  long long startStep;
 
   Settings ();
 

@@ -58,15 +58,22 @@ int main (int argc, char **argv)
   else scheme = new Scheme3D (&yeeLayout, s.numTimeSteps, s.doUsePML, s.doUseTFSF, vt, s.complexValues, exact, (int) s.cudaDevice);
 
   scheme->initScheme (s.gridStep, s.sourceWaveLength);
-  scheme->initGrids ();
+  if (!s.loadDatDir.empty ()) scheme->loadDat (s.loadDatDir, s.startStep);
+  else scheme->initGrids ();
 
   struct timeval tv1, tv2;
   gettimeofday (&tv1, NULL);
   scheme->performSteps ();
   gettimeofday (&tv2, NULL);
 
-  if (!s.dumpDatDir.empty ()) scheme->dumpDat (s.dumpDatDir);
-  else if (s.doSaveRes) scheme->dumpDat (".");
+  if (s.doSaveRes)
+  {
+    /* --save-res as in Scheme3D::performNSteps (Scheme3D.cpp:2541-2940): inside the TF/SF box the incident field
+     * is subtracted, then the grids "3D-in-time-Ex" ... are saved -- here as DAT files instead of BMP images */
+    scheme->makeScatteredField ();
+    scheme->dumpDat (s.dumpDatDir.empty () ? std::string (".") : s.dumpDatDir, dims == 3 ? "3D-in-time-" : "2D-TMz-in-time-");
+  }
+  else if (!s.dumpDatDir.empty ()) scheme->dumpDat (s.dumpDatDir);
 
   /* Source/main.cpp:173-233 */
   printf ("Total time = %f seconds\n", (double) (tv2.tv_usec - tv1.tv_usec) / 1000000 + (double) (tv2.tv_sec - tv1.tv_sec));

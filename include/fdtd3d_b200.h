@@ -158,6 +158,13 @@ int fdtd_run (fdtd_handle h, int64_t nsteps);
 int fdtd_run_async (fdtd_handle h, int64_t nsteps);
 int fdtd_sync (fdtd_handle h);
 
+/* Turns the total field inside the TF/SF box into the scattered field, in place, for all six E/H components:
+ * the post-processing the reference applies before it saves results with --save-res
+ * (Source/Scheme/Scheme3D.cpp:2767-2921): cells whose real coordinate lies in
+ * [leftBorderTotalField, rightBorderTotalField] get the projected incident field subtracted.  3D + use_tfsf only.
+ * Like the reference's, it mutates the fields: call it after the last fdtd_run, before downloading for output. */
+int fdtd_subtract_incident (fdtd_handle h);
+
 /* Device time of the last completed fdtd_run / fdtd_run_async+fdtd_sync, from CUDA events on the
  * solver's stream (milliseconds). */
 int fdtd_last_run_ms (fdtd_handle h, float *ms);

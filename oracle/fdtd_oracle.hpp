@@ -695,6 +695,40 @@ public:
       }
   }
 
+  /* ---------------------------------------------------------------- scattered field at save time */
+
+  /* The block Scheme3D::performNSteps runs before saving results when --save-res is given
+   * (Scheme3D.cpp:2767-2921, serial build): for each of the six fields, every cell whose real coordinate lies
+   * inside the TF/SF box [leftBorderTotalField, rightBorderTotalField] (inclusive) gets the projected incident
+   * field subtracted, in place. */
+  void subtractIncident ()
+  {
+    for (int isE = 1; isE >= 0; --isE)
+      for (int a = 0; a < 3; ++a)
+      {
+        std::vector<FV> &Fld = isE ? E[a] : H[a];
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < Nx; ++i)
+          for (int64_t j = 0; j < Ny; ++j)
+            for (int64_t k = 0; k < Nz; ++k)
+            {
+              const int64_t pos[3] = { i, j, k };
+              FP r[3];
+              realCoord (isE != 0, a, pos, r);
+              bool inside = true;
+              for (int ax = 0; ax < 3; ++ax)
+              {
+                FP l = (FP) p.L[ax], rr = (FP) (p.N[ax] - p.L[ax]);
+                if (r[ax] < l || r[ax] > rr) inside = false;
+              }
+              if (!inside) continue;
+              FV incVal = isE ? fromIncidentE (a, approximateIncidentWave (r, (FP) 0.0, EInc))
+                              : fromIncidentH (a, approximateIncidentWave (r, (FP) 0.5, HInc));
+              Fld[idxv (pos)] = Fld[idxv (pos)] - incVal;
+            }
+      }
+  }
+
   /* ---------------------------------------------------------------- time loop */
 
   /* Scheme3D::performNSteps, Scheme3D.cpp:1966-2069; SchemeTMz::performNSteps, SchemeTMz.cpp:1324-1427 */

@@ -38,7 +38,7 @@ Params to_params (const fdtd_config *c)
 }
 
 template <class FP, bool CPLX>
-int run_t (const fdtd_config *c, fdtd_host_arrays *arr, int64_t nsteps)
+int run_t (const fdtd_config *c, fdtd_host_arrays *arr, int64_t nsteps, bool scattered)
 {
   typedef Scheme<FP, CPLX> S;
   typedef typename S::FV FV;
@@ -65,6 +65,7 @@ int run_t (const fdtd_config *c, fdtd_host_arrays *arr, int64_t nsteps)
   }
 
   s.performNSteps (nsteps);
+  if (scattered && c->dims == 3 && c->use_tfsf) s.subtractIncident ();
 
   for (int a = 0; a < ncomp; ++a)
   {
@@ -147,18 +148,31 @@ int oracle_init_eps_sphere (const fdtd_config *cfg, void *out, double cx, double
   return 0;
 }
 
+static int oracle_run_impl (const fdtd_config *cfg, fdtd_host_arrays *arr, int64_t nsteps, int nthreads, bool scattered);
+
 /* Runs nsteps of the restated performNSteps on host arrays (reference order, in/out). */
 int oracle_run (const fdtd_config *cfg, fdtd_host_arrays *arr, int64_t nsteps, int nthreads)
+{
+  return oracle_run_impl (cfg, arr, nsteps, nthreads, false);
+}
+
+/* Same, followed by the --save-res post-processing (total -> scattered field inside the TF/SF box). */
+int oracle_run_scattered (const fdtd_config *cfg, fdtd_host_arrays *arr, int64_t nsteps, int nthreads)
+{
+  return oracle_run_impl (cfg, arr, nsteps, nthreads, true);
+}
+
+static int oracle_run_impl (const fdtd_config *cfg, fdtd_host_arrays *arr, int64_t nsteps, int nthreads, bool scattered)
 {
 #ifdef _OPENMP
   if (nthreads > 0) omp_set_num_threads (nthreads);
 #endif
   try
   {
-    if (cfg->value_type == 8 && !cfg->complex_values) return run_t<double, false> (cfg, arr, nsteps);
-    if (cfg->value_type == 8 && cfg->complex_values) return run_t<double, true> (cfg, arr, nsteps);
-    if (cfg->value_type == 4 && !cfg->complex_values) return run_t<float, false> (cfg, arr, nsteps);
-    if (cfg->value_type == 4 && cfg->complex_values) return run_t<float, true> (cfg, arr, nsteps);
+    if (cfg->value_type == 8 && !cfg->complex_values) return run_t<double, false> (cfg, arr, nsteps, scattered);
+    if (cfg->value_type == 8 && cfg->complex_values) return run_t<double, true> (cfg, arr, nsteps, scattered);
+    if (cfg->value_type == 4 && !cfg->complex_values) return run_t<float, false> (cfg, arr, nsteps, scattered);
+    if (cfg->value_type == 4 && cfg->complex_values) return run_t<float, true> (cfg, arr, nsteps, scattered);
   }
   catch (const std::bad_alloc &)
   {

@@ -10,7 +10,9 @@
  * tests/refio.py reads.  Golden fixtures under tests/golden/ are made from these dumps by
  * tests/golden/make_golden.py.
  *
- * argv: nx ny nz pml tfsf steps use_pml use_tfsf dx wavelength theta_deg phi_deg psi_deg out.bin
+ * argv: nx ny nz pml tfsf steps use_pml use_tfsf dx wavelength theta_deg phi_deg psi_deg out.bin [dump_res]
+ * dump_res = 1 constructs the scheme with doDumpRes (--save-res): the reference then turns the total field inside
+ * the TF/SF box into the scattered field in place before saving (Scheme3D.cpp:2767-2921); BMP writes are stubbed.
  */
 #include <cstdio>
 #include <cstdlib>
@@ -62,7 +64,7 @@ put_grid (const char *name, G &g)
 int
 main (int argc, char **argv)
 {
-  if (argc != 15)
+  if (argc != 15 && argc != 16)
   {
     fprintf (stderr, "usage: %s nx ny nz pml tfsf steps use_pml use_tfsf dx wavelength theta phi psi out.bin\n", argv[0]);
     return 2;
@@ -76,6 +78,7 @@ main (int argc, char **argv)
   FPValue theta = (FPValue) strtod (argv[11], NULL);
   FPValue phi = (FPValue) strtod (argv[12], NULL);
   FPValue psi = (FPValue) strtod (argv[13], NULL);
+  bool dumpRes = argc == 16 && atoi (argv[15]) != 0;
   out = fopen (argv[14], "wb");
   if (!out) { perror ("fopen"); return 2; }
 
@@ -89,14 +92,14 @@ main (int argc, char **argv)
   GridCoordinate3D pmlSize (pml, pml, pml);
   GridCoordinate3D tfsfSize (tfsf, tfsf, tfsf);
   YeeGridLayout yeeLayout (overallSize, pmlSize, tfsfSize, a1, a2, a3, false);
-  Scheme3D scheme (&yeeLayout, overallSize, steps, false, 0, usePML, useTFSF, false, false, false);
+  Scheme3D scheme (&yeeLayout, overallSize, steps, false, 0, usePML, useTFSF, false, false, dumpRes);
 #endif
 #ifdef GRID_2D
   GridCoordinate2D overallSize (nx, ny);
   GridCoordinate2D pmlSize (pml, pml);
   GridCoordinate2D tfsfSize (tfsf, tfsf);
   YeeGridLayout yeeLayout (overallSize, pmlSize, tfsfSize, a1, a2, a3, false);
-  SchemeTMz scheme (&yeeLayout, overallSize, steps, false, 0, usePML, useTFSF, a2, false, false);
+  SchemeTMz scheme (&yeeLayout, overallSize, steps, false, 0, usePML, useTFSF, a2, false, dumpRes);
 #endif
 
   scheme.initScheme (dx, PhysicsConst::SpeedOfLight / wavelength);

@@ -44,6 +44,8 @@ CASES = {
     "tmz_dc_pml_tfsf":      ("tmz_dc", 96, 80, 1, 8, 14, 60, 1, 1, 90, 0, 90),
     "tmz_f_pml_src":        ("tmz_f", 96, 80, 1, 8, 14, 60, 1, 0, 90, 0, 90),
     "tmz_f_pml_tfsf":       ("tmz_f", 96, 80, 1, 8, 14, 60, 1, 1, 90, 0, 90),
+    # --save-res: the reference subtracts the incident field inside the TF/SF box before saving (Scheme3D.cpp:2767-2921)
+    "3d_d_pml_tfsf_saveres": ("3d_d", 30, 28, 26, 5, 8, 40, 1, 1, 70, 40, 55, "saveres"),
 }
 DX, WAVELENGTH = "0.0005", "0.02"
 
@@ -51,15 +53,19 @@ DX, WAVELENGTH = "0.0005", "0.02"
 def main():
     names = sys.argv[1:] or list(CASES)
     for name in names:
-        variant, nx, ny, nz, pml, tfsf, steps, use_pml, use_tfsf, th, ph, ps = CASES[name]
+        variant, nx, ny, nz, pml, tfsf, steps, use_pml, use_tfsf, th, ph, ps = CASES[name][:12]
+        save_res = len(CASES[name]) > 12
         exe = os.path.join(ROOT, "oracle", "_ref", "ref_" + variant)
         with tempfile.TemporaryDirectory() as tmp:
             out = os.path.join(tmp, "dump.bin")
             args = [exe] + [str(v) for v in (nx, ny, nz, pml, tfsf, steps, use_pml, use_tfsf)] + [DX, WAVELENGTH, str(th), str(ph), str(ps), out]
-            subprocess.run(args, check=True, stdout=subprocess.DEVNULL)
+            if save_res:
+                args.append("1")
+            subprocess.run(args, check=True, stdout=subprocess.DEVNULL, cwd=tmp)
             rec = read_records(out)
         meta = dict(variant=variant, size=[nx, ny, nz], pml=pml, tfsf=tfsf, steps=steps, use_pml=use_pml,
-                    use_tfsf=use_tfsf, theta=th, phi=ph, psi=ps, dx=float(DX), wavelength=float(WAVELENGTH))
+                    use_tfsf=use_tfsf, theta=th, phi=ph, psi=ps, dx=float(DX), wavelength=float(WAVELENGTH),
+                    save_res=int(save_res))
         sc = rec.pop("scalars")
         meta.update(dt=float(sc[0]), rel_phase_velocity=float(sc[3]), source_frequency=float(sc[2]),
                     angle_teta=float(sc[4]), angle_phi=float(sc[5]), angle_psi=float(sc[6]))

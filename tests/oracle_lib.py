@@ -31,6 +31,7 @@ def lib():
         _lib.oracle_init_sigma.argtypes = [C.POINTER(capi.Config), C.c_int, C.c_void_p]
         _lib.oracle_init_eps_sphere.argtypes = [C.POINTER(capi.Config), C.c_void_p] + [C.c_double] * 5
         _lib.oracle_run.argtypes = [C.POINTER(capi.Config), C.POINTER(capi.HostArrays), C.c_int64, C.c_int]
+        _lib.oracle_run_scattered.argtypes = [C.POINTER(capi.Config), C.POINTER(capi.HostArrays), C.c_int64, C.c_int]
     return _lib
 
 
@@ -121,7 +122,7 @@ def reference_setup(cfg):
     return inputs
 
 
-def run(cfg, nsteps, inputs=None, fields=None, nthreads=0):
+def run(cfg, nsteps, inputs=None, fields=None, nthreads=0, scattered=False):
     """Runs the oracle.  `inputs`: dict with Eps, Mu, SigmaX/Y/Z; `fields`: dict of initial fields
     (missing ones start at zero).  Returns dict of all fields (+EInc/HInc) after nsteps."""
     inputs = inputs or {}
@@ -150,7 +151,8 @@ def run(cfg, nsteps, inputs=None, fields=None, nthreads=0):
             a = np.ascontiguousarray(fields.get(key, np.zeros(inc_len(cfg), field_dtype(cfg))), dtype=field_dtype(cfg)).copy()
             out[key] = a
             setattr(arr, attr, a.ctypes.data)
-    rc = lib().oracle_run(C.byref(cfg), C.byref(arr), nsteps, nthreads)
+    fn = lib().oracle_run_scattered if scattered else lib().oracle_run
+    rc = fn(C.byref(cfg), C.byref(arr), nsteps, nthreads)
     if rc != 0:
         raise RuntimeError("oracle_run failed: %d" % rc)
     return out

@@ -23,7 +23,7 @@ def _declared_functions():
 
 def test_library_exports_every_declared_symbol():
     names = _declared_functions()
-    assert len(names) >= 19
+    assert len(names) >= 24
     L = F.lib()
     for n in names:
         assert hasattr(L, n), n

@@ -49,3 +49,40 @@ def test_cli_run_matches_reference_dump(name, tmp_path):
             assert np.array_equal(out[key], data[key]), (key, errs[key])
         else:
             assert errs[key] <= 1e-5, (key, errs)
+
+
+def test_cli_save_res_writes_the_scattered_field(tmp_path):
+    """--save-res: like Scheme3D::performNSteps, subtract the incident field inside the TF/SF box, then save the grids
+    under the reference's names (3D-in-time-Ex ...), as DAT instead of BMP."""
+    meta, data = G.load("3d_d_pml_tfsf_saveres")
+    n = meta["size"]
+    argv = ["--3d", "--sizex", str(n[0]), "--sizey", str(n[1]), "--sizez", str(n[2]), "--pml-sizex", str(meta["pml"]), "--same-size-pml",
+            "--tfsf-sizex", str(meta["tfsf"]), "--same-size-tfsf", "--time-steps", str(meta["steps"]), "--angle-teta", str(meta["theta"]),
+            "--angle-phi", str(meta["phi"]), "--angle-psi", str(meta["psi"]), "--use-pml", "--use-tfsf", "--exact", "--save-res",
+            "--dump-dat", str(tmp_path)]
+    r = subprocess.run([EXE] + argv, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout
+    for key in ("Ex", "Ey", "Ez", "Hx", "Hy", "Hz"):
+        got = np.fromfile(str(tmp_path / ("current[%d]_rank-0_3D-in-time-%s.dat" % (meta["steps"], key))), dtype=np.float64)
+        assert np.array_equal(got, data[key]), key
+
+
+@pytest.mark.parametrize("dims", [3, 2])
+def test_cli_checkpoint_and_resume(dims, tmp_path):
+    """--dump-dat after 14 steps, --load-dat/--start-step for 9 more == 23 steps in one go, bit for bit (fields,
+    auxiliary fields and the incident lines are all part of the checkpoint)."""
+    base = (["--3d", "--sizex", "26", "--sizey", "22", "--sizez", "24"] if dims == 3 else ["--2d", "--sizex", "90", "--sizey", "40"]) + \
+        ["--pml-sizex", "4", "--same-size-pml", "--tfsf-sizex", "6", "--same-size-tfsf", "--use-pml", "--use-tfsf", "--exact"]
+    a, b, c = tmp_path / "a", tmp_path / "b", tmp_path / "c"
+    for d in (a, b, c):
+        d.mkdir()
+    for argv in (["--time-steps", "23", "--dump-dat", str(a)],
+                 ["--time-steps", "14", "--dump-dat", str(b)],
+                 ["--time-steps", "9", "--load-dat", str(b), "--start-step", "14", "--dump-dat", str(c)]):
+        r = subprocess.run([EXE] + base + argv, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout
+    names = sorted(f for f in os.listdir(a))
+    assert len(names) == (14 if dims == 3 else 8) and all(f.startswith("current[23]_rank-0_") for f in names)
+    for f in names:
+        x, y = np.fromfile(str(a / f), dtype=np.uint8), np.fromfile(str(c / f), dtype=np.uint8)
+        assert x.size > 0 and np.array_equal(x, y), f

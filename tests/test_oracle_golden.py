@@ -31,7 +31,7 @@ def test_oracle_matches_reference_dump(name):
             assert np.array_equal(mine[key], data[key]), key
     # the reference fills the sigma grids even when PML is off; they are simply unused then
 
-    out = O.run(cfg, meta["steps"], G.inputs_from_golden(cfg, data))
+    out = O.run(cfg, meta["steps"], G.inputs_from_golden(cfg, data), scattered=bool(meta.get("save_res")))
     for key in O.field_names(cfg) + (["EInc", "HInc"] if cfg.use_tfsf else []):
         assert out[key].dtype == data[key].dtype, key
         assert np.array_equal(out[key], data[key]), "%s differs: max |d| = %g" % (key, np.abs(out[key] - data[key]).max())
