@@ -253,3 +253,24 @@ def test_save_res_scattered_field_matches_reference_dump():
                 assert np.array_equal(out[key], data[key]), (key, errs[key])
             else:
                 assert errs[key] <= TOL[8], (key, errs)
+
+
+@pytest.mark.parametrize("vt,cplx", [(8, False), (8, True), (4, False)])
+def test_thousand_steps_stay_within_the_north_star_tolerance(vt, cplx):
+    """BASELINE.json quotes 1000-step runs: after 1000 steps fast mode (FMA + reciprocal tables) is still within
+    1e-12 (double) / 1e-5 (float) of the reference arithmetic, and exact mode is still bit-for-bit in double."""
+    n = 56 if cplx else 64
+    cfg_args = dict(size=(n, n, n), pml=8, tfsf=14, use_pml=True, use_tfsf=True, value_type=vt, complex_values=cplx,
+                    theta=65, phi=25, psi=40)
+    cfg = O.make_config(exact_mode=0, **cfg_args)
+    inputs = O.reference_setup(cfg)
+    ref = O.run(cfg, 1000, inputs)
+    out = run_gpu(cfg, 1000, inputs)
+    errs = family_rel_errs(out, ref, _keys(cfg))
+    assert max(errs.values()) <= TOL[vt], errs
+    assert np.abs(ref["Ez"]).max() > 0.1  # the wave has filled the total-field region
+    if vt == 8:
+        cfg_x = O.make_config(exact_mode=1, **cfg_args)
+        out_x = run_gpu(cfg_x, 1000, inputs)
+        for key in _keys(cfg):
+            assert np.array_equal(out_x[key], ref[key]), key
