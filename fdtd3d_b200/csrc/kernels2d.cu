@@ -242,7 +242,9 @@ __device__ __forceinline__ T tmz_first (bool plain, bool hx_form, T old, T ez1, 
 {
   if (EXACT && sizeof (T) == 4 && NC == 1)
   {
-    const double curl = hx_form ? (0.0 - 0.0 - (double) ez1 + (double) ez2) : ((double) ez1 - (double) ez2 - 0.0 + 0.0);
+    /* Hx: ((0.0 - 0.0) - Ez1) + Ez2 is double throughout; Hy: Ez1 - Ez2 is a float subtraction (rounded to float)
+     * before the double zeros promote it */
+    const double curl = hx_form ? (0.0 - 0.0 - (double) ez1 + (double) ez2) : ((double) (ez1 - ez2) - 0.0 + 0.0);
     const double lhs = plain ? 1.0 * (double) old : (double) (ca * old);
     return (T) (lhs + (double) cb * curl);
   }
