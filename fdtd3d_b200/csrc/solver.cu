@@ -668,7 +668,7 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   CREATE_TRY (cudaMalloc ((void **) &s->red_out, sizeof (double)));
 #undef CREATE_TRY
 
-  /* kernel selection and z-chunk per CTA: enough CTAs to fill 148 SMs twice, at most 64 planes each */
+  /* kernel selection and z-chunk per CTA */
   s->use_tma = false;
   s->kchunk = 16;
   if (is3)
@@ -676,9 +676,14 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
     const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
     s->use_tma = !(sel && strcmp (sel, "direct") == 0);
     const int txc = s->use_tma ? 32 * (16 / s->cell) : 32 * (16 / s->cell);
-    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + 7) / 8); /* approximate: 8-row tiles */
-    long long zsplit = (2 * 148 + tiles - 1) / tiles;
-    int kc = (int) (s->nzl / (zsplit > 0 ? zsplit : 1));
+    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + 7) / 8); /* 8-row tiles */
+    /* planes marched per CTA: measured best (profiles/r1_kchunk_sweep.log) when a launch has about 8192 CTAs
+     * (~55 per SM) -- short enough marches to keep the SMs evenly loaded to the end, long enough to amortise the
+     * pipeline fill; never more than 64 planes, and small grids still get at least two CTAs per SM */
+    long long kc_ll = (long long) s->nzl * tiles / 8192;
+    const long long kc_small = (long long) s->nzl * tiles / (2 * 148);
+    if (kc_ll > kc_small) kc_ll = kc_small;
+    int kc = (int) kc_ll;
     if (kc > 64) kc = 64;
     if (kc < 4) kc = 4;
     s->kchunk = kc;
@@ -693,6 +698,12 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
         return FDTD_ERROR;
       }
     }
+  }
+
+  if (const char *kc_env = getenv ("FDTD3D_B200_KCHUNK")) /* tuning aid: planes (3D) / rows (2D) marched per CTA */
+  {
+    const int kc = atoi (kc_env);
+    if (kc > 0) s->kchunk = kc;
   }
 
   *out = s;
