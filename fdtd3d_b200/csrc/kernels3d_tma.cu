@@ -41,10 +41,10 @@ namespace
 
 using namespace k3d;
 
-/* tuning knobs: rows per CTA tile, ring depth (0 = as many as fit in 200 KB, at most 4), CTAs per SM the
- * register allocator must allow */
+/* tuning knobs: rows per CTA tile (0 = by value type, see Tile), ring depth (0 = as many as fit in 200 KB, at
+ * most 4), CTAs per SM the register allocator must allow */
 #ifndef FDTD_TMA_TY
-#define FDTD_TMA_TY 8
+#define FDTD_TMA_TY 0
 #endif
 #ifndef FDTD_TMA_STAGES
 #define FDTD_TMA_STAGES 0
@@ -52,8 +52,6 @@ using namespace k3d;
 #ifndef FDTD_TMA_MINB
 #define FDTD_TMA_MINB 1
 #endif
-constexpr int TY = FDTD_TMA_TY;
-constexpr int NTHREADS = 32 * TY;
 constexpr int N_MAPS = 10;
 
 struct TmaSet
@@ -66,6 +64,15 @@ __host__ __device__ constexpr int align128 (int x) { return (x + 127) & ~127; }
 template <typename T, int NC, bool PML>
 struct Tile
 {
+  /*
+   * Rows per tile = warps per CTA.  Real float packs four cells into a thread's 16 bytes, i.e. twice the arithmetic
+   * per byte of the other types, and with 8 warps per SM its kernels are bound by instruction latency (0.88 of the
+   * HBM peak); 16 rows x 2 stages (same shared memory, 512 threads at <= 128 registers) gives 0.98
+   * (profiles/r1_tma_variants_float.log).  Double and complex types are at the roofline with 8 rows x 4 stages and
+   * would spill at 128 registers (profiles/r1_tma_variants.log).
+   */
+  static constexpr int TY = FDTD_TMA_TY > 0 ? FDTD_TMA_TY : ((sizeof (T) == 4 && NC == 1) ? 16 : 8);
+  static constexpr int NTHREADS = 32 * TY;
   static constexpr int CELL = NC * (int) sizeof (T);
   static constexpr int V = 16 / CELL;                 /* cells per thread = x halo cells */
   static constexpr int TXC = 32 * V;                  /* tile cells along x */
@@ -89,7 +96,7 @@ struct Tile
   static constexpr int OFF_M = OFF_OWN + N_OWN * align128 (SZ_OWN);
   static constexpr int STAGE = OFF_M + align128 (SZ_M);
   static constexpr int TX_BYTES = SZ_A + SZ_B + SZ_C + N_OWN * SZ_OWN + SZ_M;
-  static constexpr int STAGES = FDTD_TMA_STAGES > 0 ? FDTD_TMA_STAGES : ((4 * STAGE <= 200 * 1024) ? 4 : ((3 * STAGE <= 200 * 1024) ? 3 : 2));
+  static constexpr int STAGES = FDTD_TMA_STAGES > 0 ? FDTD_TMA_STAGES : ((4 * STAGE <= 200 * 1024) ? 4 : ((3 * STAGE <= 225 * 1024) ? 3 : 2));
   static constexpr int SMEM = STAGES * STAGE + 128;
 };
 
@@ -139,7 +146,7 @@ __device__ __forceinline__ Vec<T, W> lds (const unsigned char *p)
 /* ------------------------------------------------------------------ E half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
-__global__ void __launch_bounds__ (NTHREADS, FDTD_TMA_MINB)
+__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), FDTD_TMA_MINB)
 e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   typedef Tile<T, NC, PML> L;
@@ -153,7 +160,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
   const int tx = threadIdx.x, ty = threadIdx.y;
   const bool leader = tx == 0 && ty == 0;
-  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * TY;
+  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * L::TY;
   const int i0 = i0t + tx * V, j = j0t + ty;
   const bool active = i0 < p.nx && j < p.ny;
   const int k0 = kb + blockIdx.z * p.kchunk;
@@ -388,7 +395,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 /* ------------------------------------------------------------------ H half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
-__global__ void __launch_bounds__ (NTHREADS, FDTD_TMA_MINB)
+__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), FDTD_TMA_MINB)
 h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   typedef Tile<T, NC, PML> L;
@@ -402,7 +409,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
   const int tx = threadIdx.x, ty = threadIdx.y;
   const bool leader = tx == 0 && ty == 0;
-  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * TY;
+  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * L::TY;
   const int i0 = i0t + tx * V, j = j0t + ty;
   const bool active = i0 < p.nx && j < p.ny;
   const int k0 = kb + blockIdx.z * p.kchunk;
@@ -639,9 +646,14 @@ cudaError_t launch_t (bool e_phase, const StepParams<T> &p, const TmaSet &maps, 
 {
   typedef Tile<T, NC, PML> L;
   if (ke <= kb) return cudaSuccess;
-  dim3 block (32, TY);
-  dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + TY - 1) / TY, (ke - kb + p.kchunk - 1) / p.kchunk);
-  static bool attr_e = false, attr_h = false;
+  dim3 block (32, L::TY);
+  dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + L::TY - 1) / L::TY, (ke - kb + p.kchunk - 1) / p.kchunk);
+  /* the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute */
+  static bool attr_e_dev[64] = {}, attr_h_dev[64] = {};
+  int dev = 0;
+  cudaError_t de = cudaGetDevice (&dev);
+  if (de != cudaSuccess) return de;
+  bool &attr_e = attr_e_dev[dev & 63], &attr_h = attr_h_dev[dev & 63];
   if (e_phase)
   {
     if (!attr_e)
@@ -738,19 +750,19 @@ bool prepare_t (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu
   const int bxh = (L::TXC + L::V) * NC, bx = L::TXC * NC, bxm = L::TXC + L::HM;
   bool ok = true;
   /* E phase: Hz (A), Hy (B), Hx (C), Ex Ey Ez Dx Dy Dz, eps */
-  ok = ok && encode (&e->m[0], f[5], sb, xs, ny, planes, bxh, TY + 1, err);
-  ok = ok && encode (&e->m[1], f[4], sb, xs, ny, planes, bxh, TY, err);
-  ok = ok && encode (&e->m[2], f[3], sb, xs, ny, planes, bx, TY + 1, err);
-  for (int a = 0; a < 3 && ok; ++a) ok = encode (&e->m[3 + a], f[0 + a], sb, xs, ny, planes, bx, TY, err);
-  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&e->m[6 + a], f[6 + a], sb, xs, ny, planes, bx, TY, err);
-  ok = ok && encode (&e->m[9], eps, sb, pitchM, ny + 1, planesM, bxm, TY + 1, err);
+  ok = ok && encode (&e->m[0], f[5], sb, xs, ny, planes, bxh, L::TY + 1, err);
+  ok = ok && encode (&e->m[1], f[4], sb, xs, ny, planes, bxh, L::TY, err);
+  ok = ok && encode (&e->m[2], f[3], sb, xs, ny, planes, bx, L::TY + 1, err);
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&e->m[3 + a], f[0 + a], sb, xs, ny, planes, bx, L::TY, err);
+  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&e->m[6 + a], f[6 + a], sb, xs, ny, planes, bx, L::TY, err);
+  ok = ok && encode (&e->m[9], eps, sb, pitchM, ny + 1, planesM, bxm, L::TY + 1, err);
   /* H phase: Ez (A), Ey (B), Ex (C), Hx Hy Hz Bx By Bz, mu */
-  ok = ok && encode (&h->m[0], f[2], sb, xs, ny, planes, bxh, TY + 1, err);
-  ok = ok && encode (&h->m[1], f[1], sb, xs, ny, planes, bxh, TY, err);
-  ok = ok && encode (&h->m[2], f[0], sb, xs, ny, planes, bx, TY + 1, err);
-  for (int a = 0; a < 3 && ok; ++a) ok = encode (&h->m[3 + a], f[3 + a], sb, xs, ny, planes, bx, TY, err);
-  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&h->m[6 + a], f[9 + a], sb, xs, ny, planes, bx, TY, err);
-  ok = ok && encode (&h->m[9], mu, sb, pitchM, ny + 1, planesM, bxm, TY + 1, err);
+  ok = ok && encode (&h->m[0], f[2], sb, xs, ny, planes, bxh, L::TY + 1, err);
+  ok = ok && encode (&h->m[1], f[1], sb, xs, ny, planes, bxh, L::TY, err);
+  ok = ok && encode (&h->m[2], f[0], sb, xs, ny, planes, bx, L::TY + 1, err);
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&h->m[3 + a], f[3 + a], sb, xs, ny, planes, bx, L::TY, err);
+  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&h->m[6 + a], f[9 + a], sb, xs, ny, planes, bx, L::TY, err);
+  ok = ok && encode (&h->m[9], mu, sb, pitchM, ny + 1, planesM, bxm, L::TY + 1, err);
   out->valid = ok;
   return ok;
 }

@@ -543,7 +543,8 @@ static int validate (const fdtd_config *c)
   if (c->value_type != 4 && c->value_type != 8) return fail (FDTD_INVALID_ARGUMENT, "value_type must be 4 (float) or 8 (double); long double has no device type");
   for (int a = 0; a < c->dims; ++a)
   {
-    if (c->size[a] < 2 || c->size[a] > (1 << 20)) return fail (FDTD_INVALID_ARGUMENT, "size[%d] = %lld out of range", a, (long long) c->size[a]);
+    /* 65535: rows and planes index CUDA grid dimensions y / z in the layout-conversion and init kernels */
+    if (c->size[a] < 2 || c->size[a] > 65534) return fail (FDTD_INVALID_ARGUMENT, "size[%d] = %lld outside [2, 65534]", a, (long long) c->size[a]);
     if (c->use_tfsf && (c->tfsf_size[a] < 1 || 2 * c->tfsf_size[a] >= c->size[a]))
       return fail (FDTD_INVALID_ARGUMENT, "tfsf_size[%d] = %lld does not leave a total-field region", a, (long long) c->tfsf_size[a]);
     if (!c->use_tfsf && (c->source_pos[a] < 0 || c->source_pos[a] >= c->size[a]))
@@ -676,7 +677,8 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
     const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
     s->use_tma = !(sel && strcmp (sel, "direct") == 0);
     const int txc = s->use_tma ? 32 * (16 / s->cell) : 32 * (16 / s->cell);
-    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + 7) / 8); /* 8-row tiles */
+    const int tyr = (s->use_tma && s->fp == 4 && s->nc == 1) ? 16 : 8; /* rows per CTA tile, see Tile in kernels3d_tma.cu */
+    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + tyr - 1) / tyr);
     /* planes marched per CTA: measured best (profiles/r1_kchunk_sweep.log) when a launch has about 8192 CTAs
      * (~55 per SM) -- short enough marches to keep the SMs evenly loaded to the end, long enough to amortise the
      * pipeline fill; never more than 64 planes, and small grids still get at least two CTAs per SM */
