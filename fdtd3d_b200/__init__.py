@@ -217,6 +217,15 @@ class Solver:
         _check(lib().fdtd_get_time_step(self._h, C.byref(n)))
         return n.value
 
+    @property
+    def core_box(self):
+        """((lo_x, lo_y, lo_z), (hi_x, hi_y, hi_z)) of the cells advanced without D/B, or None (fdtd_get_core_box)."""
+        lo, hi = (C.c_int64 * 3)(), (C.c_int64 * 3)()
+        _check(lib().fdtd_get_core_box(self._h, lo, hi))
+        if any(lo[a] > hi[a] for a in range(3)):
+            return None
+        return tuple(lo), tuple(hi)
+
     def sumsq(self, field):
         fid = FIELD_IDS[field] if isinstance(field, str) else field
         out = C.c_double()

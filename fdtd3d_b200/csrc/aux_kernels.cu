@@ -178,6 +178,97 @@ __global__ void scattered_kernel (const __grid_constant__ StepParams<T> p, int c
   }
 }
 
+/* ------------------------------------------------------------------ TF/SF face tables */
+
+/*
+ * Incident values of every TF/SF face cell for one half step (layout: kernels3d_common.cuh, tfsf_curl_tab), so that
+ * the half-step kernels apply a correction with one load.  One thread per in-face position (u, v) of one of the
+ * twelve tables of the phase; the face boxes are those of tfsf_e_faces / tfsf_h_faces and the sample is the
+ * incident_sample call of tfsf_curl (Scheme3D::calculate{Ex..Hz}TFSF), bit for bit.
+ */
+template <typename T, int NC, bool IS_E>
+__global__ void face_tables_kernel (const __grid_constant__ StepParams<T> p)
+{
+  const int t = blockIdx.z, side = t & 1, pass = (t >> 1) & 1, a = t >> 2;
+  const int b = (a + 1) % 3, c = (a + 2) % 3;
+  const int n = pass == 0 ? b : c;  /* face normal */
+  const int fc = pass == 0 ? c : b; /* corrected component of the other family = the remaining in-face axis */
+  const int ua = n == 0 ? 1 : 0, va = n == 2 ? 1 : 2;
+  const int ext[3] = { p.nx, p.ny, p.nzl };
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= ext[ua]) return;
+  const bool low = side == 0;
+  int pos[3];
+  pos[n] = low ? p.L[n] - 1 : (IS_E ? p.R[n] : p.R[n] - 1);
+  if (n == 2 && (pos[2] < p.kz0 || pos[2] >= p.kz0 + p.nzl)) return; /* that face plane belongs to another rank */
+  const int kl_face = pos[2] - p.kz0;
+  for (int v = blockIdx.y; v < ext[va]; v += gridDim.y)
+  {
+    pos[ua] = u;
+    pos[va] = va == 2 ? p.kz0 + v : v;
+    /* own axis and remaining axis of the face box */
+    const int own_lo = IS_E ? p.L[a] - 1 : p.L[a], own_hi = p.R[a] - 1;
+    const int rem_lo = IS_E ? p.L[fc] : p.L[fc] - 1, rem_hi = p.R[fc] - 1;
+    if (pos[a] < own_lo || pos[a] > own_hi || pos[fc] < rem_lo || pos[fc] > rem_hi) continue;
+    int sp[3] = { pos[0], pos[1], pos[2] };
+    if (!low) sp[n] += IS_E ? -1 : 1;
+    T off[3];
+    for (int ax = 0; ax < 3; ++ax) off[ax] = IS_E ? (ax == fc ? (T) 0.5 : (T) 1) : (ax == fc ? (T) 1 : (T) 0.5);
+    T inc[NC];
+    incident_sample<T, NC> (p, IS_E ? p.hinc : p.einc, IS_E ? (T) 0.5 : (T) 0, IS_E ? p.proj_h[fc] : p.proj_e[fc],
+                            sp[0], sp[1], sp[2], off[0], off[1], off[2], inc);
+    const long long idx = (long long) v * ext[ua] + u;
+    (void) kl_face;
+#pragma unroll
+    for (int cc = 0; cc < NC; ++cc) p.face_tab[(((IS_E ? 0 : 12) + t) * p.face_stride + idx) * NC + cc] = inc[cc];
+  }
+}
+
+/* ------------------------------------------------------------------ sigma-free core: D/B <-> offsets */
+
+/*
+ * Where sigma = 0 the UPML recurrences (Kernels.h:13-29, 80-96 with Ca = 1) keep D - eps eps0 E (B - mu mu0 H)
+ * constant in time, so the CORE variants of the half-step kernels never touch D/B there.  Between runs the core
+ * cells of the D/B arrays hold that constant: fold (sign -1) stores D - m E before a run, unfold (sign +1) turns it
+ * back into D = const + m E with the E of that moment.  m is the averaged material of YeeGridLayout.h:1005-1263 as
+ * the half-step kernels form it.  The point-source cell of Dz is not folded (its Ez is overwritten every step).
+ */
+template <typename T, int NC>
+__global__ void fold_aux_kernel (const __grid_constant__ StepParams<T> p, T sign, bool skip_source)
+{
+  const int i = p.core_lo[0] + blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = p.core_lo[1] + blockIdx.y;
+  if (i > p.core_hi[0] || j > p.core_hi[1]) return;
+  const T two = (T) 2;
+  for (int gk = p.core_lo[2] + blockIdx.z; gk <= p.core_hi[2]; gk += gridDim.z)
+  {
+    const int kl = gk - p.kz0;
+    if (kl < 0 || kl >= p.nzl) continue;
+    const long long om = ((long long) (kl + 1) * (p.ny + 1) + j) * p.pitchM + i;
+    const long long rowM = p.pitchM, plM = p.psM;
+    const T e000 = p.eps[om], e100 = p.eps[om + 1], e010 = p.eps[om + rowM], e001 = p.eps[om + plM];
+    const T m000 = p.mu[om], m100 = p.mu[om + 1], m010 = p.mu[om + rowM], m001 = p.mu[om + plM];
+    const T m110 = p.mu[om + rowM + 1], m101 = p.mu[om + plM + 1], m011 = p.mu[om + plM + rowM];
+    T mod[6];
+    mod[0] = ((e000 + e100) / two) * p.eps0;
+    mod[1] = ((e000 + e010) / two) * p.eps0;
+    mod[2] = ((e000 + e001) / two) * p.eps0;
+    mod[3] = (((m000 + m001) / two + (m010 + m011) / two) / two) * p.mu0;
+    mod[4] = (((m000 + m001) / two + (m100 + m101) / two) / two) * p.mu0;
+    mod[5] = (((m000 + m010) / two + (m100 + m110) / two) / two) * p.mu0;
+    const long long o = (((long long) (kl + 1) * p.ny + j) * p.pitch + i) * NC;
+    const bool src_cell = skip_source && i == p.srcpos[0] && j == p.srcpos[1] && gk == p.srcpos[2];
+#pragma unroll
+    for (int comp = 0; comp < 6; ++comp)
+    {
+      if (comp == 2 && src_cell) continue;
+      const T m = sign * mod[comp];
+#pragma unroll
+      for (int c = 0; c < NC; ++c) p.f[6 + comp][o + c] = fma_t<T> (m, p.f[comp][o + c], p.f[6 + comp][o + c]);
+    }
+  }
+}
+
 /* ------------------------------------------------------------------ reduction */
 
 constexpr int SUMSQ_CTAS = 1184; /* 148 SMs x 8 */
@@ -284,6 +375,42 @@ cudaError_t launch_scattered (const StepParams<T> &p, bool cplx, int comp, cudaS
 }
 template cudaError_t launch_scattered<float> (const StepParams<float> &, bool, int, cudaStream_t);
 template cudaError_t launch_scattered<double> (const StepParams<double> &, bool, int, cudaStream_t);
+
+template <typename T>
+cudaError_t launch_face_tables (bool e_phase, const StepParams<T> &p, bool cplx, cudaStream_t stream)
+{
+  const int umax = p.nx > p.ny ? p.nx : p.ny, vmax = p.ny > p.nzl ? p.ny : p.nzl;
+  dim3 block (128);
+  dim3 grid ((umax + 127) / 128, vmax < 4096 ? vmax : 4096, 12);
+  if (e_phase)
+  {
+    if (cplx) face_tables_kernel<T, 2, true><<<grid, block, 0, stream>>> (p);
+    else face_tables_kernel<T, 1, true><<<grid, block, 0, stream>>> (p);
+  }
+  else
+  {
+    if (cplx) face_tables_kernel<T, 2, false><<<grid, block, 0, stream>>> (p);
+    else face_tables_kernel<T, 1, false><<<grid, block, 0, stream>>> (p);
+  }
+  return cudaGetLastError ();
+}
+template cudaError_t launch_face_tables<float> (bool, const StepParams<float> &, bool, cudaStream_t);
+template cudaError_t launch_face_tables<double> (bool, const StepParams<double> &, bool, cudaStream_t);
+
+template <typename T>
+cudaError_t launch_fold_aux (const StepParams<T> &p, bool cplx, bool tfsf, bool fold, cudaStream_t stream)
+{
+  if (p.core_lo[0] > p.core_hi[0] || p.core_lo[1] > p.core_hi[1] || p.core_lo[2] > p.core_hi[2]) return cudaSuccess;
+  const int cx = p.core_hi[0] - p.core_lo[0] + 1, cy = p.core_hi[1] - p.core_lo[1] + 1, cz = p.core_hi[2] - p.core_lo[2] + 1;
+  dim3 block (128);
+  dim3 grid ((cx + 127) / 128, cy, cz < 64 ? cz : 64);
+  const T sign = fold ? (T) -1 : (T) 1;
+  if (cplx) fold_aux_kernel<T, 2><<<grid, block, 0, stream>>> (p, sign, !tfsf);
+  else fold_aux_kernel<T, 1><<<grid, block, 0, stream>>> (p, sign, !tfsf);
+  return cudaGetLastError ();
+}
+template cudaError_t launch_fold_aux<float> (const StepParams<float> &, bool, bool, bool, cudaStream_t);
+template cudaError_t launch_fold_aux<double> (const StepParams<double> &, bool, bool, bool, cudaStream_t);
 
 cudaError_t launch_tick (long long *step, cudaStream_t stream)
 {

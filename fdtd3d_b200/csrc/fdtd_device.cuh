@@ -48,6 +48,8 @@ struct StepParams
   const T *eps, *mu;
   CoefTab<T> tab[3][2]; /* [axis][kind] */
   T *einc, *hinc;       /* 1-D incident line, cells */
+  T *face_tab;          /* TF/SF incident values of the face cells, 24 tables (kernels3d_common.cuh, tfsf_curl_tab) */
+  long long face_stride; /* cells per table */
   const T *src;         /* source samples for the steps of the current run, one cell per step */
   long long *step;      /* device step counter: index into src of the step being computed */
   long long ninc;       /* cells in einc / hinc */
@@ -60,6 +62,7 @@ struct StepParams
   long long ps, psM;    /* plane strides (cells / values) */
   int kchunk;           /* planes marched by one CTA */
 
+  int core_lo[3], core_hi[3]; /* sigma-free core (global cells, inclusive; empty if lo > hi), see kernels3d_tma.cu */
   int L[3], R[3];       /* TF/SF box: leftBorderTotalField, rightBorderTotalField */
   int srcpos[3];        /* point source cell (global) */
 

@@ -189,6 +189,48 @@ __device__ __noinline__ T tfsf_curl (const StepParams<T> &p, int a, int faces, i
   return P1 - P2 - Q1 + Q2;
 }
 
+/*
+ * The same correction with the incident values read from the per-step face tables (aux_kernels.cu,
+ * face_tables_kernel): table ((a * 2 + pass) * 2 + side) of the phase, `pass` 0 = faces normal to b, 1 = normal to c,
+ * side 0 = low, 1 = high, holds out[comp] of the incident_sample call tfsf_curl makes for that face cell, indexed by
+ * the two in-face coordinates (normal z: j * nx + i; normal y: kl * nx + i; normal x: kl * ny + j; kl = local plane).
+ * Same operations in the same order as tfsf_curl, so the results are the same bits -- but a face cell costs a load
+ * and two additions instead of ~300 instructions, which matters because every warp that crosses an x face has a
+ * lane on it in every plane (34 % of all instructions of the 512^3 run were spent there, profiles/r1_core_*).
+ */
+template <typename T, int NC, bool IS_E>
+__device__ __forceinline__ T tfsf_curl_tab (const StepParams<T> &p, int a, int faces, int comp, int i, int j, int kl,
+                                            T P1, T P2, T Q1, T Q2)
+{
+  const int b = (a + 1) % 3, c = (a + 2) % 3;
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass)
+  {
+    const int bits = pass == 0 ? (faces & 3) : ((faces >> 2) & 3);
+    if (!bits) continue;
+    const bool low = (bits & 1) != 0;
+    const int n = pass == 0 ? b : c;
+    const long long idx = n == 2 ? (long long) j * p.nx + i : (n == 1 ? (long long) kl * p.nx + i : (long long) kl * p.ny + j);
+    const int t = (IS_E ? 0 : 12) + (a * 2 + pass) * 2 + (low ? 0 : 1);
+    const T *src = p.face_tab + (t * p.face_stride + idx) * NC + comp;
+    const T d = __ldg (src);
+    /* the same lane needs the next plane's entry one plane later: have it in L1 by then */
+    if (n != 2 && kl + 1 < p.nzl)
+      asm volatile ("prefetch.global.L1 [%0];" ::"l"(src + (long long) (n == 1 ? p.nx : p.ny) * NC));
+    if (IS_E)
+    {
+      if (pass == 0) { if (low) P1 -= d; else P2 -= d; }
+      else { if (low) Q1 -= d; else Q2 -= d; }
+    }
+    else
+    {
+      if (pass == 0) { if (low) Q2 += d; else Q1 += d; }
+      else { if (low) P2 += d; else P1 += d; }
+    }
+  }
+  return P1 - P2 - Q1 + Q2;
+}
+
 } /* namespace k3d */
 } /* namespace fdtd */
 

@@ -24,6 +24,13 @@
  *   H phase stage for plane k:  Ex  TXC x 9 of plane k+1              Ey  (TXC+V) x 8 of plane k+1
  *                               Ez  (TXC+V) x 9 of plane k            B*, H*  TXC x 8
  *                               mu  (TXC+HM) x 9 of material plane k+1
+ *
+ * CORE variants (fast mode with UPML): where all three sigma are zero -- everything but the absorbing shell -- the
+ * D/B recurrences collapse to E += (dt/dx) / (eps eps0) * curl, so those cells neither read nor write D/B
+ * (DESIGN.md "sigma-free core"): 18 instead of 30 field values per cell-update.  The decision is made per plane
+ * and per quarter of a tile row (8 lanes = 128 bytes): D/B travel as quarter-width boxes and only the quarters
+ * that touch the shell are requested; the solver keeps D - eps eps0 E of the core cells in the D arrays between
+ * runs (fold / unfold kernels in aux_kernels.cu), so D/B downloads are unaffected.
  */
 #include <cuda.h>
 
@@ -52,7 +59,14 @@ using namespace k3d;
 #ifndef FDTD_TMA_MINB
 #define FDTD_TMA_MINB 1
 #endif
-constexpr int N_MAPS = 10;
+/* the same two for the CORE variants (0 = by tile height, see Tile) */
+#ifndef FDTD_TMA_CORE_STAGES
+#define FDTD_TMA_CORE_STAGES 0
+#endif
+#ifndef FDTD_TMA_CORE_MINB
+#define FDTD_TMA_CORE_MINB 0
+#endif
+constexpr int N_MAPS = 13; /* 10 full boxes + 3 quarter-width boxes of D / B (CORE variants) */
 
 struct TmaSet
 {
@@ -96,8 +110,20 @@ struct Tile
   static constexpr int OFF_M = OFF_OWN + N_OWN * align128 (SZ_OWN);
   static constexpr int STAGE = OFF_M + align128 (SZ_M);
   static constexpr int TX_BYTES = SZ_A + SZ_B + SZ_C + N_OWN * SZ_OWN + SZ_M;
+  /* CORE variants: D / B staged as four quarter-width boxes (8 lanes x 16 bytes = 128-byte rows) per array */
+  static constexpr int QX = 8 * V;                    /* cells per quarter row */
+  static constexpr int SZ_Q = 128 * TY;
+  static constexpr int TX_BASE = SZ_A + SZ_B + SZ_C + 3 * SZ_OWN + SZ_M;
   static constexpr int STAGES = FDTD_TMA_STAGES > 0 ? FDTD_TMA_STAGES : ((4 * STAGE <= 200 * 1024) ? 4 : ((3 * STAGE <= 225 * 1024) ? 3 : 2));
   static constexpr int SMEM = STAGES * STAGE + 128;
+  /*
+   * CORE variants move a third fewer bytes per plane with the same per-plane latency chain, so 8 warps per SM no
+   * longer cover it: 8-row tiles run two CTAs per SM with a 2-deep ring each (measured: 29.0 -> 31.4 Gcell/s on
+   * 512^3 double although the 128-register cap costs ~100 bytes of spills; profiles/r1_core_variants.log).
+   */
+  static constexpr int CORE_MINB = FDTD_TMA_CORE_MINB > 0 ? FDTD_TMA_CORE_MINB : (TY == 8 ? 2 : FDTD_TMA_MINB);
+  static constexpr int CORE_STAGES = FDTD_TMA_CORE_STAGES > 0 ? FDTD_TMA_CORE_STAGES : (TY == 8 ? 2 : STAGES);
+  static constexpr int CORE_SMEM = CORE_STAGES * STAGE + 128;
 };
 
 /* ------------------------------------------------------------------ PTX wrappers */
@@ -143,14 +169,37 @@ __device__ __forceinline__ Vec<T, W> lds (const unsigned char *p)
   return r;
 }
 
+/*
+ * CORE variants: which quarters (8 lanes) of a tile row need their D / B values.  `full`: every quarter that holds
+ * grid cells (planes outside the z core, tiles outside the y core); `core`: in planes of the z core, the quarters
+ * that are not entirely inside the x-y core.  p.core_lo/hi are aligned to quarters (x) and tile rows (y) by the
+ * solver, which folds exactly the cells skipped here.
+ */
+template <typename L, typename T>
+__device__ __forceinline__ void quarter_masks (const StepParams<T> &p, int i0t, int j0t, int &full, int &core)
+{
+  const bool y_core = j0t >= p.core_lo[1] && j0t + L::TY - 1 <= p.core_hi[1];
+  full = 0;
+  core = 0;
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+  {
+    const int qa = i0t + q * L::QX, qb = qa + L::QX - 1;
+    if (qa >= p.nx) continue;
+    full |= 1 << q;
+    if (!(y_core && qa >= p.core_lo[0] && qb <= p.core_hi[0])) core |= 1 << q;
+  }
+}
+
 /* ------------------------------------------------------------------ E half step */
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
-__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), FDTD_TMA_MINB)
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
+__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), (CORE ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
 e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
+  static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
   typedef Tile<T, NC, PML> L;
-  constexpr int V = L::V, W = V * NC, S = L::STAGES;
+  constexpr int V = L::V, W = V * NC, S = CORE ? L::CORE_STAGES : L::STAGES;
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
@@ -167,18 +216,39 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   const int k1 = min (k0 + p.kchunk, ke);
   if (k0 >= k1) return; /* uniform over the CTA */
 
-  /* maps: 0 Hz (A), 1 Hy (B), 2 Hx (C), 3..8 Ex Ey Ez [Dx Dy Dz], 9 eps (M) */
+  /* CORE: quarters of the tile row whose D values are needed -- all that hold cells in planes outside the z core
+   * or in tiles outside the y core, else only those that stick out of the x core */
+  int qmask_full = 0, qmask_core = 0;
+  if (CORE) quarter_masks<L> (p, i0t, j0t, qmask_full, qmask_core);
+  auto d_mask = [&] (int k) -> int
+  {
+    const int g = p.kz0 + k;
+    return (g >= p.core_lo[2] && g <= p.core_hi[2]) ? qmask_core : qmask_full;
+  };
+
+  /* maps: 0 Hz (A), 1 Hy (B), 2 Hx (C), 3..8 Ex Ey Ez [Dx Dy Dz], 9 eps (M), 10..12 Dx Dy Dz as quarter boxes */
   auto issue = [&] (int slot, int k)
   {
     unsigned char *base = smem + slot * L::STAGE;
     unsigned long long *bar = &full[slot];
-    mbar_expect_tx (bar, L::TX_BYTES);
+    const int m = CORE ? d_mask (k) : 0;
+    mbar_expect_tx (bar, CORE ? L::TX_BASE + __popc (m) * 3 * L::SZ_Q : L::TX_BYTES);
     tma_load_3d (base + L::OFF_A, &maps.m[0], bar, (i0t - V) * NC, j0t - 1, k + 1);
     tma_load_3d (base + L::OFF_B, &maps.m[1], bar, (i0t - V) * NC, j0t, k + 1);
     tma_load_3d (base + L::OFF_C, &maps.m[2], bar, i0t * NC, j0t - 1, k + 1);
 #pragma unroll
-    for (int a = 0; a < L::N_OWN; ++a)
+    for (int a = 0; a < (CORE ? 3 : L::N_OWN); ++a)
       tma_load_3d (base + L::OFF_OWN + a * L::OWN_STRIDE, &maps.m[3 + a], bar, i0t * NC, j0t, k + 1);
+    if (CORE)
+    {
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if ((m >> q) & 1)
+            tma_load_3d (base + L::OFF_OWN + (3 + a) * L::OWN_STRIDE + q * L::SZ_Q, &maps.m[10 + a], bar,
+                         (i0t + q * L::QX) * NC, j0t, k + 1);
+    }
     tma_load_3d (base + L::OFF_M, &maps.m[9], bar, i0t, j0t, k + 2);
   };
 
@@ -242,6 +312,8 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   const unsigned char *sC_own = smem + L::OFF_C + (ty + 1) * L::ROW + xo;        /* Hx[j]   */
   const unsigned char *sC_jm = smem + L::OFF_C + ty * L::ROW + xo;               /* Hx[j-1] */
   const unsigned char *sOwn = smem + L::OFF_OWN + ty * L::ROW + xo;
+  /* D tiles: one full-width box, or (CORE) four quarter boxes with 128-byte rows */
+  const unsigned char *sAux = CORE ? smem + L::OFF_OWN + (tx >> 3) * L::SZ_Q + ty * 128 + (tx & 7) * 16 : sOwn;
   const unsigned char *sM = smem + L::OFF_M + ty * L::ROW_M + tx * V * (int) sizeof (T);
 
   for (int k = k0; k < k1; ++k, o += pl)
@@ -254,6 +326,8 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
     const int gk = p.kz0 + k;
     const bool klo = gk >= 1, khi = gk < p.nzg - 1;
     const bool jk_face = j_face || (TFSF && tfsf_axis_hit (p, 2, gk, true));
+    /* false: this thread's cells are in the sigma-free core in this plane */
+    const bool shell = !CORE || ((d_mask (k) >> (tx >> 3)) & 1);
 
     const FVec hz = lds<T, W> (sA_own + so), hz_jm = lds<T, W> (sA_jm + so);
     const FVec hy = lds<T, W> (sB_own + so);
@@ -269,11 +343,11 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
     FVec ey = lds<T, W> (sOwn + so + 1 * L::OWN_STRIDE);
     FVec ez = lds<T, W> (sOwn + so + 2 * L::OWN_STRIDE);
     FVec dx, dy, dz;
-    if (PML)
+    if (PML && shell)
     {
-      dx = lds<T, W> (sOwn + so + 3 * L::OWN_STRIDE);
-      dy = lds<T, W> (sOwn + so + 4 * L::OWN_STRIDE);
-      dz = lds<T, W> (sOwn + so + 5 * L::OWN_STRIDE);
+      dx = lds<T, W> (sAux + so + 3 * L::OWN_STRIDE);
+      dy = lds<T, W> (sAux + so + 4 * L::OWN_STRIDE);
+      dz = lds<T, W> (sAux + so + 5 * L::OWN_STRIDE);
     }
     const MVec eps_kp = lds<T, V> (sM + so);
     const MVec eps_jp_next = lds<T, V> (sM + so + L::ROW_M);
@@ -323,9 +397,9 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
               const int s = v * NC + c;
               const T hz_m = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
               const T hy_m = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
-              if (fx) cex[c] = tfsf_curl<T, NC, true> (p, 0, fx, c, i, j, gk, hz.v[s], hz_jm.v[s], hy.v[s], hy_km.v[s]);
-              if (fy) cey[c] = tfsf_curl<T, NC, true> (p, 1, fy, c, i, j, gk, hx.v[s], hx_km.v[s], hz.v[s], hz_m);
-              if (fz) cez[c] = tfsf_curl<T, NC, true> (p, 2, fz, c, i, j, gk, hy.v[s], hy_m, hx.v[s], hx_jm.v[s]);
+              if (fx) cex[c] = tfsf_curl_tab<T, NC, true> (p, 0, fx, c, i, j, k, hz.v[s], hz_jm.v[s], hy.v[s], hy_km.v[s]);
+              if (fy) cey[c] = tfsf_curl_tab<T, NC, true> (p, 1, fy, c, i, j, k, hx.v[s], hx_km.v[s], hz.v[s], hz_m);
+              if (fz) cez[c] = tfsf_curl_tab<T, NC, true> (p, 2, fz, c, i, j, k, hy.v[s], hy_m, hx.v[s], hx_jm.v[s]);
             }
           }
         }
@@ -336,7 +410,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
         const T mod_y = ((e_c + eps_jp.v[v]) / (T) 2) * p.eps0;
         const T mod_z = ((e_c + eps_kp.v[v]) / (T) 2) * p.eps0;
 
-        if (PML)
+        if (PML && shell)
         {
           T cbx, ccx, cby, ccy, cbz, ccz;
           sweep3_coefs<T, EXACT> (p_x_btw.v[v], m_x_btw.v[v], q_z_at, mod_x, cbx, ccx);
@@ -370,6 +444,13 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
         {
           if (gk == p.srcpos[2] && j == p.srcpos[1] && i == p.srcpos[0])
           {
+            /* the source overwrites Ez but not Dz (Scheme3D.cpp:1995-2024): in the core this one cell keeps its
+             * true Dz in memory (the fold kernels skip it) and advances it here, Dz += Cb curl with Ca = 1 */
+            if (CORE && !shell && do_ez)
+            {
+#pragma unroll
+              for (int c = 0; c < NC; ++c) Dz[o + v * NC + c] = fma_t<T> (cbd_x_at.v[v], cez[c], Dz[o + v * NC + c]);
+            }
 #pragma unroll
             for (int c = 0; c < NC; ++c) ez.v[v * NC + c] = p.src[step * NC + c];
           }
@@ -377,7 +458,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
       }
 
       stv<T, W> (Ex + o, ex); stv<T, W> (Ey + o, ey); stv<T, W> (Ez + o, ez);
-      if (PML)
+      if (PML && shell)
       {
         stv<T, W> (Dx + o, dx); stv<T, W> (Dy + o, dy); stv<T, W> (Dz + o, dz);
       }
@@ -394,12 +475,13 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
 /* ------------------------------------------------------------------ H half step */
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
-__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), FDTD_TMA_MINB)
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
+__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), (CORE ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
 h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
+  static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
   typedef Tile<T, NC, PML> L;
-  constexpr int V = L::V, W = V * NC, S = L::STAGES;
+  constexpr int V = L::V, W = V * NC, S = CORE ? L::CORE_STAGES : L::STAGES;
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
@@ -416,19 +498,38 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   const int k1 = min (k0 + p.kchunk, ke);
   if (k0 >= k1) return;
 
+  int qmask_full = 0, qmask_core = 0; /* see e_phase_3d_tma */
+  if (CORE) quarter_masks<L> (p, i0t, j0t, qmask_full, qmask_core);
+  auto d_mask = [&] (int k) -> int
+  {
+    const int g = p.kz0 + k;
+    return (g >= p.core_lo[2] && g <= p.core_hi[2]) ? qmask_core : qmask_full;
+  };
+
   /* maps: 0 Ez (A: x+y halo, plane k), 1 Ey (B: x halo, plane k+1), 2 Ex (C: y halo, plane k+1),
-   *       3..8 Hx Hy Hz [Bx By Bz], 9 mu (M, material plane k+1) */
+   *       3..8 Hx Hy Hz [Bx By Bz], 9 mu (M, material plane k+1), 10..12 Bx By Bz as quarter boxes */
   auto issue = [&] (int slot, int k)
   {
     unsigned char *base = smem + slot * L::STAGE;
     unsigned long long *bar = &full[slot];
-    mbar_expect_tx (bar, L::TX_BYTES);
+    const int m = CORE ? d_mask (k) : 0;
+    mbar_expect_tx (bar, CORE ? L::TX_BASE + __popc (m) * 3 * L::SZ_Q : L::TX_BYTES);
     tma_load_3d (base + L::OFF_A, &maps.m[0], bar, i0t * NC, j0t, k + 1);
     tma_load_3d (base + L::OFF_B, &maps.m[1], bar, i0t * NC, j0t, k + 2);
     tma_load_3d (base + L::OFF_C, &maps.m[2], bar, i0t * NC, j0t, k + 2);
 #pragma unroll
-    for (int a = 0; a < L::N_OWN; ++a)
+    for (int a = 0; a < (CORE ? 3 : L::N_OWN); ++a)
       tma_load_3d (base + L::OFF_OWN + a * L::OWN_STRIDE, &maps.m[3 + a], bar, i0t * NC, j0t, k + 1);
+    if (CORE)
+    {
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if ((m >> q) & 1)
+            tma_load_3d (base + L::OFF_OWN + (3 + a) * L::OWN_STRIDE + q * L::SZ_Q, &maps.m[10 + a], bar,
+                         (i0t + q * L::QX) * NC, j0t, k + 1);
+    }
     tma_load_3d (base + L::OFF_M, &maps.m[9], bar, i0t, j0t, k + 2);
   };
 
@@ -494,6 +595,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   const unsigned char *sC_own = smem + L::OFF_C + ty * L::ROW + xo;         /* Ex[k+1]    */
   const unsigned char *sC_jp = smem + L::OFF_C + (ty + 1) * L::ROW + xo;    /* Ex[k+1][j+1] */
   const unsigned char *sOwn = smem + L::OFF_OWN + ty * L::ROW + xo;
+  const unsigned char *sAux = CORE ? smem + L::OFF_OWN + (tx >> 3) * L::SZ_Q + ty * 128 + (tx & 7) * 16 : sOwn;
   const unsigned char *sM = smem + L::OFF_M + ty * L::ROW_M + tx * V * (int) sizeof (T);
 
   for (int k = k0; k < k1; ++k, o += pl)
@@ -506,6 +608,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
     const int gk = p.kz0 + k;
     const bool klo = gk >= 1, khi = gk < p.nzg - 1;
     const bool jk_face = j_face || (TFSF && tfsf_axis_hit (p, 2, gk, false));
+    const bool shell = !CORE || ((d_mask (k) >> (tx >> 3)) & 1);
 
     const FVec ez = lds<T, W> (sA_own + so), ez_jp = lds<T, W> (sA_jp + so);
     const FVec ey_kp = lds<T, W> (sB_own + so);
@@ -521,11 +624,11 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
     FVec hy = lds<T, W> (sOwn + so + 1 * L::OWN_STRIDE);
     FVec hz = lds<T, W> (sOwn + so + 2 * L::OWN_STRIDE);
     FVec bx, by, bz;
-    if (PML)
+    if (PML && shell)
     {
-      bx = lds<T, W> (sOwn + so + 3 * L::OWN_STRIDE);
-      by = lds<T, W> (sOwn + so + 4 * L::OWN_STRIDE);
-      bz = lds<T, W> (sOwn + so + 5 * L::OWN_STRIDE);
+      bx = lds<T, W> (sAux + so + 3 * L::OWN_STRIDE);
+      by = lds<T, W> (sAux + so + 4 * L::OWN_STRIDE);
+      bz = lds<T, W> (sAux + so + 5 * L::OWN_STRIDE);
     }
     const MVec mu_kp = lds<T, V> (sM + so), mu_jp_kp = lds<T, V> (sM + so + L::ROW_M);
     const T mu_ip_kp = *reinterpret_cast<const T *> (sM + so + V * sizeof (T));
@@ -575,9 +678,9 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
               const int s = v * NC + c;
               const T ez_p = v + 1 < V ? ez.v[v + 1 < V ? s + NC : s] : ez_ip[c];
               const T ey_p = v + 1 < V ? ey.v[v + 1 < V ? s + NC : s] : ey_ip[c];
-              if (fx) chx[c] = tfsf_curl<T, NC, false> (p, 0, fx, c, i, j, gk, ey_kp.v[s], ey.v[s], ez_jp.v[s], ez.v[s]);
-              if (fy) chy[c] = tfsf_curl<T, NC, false> (p, 1, fy, c, i, j, gk, ez_p, ez.v[s], ex_kp.v[s], ex.v[s]);
-              if (fz) chz[c] = tfsf_curl<T, NC, false> (p, 2, fz, c, i, j, gk, ex_jp.v[s], ex.v[s], ey_p, ey.v[s]);
+              if (fx) chx[c] = tfsf_curl_tab<T, NC, false> (p, 0, fx, c, i, j, k, ey_kp.v[s], ey.v[s], ez_jp.v[s], ez.v[s]);
+              if (fy) chy[c] = tfsf_curl_tab<T, NC, false> (p, 1, fy, c, i, j, k, ez_p, ez.v[s], ex_kp.v[s], ex.v[s]);
+              if (fz) chz[c] = tfsf_curl_tab<T, NC, false> (p, 2, fz, c, i, j, k, ex_jp.v[s], ex.v[s], ey_p, ey.v[s]);
             }
           }
         }
@@ -591,7 +694,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
         const T mod_y = (((m000 + m001) / two + (m100 + m101) / two) / two) * p.mu0;
         const T mod_z = (((m000 + m010) / two + (m100 + m110) / two) / two) * p.mu0;
 
-        if (PML)
+        if (PML && shell)
         {
           T cbx, ccx, cby, ccy, cbz, ccz;
           sweep3_coefs<T, EXACT> (p_x_at.v[v], m_x_at.v[v], q_z_btw, mod_x, cbx, ccx);
@@ -623,7 +726,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
       }
 
       stv<T, W> (Hx + o, hx); stv<T, W> (Hy + o, hy); stv<T, W> (Hz + o, hz);
-      if (PML)
+      if (PML && shell)
       {
         stv<T, W> (Bx + o, bx); stv<T, W> (By + o, by); stv<T, W> (Bz + o, bz);
       }
@@ -641,11 +744,12 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
 /* ------------------------------------------------------------------ dispatch */
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE = false>
 cudaError_t launch_t (bool e_phase, const StepParams<T> &p, const TmaSet &maps, int kb, int ke, cudaStream_t stream)
 {
   typedef Tile<T, NC, PML> L;
   if (ke <= kb) return cudaSuccess;
+  constexpr int smem = CORE ? L::CORE_SMEM : L::SMEM;
   dim3 block (32, L::TY);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + L::TY - 1) / L::TY, (ke - kb + p.kchunk - 1) / p.kchunk);
   /* the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute */
@@ -658,29 +762,32 @@ cudaError_t launch_t (bool e_phase, const StepParams<T> &p, const TmaSet &maps, 
   {
     if (!attr_e)
     {
-      cudaError_t e = cudaFuncSetAttribute (e_phase_3d_tma<T, NC, PML, TFSF, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM);
+      cudaError_t e = cudaFuncSetAttribute (e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
       if (e != cudaSuccess) return e;
       attr_e = true;
     }
-    e_phase_3d_tma<T, NC, PML, TFSF, EXACT><<<grid, block, L::SMEM, stream>>> (p, maps, kb, ke);
+    e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, smem, stream>>> (p, maps, kb, ke);
   }
   else
   {
     if (!attr_h)
     {
-      cudaError_t e = cudaFuncSetAttribute (h_phase_3d_tma<T, NC, PML, TFSF, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM);
+      cudaError_t e = cudaFuncSetAttribute (h_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
       if (e != cudaSuccess) return e;
       attr_h = true;
     }
-    h_phase_3d_tma<T, NC, PML, TFSF, EXACT><<<grid, block, L::SMEM, stream>>> (p, maps, kb, ke);
+    h_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, smem, stream>>> (p, maps, kb, ke);
   }
   return cudaGetLastError ();
 }
 
 template <typename T, int NC>
-cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, const TmaSet &maps, bool pml, bool tfsf, bool exact, int kb,
-                       int ke, cudaStream_t s)
+cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, const TmaSet &maps, bool pml, bool tfsf, bool exact, bool core,
+                       int kb, int ke, cudaStream_t s)
 {
+  if (core && pml && !exact)
+    return tfsf ? launch_t<T, NC, true, true, false, true> (e_phase, p, maps, kb, ke, s)
+                : launch_t<T, NC, true, false, false, true> (e_phase, p, maps, kb, ke, s);
   const int key = (pml ? 4 : 0) | (tfsf ? 2 : 0) | (exact ? 1 : 0);
   switch (key)
   {
@@ -755,6 +862,7 @@ bool prepare_t (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu
   ok = ok && encode (&e->m[2], f[3], sb, xs, ny, planes, bx, L::TY + 1, err);
   for (int a = 0; a < 3 && ok; ++a) ok = encode (&e->m[3 + a], f[0 + a], sb, xs, ny, planes, bx, L::TY, err);
   for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&e->m[6 + a], f[6 + a], sb, xs, ny, planes, bx, L::TY, err);
+  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&e->m[10 + a], f[6 + a], sb, xs, ny, planes, bx / 4, L::TY, err);
   ok = ok && encode (&e->m[9], eps, sb, pitchM, ny + 1, planesM, bxm, L::TY + 1, err);
   /* H phase: Ez (A), Ey (B), Ex (C), Hx Hy Hz Bx By Bz, mu */
   ok = ok && encode (&h->m[0], f[2], sb, xs, ny, planes, bxh, L::TY + 1, err);
@@ -762,6 +870,7 @@ bool prepare_t (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu
   ok = ok && encode (&h->m[2], f[0], sb, xs, ny, planes, bx, L::TY + 1, err);
   for (int a = 0; a < 3 && ok; ++a) ok = encode (&h->m[3 + a], f[3 + a], sb, xs, ny, planes, bx, L::TY, err);
   for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&h->m[6 + a], f[9 + a], sb, xs, ny, planes, bx, L::TY, err);
+  for (int a = 0; a < 3 && ok && pml; ++a) ok = encode (&h->m[10 + a], f[9 + a], sb, xs, ny, planes, bx / 4, L::TY, err);
   ok = ok && encode (&h->m[9], mu, sb, pitchM, ny + 1, planesM, bxm, L::TY + 1, err);
   out->valid = ok;
   return ok;
@@ -780,16 +889,28 @@ bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, void *con
                  : prepare_t<double, 1> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
 }
 
-template <typename T>
-cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
-                                 bool exact, int kb, int ke, cudaStream_t stream)
+void tma_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *quarter_cells_x)
 {
-  const TmaSet &set = *reinterpret_cast<const TmaSet *> (e_phase ? maps.e : maps.h);
-  if (cplx) return launch_nc<T, 2> (e_phase, p, set, pml, tfsf, exact, kb, ke, stream);
-  return launch_nc<T, 1> (e_phase, p, set, pml, tfsf, exact, kb, ke, stream);
+  int txc, ty, qx;
+  if (value_type == 4 && nc == 1) { typedef Tile<float, 1, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+  else if (value_type == 4) { typedef Tile<float, 2, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+  else if (nc == 1) { typedef Tile<double, 1, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+  else { typedef Tile<double, 2, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+  if (tile_cells_x) *tile_cells_x = txc;
+  if (tile_rows) *tile_rows = ty;
+  if (quarter_cells_x) *quarter_cells_x = qx;
 }
 
-template cudaError_t launch_phase_3d_tma<float> (bool, const StepParams<float> &, const TmaMaps3D &, bool, bool, bool, bool, int, int, cudaStream_t);
-template cudaError_t launch_phase_3d_tma<double> (bool, const StepParams<double> &, const TmaMaps3D &, bool, bool, bool, bool, int, int, cudaStream_t);
+template <typename T>
+cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
+                                 bool exact, bool core, int kb, int ke, cudaStream_t stream)
+{
+  const TmaSet &set = *reinterpret_cast<const TmaSet *> (e_phase ? maps.e : maps.h);
+  if (cplx) return launch_nc<T, 2> (e_phase, p, set, pml, tfsf, exact, core, kb, ke, stream);
+  return launch_nc<T, 1> (e_phase, p, set, pml, tfsf, exact, core, kb, ke, stream);
+}
+
+template cudaError_t launch_phase_3d_tma<float> (bool, const StepParams<float> &, const TmaMaps3D &, bool, bool, bool, bool, bool, int, int, cudaStream_t);
+template cudaError_t launch_phase_3d_tma<double> (bool, const StepParams<double> &, const TmaMaps3D &, bool, bool, bool, bool, bool, int, int, cudaStream_t);
 
 } /* namespace fdtd */

@@ -17,19 +17,27 @@ template <typename T>
 cudaError_t launch_phase_3d (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact,
                              int kb, int ke, cudaStream_t stream);
 
-/* TMA-staged 3D half steps (kernels3d_tma.cu).  TmaMaps3D holds the CUtensorMap descriptors (10 per phase,
- * 128 bytes each) of one solver's arrays; tma_prepare_3d encodes them once the arrays are allocated. */
+/* TMA-staged 3D half steps (kernels3d_tma.cu).  TmaMaps3D holds the CUtensorMap descriptors (13 per phase,
+ * 128 bytes each) of one solver's arrays; tma_prepare_3d encodes them once the arrays are allocated.
+ * `core` selects the variants that skip D / B inside the box p.core_lo .. p.core_hi (fast mode with UPML only);
+ * tma_tile_geometry gives the tile shape that box has to be aligned to. */
 struct TmaMaps3D
 {
-  alignas (64) unsigned char e[10 * 128];
-  alignas (64) unsigned char h[10 * 128];
+  alignas (64) unsigned char e[13 * 128];
+  alignas (64) unsigned char h[13 * 128];
   bool valid;
 };
+void tma_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *quarter_cells_x);
 bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, void *const f[12], void *eps, void *mu, int pitch,
                      int ny, int planes, int pitchM, int planesM, std::string *err);
 template <typename T>
 cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
-                                 bool exact, int kb, int ke, cudaStream_t stream);
+                                 bool exact, bool core, int kb, int ke, cudaStream_t stream);
+
+/* D (B) -= / += eps eps0 E (mu mu0 H) over the core box, for the six components (aux_kernels.cu): `fold` before
+ * running the CORE variants, unfold before anything else reads or replaces D / B / E / H / eps / mu */
+template <typename T>
+cudaError_t launch_fold_aux (const StepParams<T> &p, bool cplx, bool tfsf, bool fold, cudaStream_t stream);
 
 /* 2D TMz half steps (kernels2d.cu) */
 template <typename T>
@@ -40,6 +48,12 @@ cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, b
  * Scheme3D::performPlaneWaveESteps / HSteps, Scheme3D.cpp:24-82 */
 template <typename T>
 cudaError_t launch_incident (bool e_phase, const StepParams<T> &p, bool cplx, bool exact, cudaStream_t stream);
+
+/* incident values of all TF/SF face cells of one half step into p.face_tab (24 tables of p.face_stride cells:
+ * kernels3d_common.cuh, tfsf_curl_tab); run after launch_incident of the same half step, before the TMA half-step
+ * kernel */
+template <typename T>
+cudaError_t launch_face_tables (bool e_phase, const StepParams<T> &p, bool cplx, cudaStream_t stream);
 
 /* total -> scattered field inside the TF/SF box for one component (0..2 = Ex..Ez, 3..5 = Hx..Hz), in place:
  * the post-processing of Scheme3D.cpp:2767-2921 */

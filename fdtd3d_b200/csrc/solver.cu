@@ -77,6 +77,8 @@ struct fdtd_solver
   void *f[12];
   void *eps, *mu;
   void *einc, *hinc;
+  void *face_tab;    /* TF/SF face tables of the TMA kernels (24 x face_stride cells) */
+  long long face_stride;
   void *tab_mem;     /* all coefficient tables, one allocation */
   size_t tab_stride; /* bytes between tables */
   void *src;         /* source samples */
@@ -95,6 +97,11 @@ struct fdtd_solver
   TmaMaps3D tma;        /* tensor maps of the TMA-staged 3D kernels */
   bool use_tma;
   int kchunk;
+
+  /* sigma-free core (kernels3d_tma.cu, CORE variants): box of cells whose D/B the time loop skips, and whether the
+   * D/B arrays currently hold the folded representation D - eps eps0 E there (aux_kernels.cu, fold_aux_kernel) */
+  bool core_allowed, core_on, folded;
+  int core_lo[3], core_hi[3];
 
   bool profiling;
   std::vector<cudaEvent_t> prof_ev; /* 4 per step: E begin/end, H begin/end */
@@ -133,6 +140,8 @@ static StepParams<T> make_params (const fdtd_solver *s)
     }
   p.einc = (T *) s->einc;
   p.hinc = (T *) s->hinc;
+  p.face_tab = (T *) s->face_tab;
+  p.face_stride = s->face_stride;
   p.src = (const T *) s->src;
   p.step = s->step;
   p.ninc = s->ninc;
@@ -141,6 +150,8 @@ static StepParams<T> make_params (const fdtd_solver *s)
   p.kchunk = s->kchunk;
   for (int a = 0; a < 3; ++a)
   {
+    p.core_lo[a] = s->core_on ? s->core_lo[a] : 0;
+    p.core_hi[a] = s->core_on ? s->core_hi[a] : -1;
     p.L[a] = (int) c.tfsf_size[a];
     p.R[a] = (int) (c.size[a] - c.tfsf_size[a]);
     p.srcpos[a] = (int) c.source_pos[a];
@@ -286,14 +297,68 @@ static int exchange (fdtd_solver *s, bool h_fields)
   return FDTD_OK;
 }
 
+/* ------------------------------------------------------------------ sigma-free core */
+
+/*
+ * The box of cells where all three sigma profiles vanish at both material samples a component can use along each
+ * axis (sigma[i] and sigma[i+1]): per axis the longest run of zeros of the profile, shrunk in x to whole quarter
+ * tile rows and in y to whole tile rows of the TMA kernels (they decide per quarter row), intersected over the axes.
+ */
+static void update_core (fdtd_solver *s)
+{
+  s->core_on = false;
+  for (int a = 0; a < 3; ++a) { s->core_lo[a] = 0; s->core_hi[a] = -1; }
+  if (!s->core_allowed) return;
+  int txc = 0, ty = 0, qx = 0;
+  tma_tile_geometry (s->fp, s->nc, &txc, &ty, &qx);
+  for (int a = 0; a < 3; ++a)
+  {
+    const std::vector<double> &sg = s->sigma[a];
+    long long best0 = 0, best1 = -1, run0 = 0;
+    for (long long i = 0; i <= (long long) sg.size (); ++i)
+    {
+      const bool zero = i < (long long) sg.size () && sg[(size_t) i] == 0.0;
+      if (!zero)
+      {
+        if (i - 1 - run0 > best1 - best0) { best0 = run0; best1 = i - 1; }
+        run0 = i + 1;
+      }
+    }
+    long long lo = best0, hi = best1 - 1; /* cells whose samples i and i+1 are both in the run */
+    if (a == 0) { lo = round_up (lo, qx); hi = (hi + 1) / qx * qx - 1; }
+    if (a == 1) { lo = round_up (lo, ty); hi = (hi + 1) / ty * ty - 1; }
+    if (hi < lo) return;
+    s->core_lo[a] = (int) lo;
+    s->core_hi[a] = (int) hi;
+  }
+  s->core_on = true;
+}
+
+static int fold_core (fdtd_solver *s, bool fold)
+{
+  const bool cplx = s->cfg.complex_values != 0, tfsf = s->cfg.use_tfsf != 0;
+  if (s->fp == 4) CUDA_TRY (launch_fold_aux<float> (make_params<float> (s), cplx, tfsf, fold, s->s_compute));
+  else CUDA_TRY (launch_fold_aux<double> (make_params<double> (s), cplx, tfsf, fold, s->s_compute));
+  s->launches++;
+  s->folded = fold;
+  return FDTD_OK;
+}
+
+/* before anything but the time loop reads or changes D, B, E, H, eps, mu or sigma (stream-ordered, no sync) */
+static int ensure_unfolded (fdtd_solver *s)
+{
+  if (!s->folded) return FDTD_OK;
+  return fold_core (s, false);
+}
+
 /* ------------------------------------------------------------------ time loop */
 
 template <typename T>
 static cudaError_t phase_3d (fdtd_solver *s, bool e_phase, const StepParams<T> &p, int kb, int ke, cudaStream_t S)
 {
   const fdtd_config &c = s->cfg;
-  const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode != 0;
-  if (s->use_tma) return launch_phase_3d_tma<T> (e_phase, p, s->tma, cplx, pml, tfsf, exact, kb, ke, S);
+  const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode == 1;
+  if (s->use_tma) return launch_phase_3d_tma<T> (e_phase, p, s->tma, cplx, pml, tfsf, exact, s->core_on, kb, ke, S);
   return launch_phase_3d<T> (e_phase, p, cplx, pml, tfsf, exact, kb, ke, S);
 }
 
@@ -302,7 +367,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
 {
   const fdtd_config &c = s->cfg;
   const StepParams<T> p = make_params<T> (s);
-  const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode != 0;
+  const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode == 1;
   const bool multi = c.nranks > 1;
   cudaStream_t S = s->s_compute, C = s->s_comm;
   const bool prof = s->profiling && !multi;
@@ -332,6 +397,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
   {
     /* Scheme3D::performNSteps, Scheme3D.cpp:1986-2069 (SchemeTMz.cpp:1336-1427) */
     if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, exact, S)); s->launches++; }
+    if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (true, p, cplx, S)); s->launches++; }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
     if (c.dims == 2)
     {
@@ -355,6 +421,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
 
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
     if (tfsf) { CUDA_TRY (launch_incident<T> (false, p, cplx, exact, S)); s->launches++; }
+    if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (false, p, cplx, S)); s->launches++; }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
     if (c.dims == 2)
     {
@@ -396,6 +463,7 @@ static int run_async (fdtd_solver *s, long long nsteps)
   if (rc) return rc;
   CUDA_TRY (cudaMemsetAsync (s->step, 0, sizeof (long long), s->s_compute));
   CUDA_TRY (cudaEventRecord (s->ev_start, s->s_compute));
+  if (s->core_on && !s->folded && (rc = fold_core (s, true))) return rc;
   rc = s->fp == 4 ? enqueue_steps<float> (s, nsteps) : enqueue_steps<double> (s, nsteps);
   if (rc) return rc;
   CUDA_TRY (cudaEventRecord (s->ev_stop, s->s_compute));
@@ -474,6 +542,8 @@ static int transfer (fdtd_solver *s, int field, void *host, int order, long long
   FieldInfo fi;
   rc = field_info (s, field, &fi);
   if (rc) return rc;
+  /* uploads of anything the folded representation depends on, and reads of D / B, need the plain arrays */
+  if (!fi.is_inc && (to_device || (field >= FDTD_DX && field <= FDTD_BZ)) && (rc = ensure_unfolded (s))) return rc;
   cudaStream_t S = s->s_compute;
   if (fi.is_inc)
   {
@@ -540,6 +610,7 @@ static int validate (const fdtd_config *c)
   if (!c) return fail (FDTD_INVALID_ARGUMENT, "NULL config");
   if (c->abi_version != FDTD3D_B200_ABI_VERSION) return fail (FDTD_INVALID_ARGUMENT, "abi_version %d, library is %d", c->abi_version, FDTD3D_B200_ABI_VERSION);
   if (c->dims != 2 && c->dims != 3) return fail (FDTD_INVALID_ARGUMENT, "dims must be 2 (TMz) or 3");
+  if (c->exact_mode < 0 || c->exact_mode > 2) return fail (FDTD_INVALID_ARGUMENT, "exact_mode must be 0 (fast), 1 (exact) or 2 (fast, D/B kept everywhere)");
   if (c->value_type != 4 && c->value_type != 8) return fail (FDTD_INVALID_ARGUMENT, "value_type must be 4 (float) or 8 (double); long double has no device type");
   for (int a = 0; a < c->dims; ++a)
   {
@@ -676,8 +747,8 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   {
     const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
     s->use_tma = !(sel && strcmp (sel, "direct") == 0);
-    const int txc = s->use_tma ? 32 * (16 / s->cell) : 32 * (16 / s->cell);
-    const int tyr = (s->use_tma && s->fp == 4 && s->nc == 1) ? 16 : 8; /* rows per CTA tile, see Tile in kernels3d_tma.cu */
+    int txc = 32 * (16 / s->cell), tyr = 8; /* cells per CTA tile row, rows per CTA tile */
+    if (s->use_tma) tma_tile_geometry (s->fp, s->nc, &txc, &tyr, NULL);
     const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + tyr - 1) / tyr);
     /* planes marched per CTA: measured best (profiles/r1_kchunk_sweep.log) when a launch has about 8192 CTAs
      * (~55 per SM) -- short enough marches to keep the SMs evenly loaded to the end, long enough to amortise the
@@ -689,6 +760,21 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
     if (kc > 64) kc = 64;
     if (kc < 4) kc = 4;
     s->kchunk = kc;
+    if (s->use_tma && cfg->use_tfsf)
+    {
+      long long m = (long long) s->nx * s->ny;
+      if ((long long) s->nx * s->nzl > m) m = (long long) s->nx * s->nzl;
+      if ((long long) s->ny * s->nzl > m) m = (long long) s->ny * s->nzl;
+      s->face_stride = m;
+      cudaError_t fe = cudaMalloc (&s->face_tab, (size_t) 24 * m * s->cell);
+      if (fe == cudaSuccess) fe = cudaMemsetAsync (s->face_tab, 0, (size_t) 24 * m * s->cell, s->s_compute);
+      if (fe != cudaSuccess)
+      {
+        fail (FDTD_ERROR, "allocating the TF/SF face tables failed: %s", cudaGetErrorString (fe));
+        fdtd_destroy (s);
+        return FDTD_ERROR;
+      }
+    }
     if (s->use_tma)
     {
       std::string err;
@@ -701,6 +787,12 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
       }
     }
   }
+
+  /* fast mode with UPML on the TMA kernels skips D / B where sigma = 0; exact_mode 2 (or FDTD3D_B200_CORE=0, for
+   * A/B measurements) keeps the reference's formulation everywhere */
+  s->core_allowed = is3 && s->use_tma && cfg->use_pml && cfg->exact_mode == 0;
+  if (const char *ce = getenv ("FDTD3D_B200_CORE")) { if (atoi (ce) == 0) s->core_allowed = false; }
+  update_core (s);
 
   if (const char *kc_env = getenv ("FDTD3D_B200_KCHUNK")) /* tuning aid: planes (3D) / rows (2D) marched per CTA */
   {
@@ -730,7 +822,7 @@ int fdtd_destroy (fdtd_handle s)
     if (nccl) nccl->CommDestroy (s->comm);
   }
   for (int f = 0; f < 12; ++f) if (s->f[f]) cudaFree (s->f[f]);
-  void *ptrs[] = { s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->step, s->staging, s->red_partials, s->red_out };
+  void *ptrs[] = { s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->step, s->staging, s->red_partials, s->red_out };
   for (void *p : ptrs) if (p) cudaFree (p);
   cudaEvent_t evs[] = { s->ev_start, s->ev_stop, s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx };
   for (cudaEvent_t e : evs) if (e) cudaEventDestroy (e);
@@ -749,8 +841,10 @@ int fdtd_set_sigma (fdtd_handle s, int axis, const void *profile, int64_t count)
   CUDA_TRY (cudaSetDevice (s->cfg.device));
   int rc = sync_run (s);
   if (rc) return rc;
+  if ((rc = ensure_unfolded (s))) return rc; /* with the core box of the old profiles */
   for (int64_t i = 0; i < count; ++i)
     s->sigma[axis][(size_t) i] = s->fp == 4 ? (double) ((const float *) profile)[i] : ((const double *) profile)[i];
+  update_core (s);
   return build_tables_any (s);
 }
 
@@ -776,6 +870,7 @@ int fdtd_fill (fdtd_handle s, int field, double re, double im)
   rc = field_info (s, field, &fi);
   if (rc) return rc;
   const bool material = field == FDTD_EPS || field == FDTD_MU;
+  if (!fi.is_inc && (rc = ensure_unfolded (s))) return rc;
   long long count = fi.is_inc ? s->ninc : (material ? s->mat_vals : s->field_cells);
   alignas (16) char pat[16];
   memset (pat, 0, sizeof (pat));
@@ -802,6 +897,7 @@ int fdtd_init_eps_sphere (fdtd_handle s, double cx, double cy, double cz, double
   CUDA_TRY (cudaSetDevice (s->cfg.device));
   int rc = sync_run (s);
   if (rc) return rc;
+  if ((rc = ensure_unfolded (s))) return rc;
   if (s->fp == 4)
     CUDA_TRY (launch_eps_sphere<float> ((float *) s->eps, s->nx + 1, s->ny + 1, s->nzm, s->kz0, s->pitchM, s->psM, (float) cx, (float) cy, (float) cz, (float) radius, (float) eps_inside, s->s_compute));
   else
@@ -818,6 +914,7 @@ int fdtd_subtract_incident (fdtd_handle s)
   CUDA_TRY (cudaSetDevice (s->cfg.device));
   int rc = sync_run (s);
   if (rc) return rc;
+  if ((rc = ensure_unfolded (s))) return rc;
   for (int comp = 0; comp < 6; ++comp)
   {
     if (s->fp == 4) CUDA_TRY (launch_scattered<float> (make_params<float> (s), s->cfg.complex_values != 0, comp, s->s_compute));
@@ -888,6 +985,17 @@ int fdtd_get_time_step (fdtd_handle s, int64_t *t)
   return FDTD_OK;
 }
 
+int fdtd_get_core_box (fdtd_handle s, int64_t lo[3], int64_t hi[3])
+{
+  if (!s || !lo || !hi) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  for (int a = 0; a < 3; ++a)
+  {
+    lo[a] = s->core_on ? s->core_lo[a] : 0;
+    hi[a] = s->core_on ? s->core_hi[a] : -1;
+  }
+  return FDTD_OK;
+}
+
 int fdtd_field_sumsq (fdtd_handle s, int field, double *out)
 {
   if (!s || !out) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
@@ -898,6 +1006,7 @@ int fdtd_field_sumsq (fdtd_handle s, int field, double *out)
   rc = field_info (s, field, &fi);
   if (rc) return rc;
   const bool material = field == FDTD_EPS || field == FDTD_MU;
+  if (field >= FDTD_DX && field <= FDTD_BZ && (rc = ensure_unfolded (s))) return rc;
   const int scal_per_cell = material ? 1 : s->nc;
   cudaStream_t S = s->s_compute;
   if (fi.is_inc)

@@ -76,8 +76,12 @@ typedef struct fdtd_config
   int32_t use_pml;         /* --use-pml  (Scheme3D::usePML)  */
   int32_t use_tfsf;        /* --use-tfsf (Scheme3D::useTFSF); when 0 the point source is active */
   int32_t exact_mode;      /* 1: reference evaluation order, IEEE division per cell, no FMA contraction
-                              (bit-for-bit with the reference CPU solver in double);
-                              0: reciprocal tables + FMA (within the stated tolerance) */
+                              (bit-for-bit with the reference CPU solver in double and real float);
+                              0: reciprocal tables + FMA (within the stated tolerance); in 3D with use_pml the
+                                 cells where all sigma are zero are advanced without their D / B values
+                                 (E += dt/dx / (eps eps0) curl), which the library reconstructs whenever D / B
+                                 are read -- same tolerance, 18 instead of 30 field values of traffic per cell;
+                              2: as 0 but D / B are carried through every cell as the reference does */
   int32_t device;          /* CUDA device ordinal; cudaInit(device) of Source/Cuda/CudaInterface.cu:934 */
 
   int64_t size[3];         /* --sizex/y/z; size[2] must be 1 for dims == 2 */
@@ -182,6 +186,14 @@ int fdtd_launch_count (fdtd_handle h, int64_t *count);
 
 /* Current value of t (number of steps done + time_step_start). */
 int fdtd_get_time_step (fdtd_handle h, int64_t *t);
+
+/*
+ * The box of cells (global indices, inclusive) that the time loop currently advances without their D / B values
+ * (exact_mode 0, dims 3, use_pml: the region where all three sigma profiles are zero, shrunk to the kernels' tile
+ * granularity); lo > hi on some axis when the box is empty or the optimisation is off.  No reference counterpart:
+ * a diagnostic (bench.py reports the fraction of the grid it covers).
+ */
+int fdtd_get_core_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
 
 /* sum over this rank's cells of |cur|^2 of a field, accumulated in double (diagnostic used by the
  * parity tests at sizes where a full download is impractical; the known-answer vectors of

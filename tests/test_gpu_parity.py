@@ -287,3 +287,78 @@ def test_thousand_steps_stay_within_the_north_star_tolerance(vt, cplx):
     out_x = run_gpu(cfg_x, 1000, inputs)
     for key in _keys(cfg):
         assert np.array_equal(out_x[key], ref[key]), key
+
+
+# ----------------------------------------------------------------------------- sigma-free core (fast mode, 3D, UPML)
+
+CORE_CASES = [
+    # size, pml, tfsf, use_tfsf, value_type, complex, steps
+    ((40, 24, 20), 3, 5, False, 8, False, 14),   # point source inside the core: its Dz is advanced explicitly
+    ((70, 26, 18), 3, 6, True, 8, False, 12),    # two tiles along x, TF/SF faces inside the core
+    ((40, 24, 20), 3, 5, True, 8, True, 10),
+    ((140, 40, 18), 4, 6, False, 4, False, 12),  # float: 128-cell tiles, 32-cell quarters, 16-row tiles
+    ((70, 26, 18), 3, 6, True, 4, True, 10),
+]
+
+
+@pytest.mark.parametrize("case", CORE_CASES, ids=lambda c: "%s-t%d-vt%d%s" % ("x".join(map(str, c[0])), c[3], c[4], "c" if c[5] else ""))
+def test_sigma_free_core_matches_oracle_and_full_formulation(case):
+    """exact_mode 0 advances the cells with sigma = 0 without D/B and reconstructs D/B on demand: every field,
+    D and B included, is within the north-star tolerance of the oracle, and of exact_mode 2 (same arithmetic, D/B
+    carried through every cell), also when D/B are read and E is replaced between two runs."""
+    size, pml, tfsf, use_tfsf, vt, cplx, steps = case
+    src = (size[0] // 2, size[1] // 2, size[2] // 2)
+    kw = dict(dims=3, size=size, pml=pml, tfsf=tfsf, use_pml=True, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx,
+              theta=60, phi=30, psi=20, source_pos=src)
+    cfg = O.make_config(exact_mode=0, **kw)
+    inputs, fields = random_inputs(cfg, seed=99)
+    keys = _keys(cfg)
+    with F.Solver(cfg) as s:
+        for a in range(3):
+            s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+        box = s.core_box
+    assert box is not None, "this grid is meant to have a non-empty core"
+    lo, hi = box
+    assert all(lo[a] >= pml and hi[a] <= size[a] - pml - 1 for a in range(3)), box
+    if not use_tfsf:
+        assert all(lo[a] <= src[a] <= hi[a] for a in range(3)), (box, src)
+
+    ref = O.run(cfg, steps, inputs, fields)
+    out = run_gpu(cfg, steps, inputs, fields)
+    full = run_gpu(O.make_config(exact_mode=2, **kw), steps, inputs, fields)
+    for got in (out, full):
+        errs = family_rel_errs(got, ref, keys)
+        assert max(errs.values()) <= TOL[vt], errs
+
+    # read D/B (unfold), replace a field (unfold + refold) between two runs
+    half = steps // 2
+    mid = O.run(cfg, half, inputs, fields)
+    with F.Solver(cfg) as s:
+        for a in range(3):
+            s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+        s.upload("Eps", inputs["Eps"])
+        s.upload("Mu", inputs["Mu"])
+        for name in O.field_names(cfg):
+            s.upload(name, fields[name])
+        s.run(half)
+        got_mid = {k: s.download(k) for k in ("Dx", "Bz", "Ez")}
+        assert abs(s.sumsq("Dy") - float((np.abs(mid["Dy"].astype(np.complex128)) ** 2).sum())) <= 1e-4 * float((np.abs(mid["Dy"]) ** 2).sum())
+        s.upload("Ey", mid["Ey"])  # same values the oracle has at this point, through the upload path
+        s.run(steps - half)
+        again = {k: s.download(k) for k in O.field_names(cfg)}
+    errs = family_rel_errs(got_mid, mid, ["Dx", "Bz", "Ez"])
+    assert max(errs.values()) <= TOL[vt], errs
+    errs = family_rel_errs(again, ref, O.field_names(cfg))
+    assert max(errs.values()) <= TOL[vt], errs
+
+
+def test_sigma_free_core_with_all_zero_sigma():
+    """use_pml with sigma = 0 everywhere: the core is the whole (tile-aligned) grid, border cells included."""
+    cfg = O.make_config(size=(36, 19, 12), pml=3, tfsf=5, use_pml=True, use_tfsf=True, exact_mode=0)
+    inputs, fields = random_inputs(cfg, seed=5)
+    for a in range(3):
+        inputs["Sigma" + "XYZ"[a]] = np.zeros(cfg.size[a] + 1)
+    ref = O.run(cfg, 8, inputs, fields)
+    out = run_gpu(cfg, 8, inputs, fields)
+    errs = family_rel_errs(out, ref, _keys(cfg))
+    assert max(errs.values()) <= TOL[8], errs
