@@ -269,6 +269,33 @@ __global__ void fold_aux_kernel (const __grid_constant__ StepParams<T> p, T sign
   }
 }
 
+/* TMz: Dz <-> eps[i,j] eps0 Ez (single cell, SchemeTMz.cpp:181,326,528-530); Bx <-> (mu[i,j+1] + mu[i,j]) / 2 mu0 Hx
+ * (cpp:606-612); By <-> (mu[i,j] + mu[i+1,j]) / 2 mu0 Hy (cpp:975-981) -- as kernels2d.cu forms them */
+template <typename T, int NC>
+__global__ void fold_aux_tmz_kernel (const __grid_constant__ StepParams<T> p, T sign, bool skip_source)
+{
+  const int i = p.core_lo[0] + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > p.core_hi[0]) return;
+  const T two = (T) 2;
+  for (int j = p.core_lo[1] + blockIdx.y; j <= p.core_hi[1]; j += gridDim.y)
+  {
+    const long long om = p.psM + (long long) j * p.pitchM + i;
+    const T m00 = p.mu[om], m10 = p.mu[om + 1], m01 = p.mu[om + p.pitchM];
+    const T mod_ez = p.eps[om] * p.eps0;
+    const T mod_hx = ((m01 + m00) / two) * p.mu0;
+    const T mod_hy = ((m00 + m10) / two) * p.mu0;
+    const long long o = (p.ps + (long long) j * p.pitch + i) * NC;
+    const bool src_cell = skip_source && i == p.srcpos[0] && j == p.srcpos[1];
+#pragma unroll
+    for (int c = 0; c < NC; ++c)
+    {
+      if (!src_cell) p.f[8][o + c] = fma_t<T> (sign * mod_ez, p.f[2][o + c], p.f[8][o + c]);
+      p.f[9][o + c] = fma_t<T> (sign * mod_hx, p.f[3][o + c], p.f[9][o + c]);
+      p.f[10][o + c] = fma_t<T> (sign * mod_hy, p.f[4][o + c], p.f[10][o + c]);
+    }
+  }
+}
+
 /* ------------------------------------------------------------------ reduction */
 
 constexpr int SUMSQ_CTAS = 1184; /* 148 SMs x 8 */
@@ -398,19 +425,26 @@ template cudaError_t launch_face_tables<float> (bool, const StepParams<float> &,
 template cudaError_t launch_face_tables<double> (bool, const StepParams<double> &, bool, cudaStream_t);
 
 template <typename T>
-cudaError_t launch_fold_aux (const StepParams<T> &p, bool cplx, bool tfsf, bool fold, cudaStream_t stream)
+cudaError_t launch_fold_aux (const StepParams<T> &p, bool tmz, bool cplx, bool tfsf, bool fold, cudaStream_t stream)
 {
   if (p.core_lo[0] > p.core_hi[0] || p.core_lo[1] > p.core_hi[1] || p.core_lo[2] > p.core_hi[2]) return cudaSuccess;
   const int cx = p.core_hi[0] - p.core_lo[0] + 1, cy = p.core_hi[1] - p.core_lo[1] + 1, cz = p.core_hi[2] - p.core_lo[2] + 1;
   dim3 block (128);
-  dim3 grid ((cx + 127) / 128, cy, cz < 64 ? cz : 64);
   const T sign = fold ? (T) -1 : (T) 1;
+  if (tmz)
+  {
+    dim3 grid ((cx + 127) / 128, cy < 16384 ? cy : 16384);
+    if (cplx) fold_aux_tmz_kernel<T, 2><<<grid, block, 0, stream>>> (p, sign, !tfsf);
+    else fold_aux_tmz_kernel<T, 1><<<grid, block, 0, stream>>> (p, sign, !tfsf);
+    return cudaGetLastError ();
+  }
+  dim3 grid ((cx + 127) / 128, cy, cz < 64 ? cz : 64);
   if (cplx) fold_aux_kernel<T, 2><<<grid, block, 0, stream>>> (p, sign, !tfsf);
   else fold_aux_kernel<T, 1><<<grid, block, 0, stream>>> (p, sign, !tfsf);
   return cudaGetLastError ();
 }
-template cudaError_t launch_fold_aux<float> (const StepParams<float> &, bool, bool, bool, cudaStream_t);
-template cudaError_t launch_fold_aux<double> (const StepParams<double> &, bool, bool, bool, cudaStream_t);
+template cudaError_t launch_fold_aux<float> (const StepParams<float> &, bool, bool, bool, bool, cudaStream_t);
+template cudaError_t launch_fold_aux<double> (const StepParams<double> &, bool, bool, bool, bool, cudaStream_t);
 
 cudaError_t launch_tick (long long *step, cudaStream_t stream)
 {

@@ -14,6 +14,10 @@
  *
  * exact mode reproduces the reference's promotions for real float builds: the `0.0` literals of
  * Kernels.h:38-42 and the `1.0` of Kernels.h:45-61 make parts of the expression double.
+ *
+ * CORE variants (fast mode with UPML): vectors whose cells all have sigma_x = sigma_y = 0 neither load nor store
+ * Dz / Bx / By and take the direct update E += (dt/dx) / (eps eps0) curl, as in 3D (kernels3d_tma.cu); the solver
+ * folds / unfolds the D/B arrays of exactly those cells (p.core_lo/hi, x aligned to whole vectors).
  */
 #include "fdtd_device.cuh"
 #include "launch.h"
@@ -72,10 +76,11 @@ __device__ __forceinline__ T plain_coef (T m, const StepParams<T> &p)
 
 /* ------------------------------------------------------------------ Ez half step */
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
 __global__ void __launch_bounds__ (TX)
 ez_phase_tmz (const __grid_constant__ StepParams<T> p)
 {
+  static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
   constexpr int V = 16 / (NC * (int) sizeof (T));
   constexpr int W = V * NC;
   typedef Vec<T, W> FVec;
@@ -107,10 +112,12 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
   FVec hx_jm = ldv<T, W> (Hx + o - row);
   long long step = 0;
   if (!TFSF) step = *p.step;
+  const bool x_core = CORE && i0 >= p.core_lo[0] && i0 + V - 1 <= p.core_hi[0];
 
   for (int j = j0; j < j1; ++j, o += row, om += p.pitchM)
   {
     const bool jlo = j >= 1;
+    const bool shell = !(x_core && j >= p.core_lo[1] && j <= p.core_hi[1]); /* false: no Dz needed for this vector */
     FVec hx = ldv<T, W> (Hx + o), hy = ldv<T, W> (Hy + o);
     T hy_im[NC];
 #pragma unroll
@@ -118,7 +125,7 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
     MVec eps = ldv<T, V> (p.eps + om);
     FVec ez = ldv_rw<T, W> (Ez + o);
     FVec dz;
-    if (PML) dz = ldv_rw<T, W> (Dz + o);
+    if (PML && shell) dz = ldv_rw<T, W> (Dz + o);
 
     T ca_y_at = 0, q_y_at = 0;
     if (PML)
@@ -177,7 +184,7 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
       const T mod = eps.v[v] * p.eps0;
       if (do_ez)
       {
-        if (PML)
+        if (PML && shell)
         {
           T cb3, cc3;
           sweep3_coefs<T, EXACT> (p_z, m_z, q_y_at, mod, cb3, cc3);
@@ -221,6 +228,14 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
       {
         if (j == p.srcpos[1] && i == p.srcpos[0])
         {
+          /* the source overwrites Ez, not Dz (SchemeTMz.cpp:1341-1355): in the core this cell keeps its true Dz in
+           * memory (not folded) and advances it here, Dz += Cb curl with Ca = 1 */
+          if (CORE && !shell && do_ez)
+          {
+#pragma unroll
+            for (int c = 0; c < NC; ++c)
+              Dz[o + v * NC + c] = fma_t<T> (cbd_x_at.v[v], hy1[c] - hy2[c] - hx1[c] + hx2[c], Dz[o + v * NC + c]);
+          }
 #pragma unroll
           for (int c = 0; c < NC; ++c) ez.v[v * NC + c] = p.src[step * NC + c];
         }
@@ -228,7 +243,7 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
     }
 
     stv<T, W> (Ez + o, ez);
-    if (PML) stv<T, W> (Dz + o, dz);
+    if (PML && shell) stv<T, W> (Dz + o, dz);
     hx_jm = hx;
   }
 }
@@ -253,10 +268,11 @@ __device__ __forceinline__ T tmz_first (bool plain, bool hx_form, T old, T ez1, 
   return fma_t<T> (cb, curl, plain ? old : ca * old);
 }
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
 __global__ void __launch_bounds__ (TX)
 h_phase_tmz (const __grid_constant__ StepParams<T> p)
 {
+  static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
   constexpr int V = 16 / (NC * (int) sizeof (T));
   constexpr int W = V * NC;
   typedef Vec<T, W> FVec;
@@ -290,10 +306,12 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
 
   FVec ez = ldv<T, W> (Ez + o);
   MVec mu_c = ldv<T, V> (p.mu + om);
+  const bool x_core = CORE && i0 >= p.core_lo[0] && i0 + V - 1 <= p.core_hi[0];
 
   for (int j = j0; j < j1; ++j, o += row, om += p.pitchM)
   {
     const bool jlo = j >= 1, jhi = j < p.ny - 1;
+    const bool shell = !(x_core && j >= p.core_lo[1] && j <= p.core_hi[1]);
     FVec ez_jp = ldv<T, W> (Ez + o + row);
     T ez_ip[NC];
 #pragma unroll
@@ -303,7 +321,7 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
 
     FVec hx = ldv_rw<T, W> (Hx + o), hy = ldv_rw<T, W> (Hy + o);
     FVec bx, by;
-    if (PML) { bx = ldv_rw<T, W> (Bx + o); by = ldv_rw<T, W> (By + o); }
+    if (PML && shell) { bx = ldv_rw<T, W> (Bx + o); by = ldv_rw<T, W> (By + o); }
 
     T ca_y_btw = 0, cbd_y_btw = 0, p_y_at = 0, m_y_at = 0;
     if (PML)
@@ -356,7 +374,7 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
       const T mod_x = ((mu_jp.v[v] + m00) / (T) 2) * p.mu0;
       const T mod_y = ((m00 + m10) / (T) 2) * p.mu0;
 
-      if (PML)
+      if (PML && shell)
       {
         T cbx, ccx, cby, ccy;
         sweep3_coefs<T, EXACT> (p_x_at.v[v], m_x_at.v[v], q_z, mod_x, cbx, ccx);
@@ -398,26 +416,28 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
     }
 
     stv<T, W> (Hx + o, hx); stv<T, W> (Hy + o, hy);
-    if (PML) { stv<T, W> (Bx + o, bx); stv<T, W> (By + o, by); }
+    if (PML && shell) { stv<T, W> (Bx + o, bx); stv<T, W> (By + o, by); }
     ez = ez_jp;
     mu_c = mu_jp;
   }
 }
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT>
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE = false>
 cudaError_t launch_t (bool e_phase, const StepParams<T> &p, cudaStream_t stream)
 {
   constexpr int V = 16 / (NC * (int) sizeof (T));
   dim3 block (TX);
   dim3 grid ((p.nx + TX * V - 1) / (TX * V), (p.ny + p.kchunk - 1) / p.kchunk);
-  if (e_phase) ez_phase_tmz<T, NC, PML, TFSF, EXACT><<<grid, block, 0, stream>>> (p);
-  else h_phase_tmz<T, NC, PML, TFSF, EXACT><<<grid, block, 0, stream>>> (p);
+  if (e_phase) ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, 0, stream>>> (p);
+  else h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, 0, stream>>> (p);
   return cudaGetLastError ();
 }
 
 template <typename T, int NC>
-cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, bool pml, bool tfsf, bool exact, cudaStream_t s)
+cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, bool pml, bool tfsf, bool exact, bool core, cudaStream_t s)
 {
+  if (core && pml && !exact)
+    return tfsf ? launch_t<T, NC, true, true, false, true> (e_phase, p, s) : launch_t<T, NC, true, false, false, true> (e_phase, p, s);
   const int key = (pml ? 4 : 0) | (tfsf ? 2 : 0) | (exact ? 1 : 0);
   switch (key)
   {
@@ -435,14 +455,14 @@ cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, bool pml, bool tfsf
 } /* namespace */
 
 template <typename T>
-cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact,
+cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact, bool core,
                               cudaStream_t stream)
 {
-  if (cplx) return launch_nc<T, 2> (e_phase, p, pml, tfsf, exact, stream);
-  return launch_nc<T, 1> (e_phase, p, pml, tfsf, exact, stream);
+  if (cplx) return launch_nc<T, 2> (e_phase, p, pml, tfsf, exact, core, stream);
+  return launch_nc<T, 1> (e_phase, p, pml, tfsf, exact, core, stream);
 }
 
-template cudaError_t launch_phase_tmz<float> (bool, const StepParams<float> &, bool, bool, bool, bool, cudaStream_t);
-template cudaError_t launch_phase_tmz<double> (bool, const StepParams<double> &, bool, bool, bool, bool, cudaStream_t);
+template cudaError_t launch_phase_tmz<float> (bool, const StepParams<float> &, bool, bool, bool, bool, bool, cudaStream_t);
+template cudaError_t launch_phase_tmz<double> (bool, const StepParams<double> &, bool, bool, bool, bool, bool, cudaStream_t);
 
 } /* namespace fdtd */

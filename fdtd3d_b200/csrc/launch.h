@@ -37,11 +37,11 @@ cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const Tma
 /* D (B) -= / += eps eps0 E (mu mu0 H) over the core box, for the six components (aux_kernels.cu): `fold` before
  * running the CORE variants, unfold before anything else reads or replaces D / B / E / H / eps / mu */
 template <typename T>
-cudaError_t launch_fold_aux (const StepParams<T> &p, bool cplx, bool tfsf, bool fold, cudaStream_t stream);
+cudaError_t launch_fold_aux (const StepParams<T> &p, bool tmz, bool cplx, bool tfsf, bool fold, cudaStream_t stream);
 
 /* 2D TMz half steps (kernels2d.cu) */
 template <typename T>
-cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact,
+cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact, bool core,
                               cudaStream_t stream);
 
 /* 1-D incident line: E update + source sample at cell 0, H update (aux_kernels.cu);

@@ -310,7 +310,8 @@ static void update_core (fdtd_solver *s)
   for (int a = 0; a < 3; ++a) { s->core_lo[a] = 0; s->core_hi[a] = -1; }
   if (!s->core_allowed) return;
   int txc = 0, ty = 0, qx = 0;
-  tma_tile_geometry (s->fp, s->nc, &txc, &ty, &qx);
+  if (s->cfg.dims == 3) tma_tile_geometry (s->fp, s->nc, &txc, &ty, &qx);
+  else { qx = 16 / s->cell; ty = 1; } /* TMz kernels decide per 16-byte vector and per row (kernels2d.cu) */
   for (int a = 0; a < 3; ++a)
   {
     const std::vector<double> &sg = s->sigma[a];
@@ -337,8 +338,9 @@ static void update_core (fdtd_solver *s)
 static int fold_core (fdtd_solver *s, bool fold)
 {
   const bool cplx = s->cfg.complex_values != 0, tfsf = s->cfg.use_tfsf != 0;
-  if (s->fp == 4) CUDA_TRY (launch_fold_aux<float> (make_params<float> (s), cplx, tfsf, fold, s->s_compute));
-  else CUDA_TRY (launch_fold_aux<double> (make_params<double> (s), cplx, tfsf, fold, s->s_compute));
+  const bool tmz = s->cfg.dims == 2;
+  if (s->fp == 4) CUDA_TRY (launch_fold_aux<float> (make_params<float> (s), tmz, cplx, tfsf, fold, s->s_compute));
+  else CUDA_TRY (launch_fold_aux<double> (make_params<double> (s), tmz, cplx, tfsf, fold, s->s_compute));
   s->launches++;
   s->folded = fold;
   return FDTD_OK;
@@ -401,7 +403,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
     if (c.dims == 2)
     {
-      CUDA_TRY (launch_phase_tmz<T> (true, p, cplx, pml, tfsf, exact, S)); s->launches++;
+      CUDA_TRY (launch_phase_tmz<T> (true, p, cplx, pml, tfsf, exact, s->core_on, S)); s->launches++;
     }
     else if (!multi)
     {
@@ -425,7 +427,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
     if (c.dims == 2)
     {
-      CUDA_TRY (launch_phase_tmz<T> (false, p, cplx, pml, tfsf, exact, S)); s->launches++;
+      CUDA_TRY (launch_phase_tmz<T> (false, p, cplx, pml, tfsf, exact, s->core_on, S)); s->launches++;
     }
     else if (!multi)
     {
@@ -790,7 +792,7 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
 
   /* fast mode with UPML on the TMA kernels skips D / B where sigma = 0; exact_mode 2 (or FDTD3D_B200_CORE=0, for
    * A/B measurements) keeps the reference's formulation everywhere */
-  s->core_allowed = is3 && s->use_tma && cfg->use_pml && cfg->exact_mode == 0;
+  s->core_allowed = (is3 ? s->use_tma : true) && cfg->use_pml && cfg->exact_mode == 0;
   if (const char *ce = getenv ("FDTD3D_B200_CORE")) { if (atoi (ce) == 0) s->core_allowed = false; }
   update_core (s);
 

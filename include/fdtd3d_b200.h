@@ -77,7 +77,7 @@ typedef struct fdtd_config
   int32_t use_tfsf;        /* --use-tfsf (Scheme3D::useTFSF); when 0 the point source is active */
   int32_t exact_mode;      /* 1: reference evaluation order, IEEE division per cell, no FMA contraction
                               (bit-for-bit with the reference CPU solver in double and real float);
-                              0: reciprocal tables + FMA (within the stated tolerance); in 3D with use_pml the
+                              0: reciprocal tables + FMA (within the stated tolerance); with use_pml the
                                  cells where all sigma are zero are advanced without their D / B values
                                  (E += dt/dx / (eps eps0) curl), which the library reconstructs whenever D / B
                                  are read -- same tolerance, 18 instead of 30 field values of traffic per cell;
@@ -189,7 +189,7 @@ int fdtd_get_time_step (fdtd_handle h, int64_t *t);
 
 /*
  * The box of cells (global indices, inclusive) that the time loop currently advances without their D / B values
- * (exact_mode 0, dims 3, use_pml: the region where all three sigma profiles are zero, shrunk to the kernels' tile
+ * (exact_mode 0, use_pml: the region where all three sigma profiles are zero, shrunk to the kernels' tile
  * granularity); lo > hi on some axis when the box is empty or the optimisation is off.  No reference counterpart:
  * a diagnostic (bench.py reports the fraction of the grid it covers).
  */

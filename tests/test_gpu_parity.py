@@ -298,6 +298,9 @@ CORE_CASES = [
     ((40, 24, 20), 3, 5, True, 8, True, 10),
     ((140, 40, 18), 4, 6, False, 4, False, 12),  # float: 128-cell tiles, 32-cell quarters, 16-row tiles
     ((70, 26, 18), 3, 6, True, 4, True, 10),
+    ((90, 40), 5, 8, False, 8, False, 20),       # 2D TMz: per-vector decision, source cell in the core
+    ((131, 47), 6, 9, True, 4, False, 20),
+    ((64, 50), 5, 8, True, 8, True, 16),
 ]
 
 
@@ -307,21 +310,23 @@ def test_sigma_free_core_matches_oracle_and_full_formulation(case):
     D and B included, is within the north-star tolerance of the oracle, and of exact_mode 2 (same arithmetic, D/B
     carried through every cell), also when D/B are read and E is replaced between two runs."""
     size, pml, tfsf, use_tfsf, vt, cplx, steps = case
-    src = (size[0] // 2, size[1] // 2, size[2] // 2)
-    kw = dict(dims=3, size=size, pml=pml, tfsf=tfsf, use_pml=True, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx,
-              theta=60, phi=30, psi=20, source_pos=src)
+    dims = len(size)
+    src = (size[0] // 2, size[1] // 2, size[2] // 2 if dims == 3 else 0)
+    ang = dict(theta=60, phi=30, psi=20) if dims == 3 else dict(theta=90, phi=0, psi=90)  # TMz allows phi = 0 or 45 only
+    kw = dict(dims=dims, size=size, pml=pml, tfsf=tfsf, use_pml=True, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx,
+              source_pos=src, **ang)
     cfg = O.make_config(exact_mode=0, **kw)
     inputs, fields = random_inputs(cfg, seed=99)
     keys = _keys(cfg)
     with F.Solver(cfg) as s:
-        for a in range(3):
+        for a in range(dims):
             s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
         box = s.core_box
     assert box is not None, "this grid is meant to have a non-empty core"
     lo, hi = box
-    assert all(lo[a] >= pml and hi[a] <= size[a] - pml - 1 for a in range(3)), box
+    assert all(lo[a] >= pml and hi[a] <= size[a] - pml - 1 for a in range(dims)), box
     if not use_tfsf:
-        assert all(lo[a] <= src[a] <= hi[a] for a in range(3)), (box, src)
+        assert all(lo[a] <= src[a] <= hi[a] for a in range(dims)), (box, src)
 
     ref = O.run(cfg, steps, inputs, fields)
     out = run_gpu(cfg, steps, inputs, fields)
@@ -333,20 +338,23 @@ def test_sigma_free_core_matches_oracle_and_full_formulation(case):
     # read D/B (unfold), replace a field (unfold + refold) between two runs
     half = steps // 2
     mid = O.run(cfg, half, inputs, fields)
+    probe = ("Dx", "Bz", "Ez") if dims == 3 else ("Dz", "By", "Ez")
+    dsum, eup = ("Dy", "Ey") if dims == 3 else ("Bx", "Hx")
     with F.Solver(cfg) as s:
-        for a in range(3):
+        for a in range(dims):
             s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
         s.upload("Eps", inputs["Eps"])
         s.upload("Mu", inputs["Mu"])
         for name in O.field_names(cfg):
             s.upload(name, fields[name])
         s.run(half)
-        got_mid = {k: s.download(k) for k in ("Dx", "Bz", "Ez")}
-        assert abs(s.sumsq("Dy") - float((np.abs(mid["Dy"].astype(np.complex128)) ** 2).sum())) <= 1e-4 * float((np.abs(mid["Dy"]) ** 2).sum())
-        s.upload("Ey", mid["Ey"])  # same values the oracle has at this point, through the upload path
+        got_mid = {k: s.download(k) for k in probe}
+        want = float((np.abs(mid[dsum].astype(np.complex128)) ** 2).sum())
+        assert abs(s.sumsq(dsum) - want) <= 1e-4 * want
+        s.upload(eup, mid[eup])  # same values the oracle has at this point, through the upload path
         s.run(steps - half)
         again = {k: s.download(k) for k in O.field_names(cfg)}
-    errs = family_rel_errs(got_mid, mid, ["Dx", "Bz", "Ez"])
+    errs = family_rel_errs(got_mid, mid, list(probe))
     assert max(errs.values()) <= TOL[vt], errs
     errs = family_rel_errs(again, ref, O.field_names(cfg))
     assert max(errs.values()) <= TOL[vt], errs

@@ -57,6 +57,9 @@ def main():
         lines.append("| DRAM read+write per launch | %.3f GB |" % (dram / 1e9))
         lines.append("")
         base = short.replace("_tma", "")
+        targs = re.search(r"<(.*?)>\(", name)
+        if targs and len(targs.group(1).split(",")) == 6 and targs.group(1).split(",")[5].strip() in ("1", "(bool)1", "true"):
+            base += "_core"  # the variants that skip D/B in the sigma-free core
         js[base] = {"dram_bytes_per_launch": dram, "tag": tag, "kernel": name}
     open(os.path.join(ROOT, "profiles", tag + "_ncu_summary.md"), "w").write("\n".join(lines))
     json.dump(js, open(js_path, "w"), indent=1)
