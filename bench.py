@@ -46,6 +46,8 @@ WORKLOADS = {
                label="2D TMz 4096x4096 float real, UPML(10), point source at Ez(70, 2048); BASELINE.json configs[1]"),
     "c4": dict(dims=3, nx=1024, ny=1024, nz_total=1024, vt=8, cplx=True, pml=True, tfsf=True, sphere=True,
                label="3D 1024x1024x%(nz)d complex double, UPML(10)+TF/SF(20), z-slab sharded; BASELINE.json configs[3]"),
+    "c4w": dict(dims=3, nx=1024, ny=1024, nz=128, vt=8, cplx=True, pml=True, tfsf=True, sphere=True,
+                label="3D 1024x1024x%(nz)d complex double, UPML(10)+TF/SF(20); 128 planes per GPU = configs[3]'s slab at 8 GPUs (tuning aid)"),
     "c4s": dict(dims=3, nx=512, ny=512, nz=256, vt=8, cplx=True, pml=True, tfsf=True, sphere=True,
                 label="3D 512x512x%(nz)d complex double, UPML(10)+TF/SF(20); one-GPU sized replica of configs[3] (tuning aid)"),
     "c5": dict(dims=3, nx=1024, ny=1024, nz=512, vt=4, cplx=False, pml=True, tfsf=False, sphere=True,
