@@ -123,9 +123,17 @@ template <> __device__ __forceinline__ double fma_t<double> (double a, double b,
 
 /* Reciprocal for fast mode (exact mode divides).  double: hardware seed (rcp.approx.ftz.f64, ~20 bits) plus two
  * Newton steps -- branch-free, relative error about 1 ulp, no denormal / special-case handling (the argument is
- * eps*eps0 or mu*mu0, about 1e-11 .. 1e-5).  float: the correctly rounded intrinsic (one MUFU + fix-up). */
+ * eps*eps0 or mu*mu0, about 1e-11 .. 1e-5).  float: MUFU seed (~1 ulp) plus one Newton step, also branch-free --
+ * the correctly rounded __frcp_rn (seed + fix-up + a special-case branch, three per cell) was 20 % of all
+ * instructions of the float kernels (profiles/r1_core_c5_ncu_summary.md). */
 template <typename T> __device__ __forceinline__ T rcp_t (T a);
-template <> __device__ __forceinline__ float rcp_t<float> (float a) { return __frcp_rn (a); }
+template <> __device__ __forceinline__ float rcp_t<float> (float a)
+{
+  float r;
+  asm ("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+  const float e = __fmaf_rn (-a, r, 1.0f);
+  return __fmaf_rn (r, e, r);
+}
 template <> __device__ __forceinline__ double rcp_t<double> (double a)
 {
   double r;

@@ -744,7 +744,7 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
 
   /* kernel selection and z-chunk per CTA */
   s->use_tma = false;
-  s->kchunk = 16;
+  s->kchunk = 8; /* 2D: rows marched per thread (profiles/r1_kchunk_sweep.log) */
   if (is3)
   {
     const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
