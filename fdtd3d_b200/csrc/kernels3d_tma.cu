@@ -120,6 +120,8 @@ struct Tile
    * CORE variants move a third fewer bytes per plane with the same per-plane latency chain, so 8 warps per SM no
    * longer cover it: 8-row tiles run two CTAs per SM with a 2-deep ring each (measured: 29.0 -> 31.4 Gcell/s on
    * 512^3 double although the 128-register cap costs ~100 bytes of spills; profiles/r1_core_variants.log).
+   * The same holds for the EXACT variants, whose IEEE divisions make them latency-bound (16.9 -> 19.6 Gcell/s).
+   * The plain fast variants are HBM-bound with one CTA per SM and a 4-deep ring and lose with two.
    */
   static constexpr int CORE_MINB = FDTD_TMA_CORE_MINB > 0 ? FDTD_TMA_CORE_MINB : (TY == 8 ? 2 : FDTD_TMA_MINB);
   static constexpr int CORE_STAGES = FDTD_TMA_CORE_STAGES > 0 ? FDTD_TMA_CORE_STAGES : (TY == 8 ? 2 : STAGES);
@@ -194,12 +196,12 @@ __device__ __forceinline__ void quarter_masks (const StepParams<T> &p, int i0t, 
 /* ------------------------------------------------------------------ E half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
-__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), (CORE ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
+__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), ((CORE || EXACT) ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
 e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
   typedef Tile<T, NC, PML> L;
-  constexpr int V = L::V, W = V * NC, S = CORE ? L::CORE_STAGES : L::STAGES;
+  constexpr int V = L::V, W = V * NC, S = (CORE || EXACT) ? L::CORE_STAGES : L::STAGES;
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
@@ -476,12 +478,12 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 /* ------------------------------------------------------------------ H half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
-__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), (CORE ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
+__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), ((CORE || EXACT) ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
 h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
   typedef Tile<T, NC, PML> L;
-  constexpr int V = L::V, W = V * NC, S = CORE ? L::CORE_STAGES : L::STAGES;
+  constexpr int V = L::V, W = V * NC, S = (CORE || EXACT) ? L::CORE_STAGES : L::STAGES;
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
@@ -749,7 +751,7 @@ cudaError_t launch_t (bool e_phase, const StepParams<T> &p, const TmaSet &maps, 
 {
   typedef Tile<T, NC, PML> L;
   if (ke <= kb) return cudaSuccess;
-  constexpr int smem = CORE ? L::CORE_SMEM : L::SMEM;
+  constexpr int smem = (CORE || EXACT) ? L::CORE_SMEM : L::SMEM;
   dim3 block (32, L::TY);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + L::TY - 1) / L::TY, (ke - kb + p.kchunk - 1) / p.kchunk);
   /* the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute */
