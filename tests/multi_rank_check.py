@@ -1,5 +1,6 @@
-"""Launched by torchrun (one rank per GPU) from tests/test_gpu_multi.py: a z-slab sharded run in exact mode, every
-rank's slab compared bit for bit with the oracle's whole-grid result.  Exit code 0 = parity."""
+"""Launched by torchrun (one rank per GPU) from tests/test_gpu_multi.py: z-slab sharded runs, every rank's slab compared
+with the oracle's whole-grid result -- bit for bit in exact mode, within the north-star tolerance in fast mode (where
+the sigma-free core, whose box spans the slabs, skips D/B).  Exit code 0 = parity."""
 import os
 import sys
 
@@ -29,10 +30,17 @@ def main():
         ((21, 18, 26), 3, 5, True, True, 8, True, 7, (40, 50, 30)),
         ((20, 22, 24), 4, 6, True, False, 8, False, 8, (90, 0, 90)),
         ((18, 16, 22), 3, 5, False, True, 4, False, 8, (90, 0, 90)),
+        # large enough in x and y for a non-empty core box in fast mode
+        ((40, 24, 27), 3, 5, True, True, 8, False, 9, (60, 30, 20)),
+        ((40, 24, 26), 3, 5, True, False, 8, False, 9, (90, 0, 90)),
+        ((140, 40, 22), 4, 6, True, True, 4, False, 8, (90, 0, 90)),
     ]
-    for size, pml, tfsf, use_pml, use_tfsf, vt, cplx, steps, ang in cases:
+    tol = {8: 1e-12, 4: 1e-5}
+    for exact_mode in (1, 0):
+      for size, pml, tfsf, use_pml, use_tfsf, vt, cplx, steps, ang in cases:
         kw = dict(size=size, pml=pml, tfsf=tfsf, use_pml=use_pml, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx,
-                  theta=ang[0], phi=ang[1], psi=ang[2], exact_mode=1)
+                  theta=ang[0], phi=ang[1], psi=ang[2], exact_mode=exact_mode,
+                  source_pos=(size[0] // 2, size[1] // 2, size[2] // 2))
         cfg1 = O.make_config(**kw)
         inputs, fields = random_inputs(cfg1, seed=99)
         ref = O.run(cfg1, steps, inputs, fields)  # whole grid, on every rank's CPU
@@ -49,14 +57,21 @@ def main():
                 s.upload(name, fields[name])
             s.run(steps - 3)
             s.run(3)                          # a second run exercises the halo refresh at run start
+            scale = {}
+            for name in O.field_names(cfg):
+                scale[name[0]] = max(scale.get(name[0], 0.0), float(np.abs(ref[name]).max()))
             for name in O.field_names(cfg):
                 got = s.download(name, z0=z0, nz=nzl)
                 want = multi.slab_of_array(ref[name], size, z0, nzl)
-                exact = np.array_equal(got, want)
-                if not exact:
+                if exact_mode == 1 and (vt == 8 or not cplx):
+                    ok = np.array_equal(got, want)
+                else:
+                    ok = float(np.abs(got - want).max()) <= tol[vt] * scale[name[0]]
+                if not ok:
                     failures += 1
-                    print("rank %d case %s field %s: max |d| = %g" % (rank, size, name, np.abs(got - want).max()), flush=True)
-            if use_tfsf:
+                    print("rank %d mode %d case %s field %s: max |d| = %g (family scale %g)"
+                          % (rank, exact_mode, size, name, np.abs(got - want).max(), scale[name[0]]), flush=True)
+            if use_tfsf and exact_mode == 1:
                 for name in ("EInc", "HInc"):
                     if vt == 8 and not np.array_equal(s.download(name), ref[name]):
                         failures += 1
