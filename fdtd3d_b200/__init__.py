@@ -104,6 +104,19 @@ def pml_sigma_profile(cfg, axis):
     return out
 
 
+def plan_core_box(cfg, sigmas=None):
+    """Box of cells fast mode advances without D/B for `cfg` and the sigma profiles [sx, sy, sz] (None = zero), or None
+    (fdtd_plan_core_box; host only)."""
+    keep = [None if sg is None else np.ascontiguousarray(sg, dtype=real_dtype(cfg)) for sg in (sigmas or [None] * 3)]
+    keep += [None] * (3 - len(keep))
+    ptrs = (C.c_void_p * 3)(*[None if a is None else a.ctypes.data for a in keep])
+    lo, hi = (C.c_int64 * 3)(), (C.c_int64 * 3)()
+    _check(lib().fdtd_plan_core_box(C.byref(cfg), ptrs, lo, hi))
+    if any(lo[a] > hi[a] for a in range(3)):
+        return None
+    return tuple(lo), tuple(hi)
+
+
 class Solver:
     """One device-resident Scheme (Scheme3D or SchemeTMz) -- wraps an ``fdtd_handle``."""
 

@@ -81,6 +81,7 @@ PROTOTYPES = {
     "fdtd_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "fdtd_get_time_step": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "fdtd_get_core_box": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "fdtd_plan_core_box": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "fdtd_field_sumsq": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
     "fdtd_sumsq_noalloc": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int64]),
     "fdtd_comm_unique_id": (C.c_int, [C.c_void_p]),

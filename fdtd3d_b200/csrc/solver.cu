@@ -304,17 +304,16 @@ static int exchange (fdtd_solver *s, bool h_fields)
  * axis (sigma[i] and sigma[i+1]): per axis the longest run of zeros of the profile, shrunk in x to whole quarter
  * tile rows and in y to whole tile rows of the TMA kernels (they decide per quarter row), intersected over the axes.
  */
-static void update_core (fdtd_solver *s)
+static bool compute_core_box (int dims, int fp, int nc, const std::vector<double> sigma[3], int lo_out[3], int hi_out[3])
 {
-  s->core_on = false;
-  for (int a = 0; a < 3; ++a) { s->core_lo[a] = 0; s->core_hi[a] = -1; }
-  if (!s->core_allowed) return;
+  for (int a = 0; a < 3; ++a) { lo_out[a] = 0; hi_out[a] = -1; }
   int txc = 0, ty = 0, qx = 0;
-  if (s->cfg.dims == 3) tma_tile_geometry (s->fp, s->nc, &txc, &ty, &qx);
-  else { qx = 16 / s->cell; ty = 1; } /* TMz kernels decide per 16-byte vector and per row (kernels2d.cu) */
+  if (dims == 3) tma_tile_geometry (fp, nc, &txc, &ty, &qx);
+  else { qx = 16 / (fp * nc); ty = 1; } /* TMz kernels decide per 16-byte vector and per row (kernels2d.cu) */
+  int lo3[3], hi3[3];
   for (int a = 0; a < 3; ++a)
   {
-    const std::vector<double> &sg = s->sigma[a];
+    const std::vector<double> &sg = sigma[a];
     long long best0 = 0, best1 = -1, run0 = 0;
     for (long long i = 0; i <= (long long) sg.size (); ++i)
     {
@@ -328,11 +327,20 @@ static void update_core (fdtd_solver *s)
     long long lo = best0, hi = best1 - 1; /* cells whose samples i and i+1 are both in the run */
     if (a == 0) { lo = round_up (lo, qx); hi = (hi + 1) / qx * qx - 1; }
     if (a == 1) { lo = round_up (lo, ty); hi = (hi + 1) / ty * ty - 1; }
-    if (hi < lo) return;
-    s->core_lo[a] = (int) lo;
-    s->core_hi[a] = (int) hi;
+    if (hi < lo) return false;
+    lo3[a] = (int) lo;
+    hi3[a] = (int) hi;
   }
-  s->core_on = true;
+  for (int a = 0; a < 3; ++a) { lo_out[a] = lo3[a]; hi_out[a] = hi3[a]; }
+  return true;
+}
+
+static void update_core (fdtd_solver *s)
+{
+  s->core_on = false;
+  for (int a = 0; a < 3; ++a) { s->core_lo[a] = 0; s->core_hi[a] = -1; }
+  if (!s->core_allowed) return;
+  s->core_on = compute_core_box (s->cfg.dims, s->fp, s->nc, s->sigma, s->core_lo, s->core_hi);
 }
 
 static int fold_core (fdtd_solver *s, bool fold)
@@ -984,6 +992,27 @@ int fdtd_get_time_step (fdtd_handle s, int64_t *t)
 {
   if (!s || !t) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
   *t = s->t;
+  return FDTD_OK;
+}
+
+int fdtd_plan_core_box (const fdtd_config *cfg, const void *const sigma[3], int64_t lo[3], int64_t hi[3])
+{
+  if (!sigma || !lo || !hi) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  int rc = validate (cfg);
+  if (rc) return rc;
+  std::vector<double> sg[3];
+  for (int a = 0; a < 3; ++a)
+  {
+    const size_t n = (size_t) (a < cfg->dims ? cfg->size[a] : 1) + 1;
+    sg[a].assign (n, 0.0);
+    if (a < cfg->dims && sigma[a])
+      for (size_t i = 0; i < n; ++i)
+        sg[a][i] = cfg->value_type == 4 ? (double) ((const float *) sigma[a])[i] : ((const double *) sigma[a])[i];
+  }
+  int l[3], h[3];
+  const bool on = cfg->use_pml && cfg->exact_mode == 0
+                  && compute_core_box (cfg->dims, cfg->value_type, cfg->complex_values ? 2 : 1, sg, l, h);
+  for (int a = 0; a < 3; ++a) { lo[a] = on ? l[a] : 0; hi[a] = on ? h[a] : -1; }
   return FDTD_OK;
 }
 

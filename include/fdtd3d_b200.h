@@ -195,6 +195,10 @@ int fdtd_get_time_step (fdtd_handle h, int64_t *t);
  */
 int fdtd_get_core_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
 
+/* The same box for a configuration and sigma profiles (FPValue arrays of size[a] + 1 values, NULL = all zero) without
+ * creating a handle; host only, no GPU needed (planning, tests).  No reference counterpart. */
+int fdtd_plan_core_box (const fdtd_config *cfg, const void *const sigma[3], int64_t lo[3], int64_t hi[3]);
+
 /* sum over this rank's cells of |cur|^2 of a field, accumulated in double (diagnostic used by the
  * parity tests at sizes where a full download is impractical; the known-answer vectors of
  * SURVEY.md §8c are quoted in this form). */

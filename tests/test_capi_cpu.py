@@ -138,3 +138,43 @@ def test_host_scheme_init_matches_reference_dumps():
         if meta["use_pml"]:
             for a in range(dims):
                 assert np.array_equal(F.pml_sigma_profile(cfg, a), data["Sigma" + "XYZ"[a]]), (name, a)
+
+
+def _cfg(**kw):
+    import oracle_lib as O
+    return O.make_config(**kw)
+
+
+def test_core_box_planning_is_host_logic():
+    """fdtd_plan_core_box (no GPU): the cells fast mode advances without D/B = per axis the longest zero run of the
+    sigma profile (both material samples i and i+1 of a cell inside it), shrunk in x to whole quarter tile rows and in y
+    to whole tile rows of the kernels."""
+    import numpy as np
+    import oracle_lib as O
+
+    def box(cfg, sig="profile"):
+        if sig == "profile":
+            sig = [O.sigma_profile(cfg, a) for a in range(cfg.dims)]
+        return F.plan_core_box(cfg, sig)
+
+    # 512^3 double, PML 10: sigma is zero for material cells 10..502 -> field cells 10..501; x to 16-cell quarters, y to 8 rows
+    assert box(_cfg(size=(512, 512, 512), pml=10, exact_mode=0)) == ((16, 16, 10), (495, 495, 501))
+    # complex double: one cell per 16 bytes -> 8-cell quarters
+    assert box(_cfg(size=(512, 512, 512), pml=10, exact_mode=0, complex_values=True)) == ((16, 16, 10), (495, 495, 501))
+    # real float: 32-cell quarters, 16-row tiles
+    assert box(_cfg(size=(1024, 1024, 512), pml=10, exact_mode=0, value_type=4)) == ((32, 16, 10), (991, 1007, 501))
+    # 2D TMz float: per 4-cell vector and per row; z is the single plane
+    assert box(_cfg(dims=2, size=(4096, 4096), pml=10, exact_mode=0, value_type=4)) == ((12, 10, 0), (4083, 4085, 0))
+    # exact mode and the D/B-everywhere mode never skip anything; nor does a run without UPML
+    assert box(_cfg(size=(64, 64, 64), pml=6, tfsf=9, exact_mode=1)) is None
+    assert box(_cfg(size=(64, 64, 64), pml=6, tfsf=9, exact_mode=2)) is None
+    assert box(_cfg(size=(64, 64, 64), pml=6, tfsf=9, exact_mode=0, use_pml=False)) is None
+    # too small for one whole quarter row inside the zero run
+    assert box(_cfg(size=(24, 64, 64), pml=6, tfsf=9, exact_mode=0)) is None
+    # all-zero sigma: the whole grid, tile-aligned
+    cfg = _cfg(size=(70, 30, 20), pml=3, tfsf=5, exact_mode=0)
+    assert box(cfg, None) == ((0, 0, 0), (63, 23, 19))
+    # an absorbing sheet in the middle of x: the longer zero run wins
+    sig = [np.zeros(71), np.zeros(31), np.zeros(21)]
+    sig[0][20] = 1.0
+    assert box(cfg, sig) == ((32, 0, 0), (63, 23, 19))
