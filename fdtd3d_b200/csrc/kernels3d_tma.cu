@@ -59,12 +59,15 @@ using namespace k3d;
 #ifndef FDTD_TMA_MINB
 #define FDTD_TMA_MINB 1
 #endif
-/* the same two for the CORE variants (0 = by tile height, see Tile) */
-#ifndef FDTD_TMA_CORE_STAGES
-#define FDTD_TMA_CORE_STAGES 0
+/* the same three for the CORE and EXACT variants ("ALT" configuration; 0 = the defaults of TileRows / Tile) */
+#ifndef FDTD_TMA_ALT_TY
+#define FDTD_TMA_ALT_TY 0
 #endif
-#ifndef FDTD_TMA_CORE_MINB
-#define FDTD_TMA_CORE_MINB 0
+#ifndef FDTD_TMA_ALT_STAGES
+#define FDTD_TMA_ALT_STAGES 0
+#endif
+#ifndef FDTD_TMA_ALT_MINB
+#define FDTD_TMA_ALT_MINB 0
 #endif
 constexpr int N_MAPS = 13; /* 10 full boxes + 3 quarter-width boxes of D / B (CORE variants) */
 
@@ -75,17 +78,34 @@ struct TmaSet
 
 __host__ __device__ constexpr int align128 (int x) { return (x + 127) & ~127; }
 
-template <typename T, int NC, bool PML>
+/*
+ * Rows per CTA tile = warps per CTA, and with it the occupancy recipe.  Two configurations per value type:
+ *
+ *  - the plain fast variants (D/B through every cell) are HBM-bound with ONE CTA per SM and a deep ring: 8 rows x 4
+ *    stages; real float, which packs four cells into a thread's 16 bytes (twice the arithmetic per byte) and was
+ *    latency-bound with 8 warps (0.88 of the HBM peak), 16 rows x 2 stages = 512 threads at <= 128 registers (0.99;
+ *    profiles/r1_tma_variants.log, r1_tma_variants_float.log);
+ *  - the CORE variants move a third fewer bytes per plane with the same per-plane latency chain, and the EXACT variants
+ *    are latency-bound by their IEEE divisions: both want more CTAs per SM.  ALT = 4 rows x 3 stages x THREE CTAs
+ *    per SM (384 threads at up to 168 registers: no spills, 134 KB of ring per SM in flight) -- 512^3 double:
+ *    29.0 (8 rows, 1 CTA) -> 31.4 (8 rows, 2 CTAs x 2 stages, 128 registers with spills) -> 33.9 Gcell/s
+ *    (profiles/r1_core_variants.log).  Real float keeps its 16-row tiles (no difference measured).
+ *
+ * The tensor maps are encoded for the configuration in use (tma_prepare_3d (..., alt)).
+ */
+template <typename T, int NC, bool ALT>
+struct TileRows
+{
+  static constexpr bool F1 = sizeof (T) == 4 && NC == 1;
+  static constexpr int BASE = FDTD_TMA_TY > 0 ? FDTD_TMA_TY : (F1 ? 16 : 8);
+  static constexpr int ALTV = FDTD_TMA_ALT_TY > 0 ? FDTD_TMA_ALT_TY : (F1 ? BASE : 4);
+  static constexpr int value = ALT ? ALTV : BASE;
+};
+
+template <typename T, int NC, bool PML, bool ALT>
 struct Tile
 {
-  /*
-   * Rows per tile = warps per CTA.  Real float packs four cells into a thread's 16 bytes, i.e. twice the arithmetic
-   * per byte of the other types, and with 8 warps per SM its kernels are bound by instruction latency (0.88 of the
-   * HBM peak); 16 rows x 2 stages (same shared memory, 512 threads at <= 128 registers) gives 0.98
-   * (profiles/r1_tma_variants_float.log).  Double and complex types are at the roofline with 8 rows x 4 stages and
-   * would spill at 128 registers (profiles/r1_tma_variants.log).
-   */
-  static constexpr int TY = FDTD_TMA_TY > 0 ? FDTD_TMA_TY : ((sizeof (T) == 4 && NC == 1) ? 16 : 8);
+  static constexpr int TY = TileRows<T, NC, ALT>::value;
   static constexpr int NTHREADS = 32 * TY;
   static constexpr int CELL = NC * (int) sizeof (T);
   static constexpr int V = 16 / CELL;                 /* cells per thread = x halo cells */
@@ -114,18 +134,12 @@ struct Tile
   static constexpr int QX = 8 * V;                    /* cells per quarter row */
   static constexpr int SZ_Q = 128 * TY;
   static constexpr int TX_BASE = SZ_A + SZ_B + SZ_C + 3 * SZ_OWN + SZ_M;
-  static constexpr int STAGES = FDTD_TMA_STAGES > 0 ? FDTD_TMA_STAGES : ((4 * STAGE <= 200 * 1024) ? 4 : ((3 * STAGE <= 225 * 1024) ? 3 : 2));
+  static constexpr int BASE_STAGES = FDTD_TMA_STAGES > 0 ? FDTD_TMA_STAGES : ((4 * STAGE <= 200 * 1024) ? 4 : ((3 * STAGE <= 225 * 1024) ? 3 : 2));
+  static constexpr int ALT_STAGES = FDTD_TMA_ALT_STAGES > 0 ? FDTD_TMA_ALT_STAGES : (TY <= 4 ? 3 : (TY == 8 ? 2 : BASE_STAGES));
+  static constexpr int ALT_MINB = FDTD_TMA_ALT_MINB > 0 ? FDTD_TMA_ALT_MINB : (TY <= 4 ? 3 : (TY == 8 ? 2 : FDTD_TMA_MINB));
+  static constexpr int STAGES = ALT ? ALT_STAGES : BASE_STAGES;
+  static constexpr int MINB = ALT ? ALT_MINB : FDTD_TMA_MINB;
   static constexpr int SMEM = STAGES * STAGE + 128;
-  /*
-   * CORE variants move a third fewer bytes per plane with the same per-plane latency chain, so 8 warps per SM no
-   * longer cover it: 8-row tiles run two CTAs per SM with a 2-deep ring each (measured: 29.0 -> 31.4 Gcell/s on
-   * 512^3 double although the 128-register cap costs ~100 bytes of spills; profiles/r1_core_variants.log).
-   * The same holds for the EXACT variants, whose IEEE divisions make them latency-bound (16.9 -> 19.6 Gcell/s).
-   * The plain fast variants are HBM-bound with one CTA per SM and a 4-deep ring and lose with two.
-   */
-  static constexpr int CORE_MINB = FDTD_TMA_CORE_MINB > 0 ? FDTD_TMA_CORE_MINB : (TY == 8 ? 2 : FDTD_TMA_MINB);
-  static constexpr int CORE_STAGES = FDTD_TMA_CORE_STAGES > 0 ? FDTD_TMA_CORE_STAGES : (TY == 8 ? 2 : STAGES);
-  static constexpr int CORE_SMEM = CORE_STAGES * STAGE + 128;
 };
 
 /* ------------------------------------------------------------------ PTX wrappers */
@@ -196,12 +210,12 @@ __device__ __forceinline__ void quarter_masks (const StepParams<T> &p, int i0t, 
 /* ------------------------------------------------------------------ E half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
-__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), ((CORE || EXACT) ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
+__global__ void __launch_bounds__ ((Tile<T, NC, PML, (CORE || EXACT)>::NTHREADS), (Tile<T, NC, PML, (CORE || EXACT)>::MINB))
 e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
-  typedef Tile<T, NC, PML> L;
-  constexpr int V = L::V, W = V * NC, S = (CORE || EXACT) ? L::CORE_STAGES : L::STAGES;
+  typedef Tile<T, NC, PML, (CORE || EXACT)> L;
+  constexpr int V = L::V, W = V * NC, S = L::STAGES;
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
@@ -478,12 +492,12 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 /* ------------------------------------------------------------------ H half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
-__global__ void __launch_bounds__ ((Tile<T, NC, PML>::NTHREADS), ((CORE || EXACT) ? Tile<T, NC, PML>::CORE_MINB : FDTD_TMA_MINB))
+__global__ void __launch_bounds__ ((Tile<T, NC, PML, (CORE || EXACT)>::NTHREADS), (Tile<T, NC, PML, (CORE || EXACT)>::MINB))
 h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
   static_assert (!CORE || (PML && !EXACT), "the sigma-free core is a fast-mode UPML optimisation");
-  typedef Tile<T, NC, PML> L;
-  constexpr int V = L::V, W = V * NC, S = (CORE || EXACT) ? L::CORE_STAGES : L::STAGES;
+  typedef Tile<T, NC, PML, (CORE || EXACT)> L;
+  constexpr int V = L::V, W = V * NC, S = L::STAGES;
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
@@ -749,9 +763,9 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE = false>
 cudaError_t launch_t (bool e_phase, const StepParams<T> &p, const TmaSet &maps, int kb, int ke, cudaStream_t stream)
 {
-  typedef Tile<T, NC, PML> L;
+  typedef Tile<T, NC, PML, (CORE || EXACT)> L;
   if (ke <= kb) return cudaSuccess;
-  constexpr int smem = (CORE || EXACT) ? L::CORE_SMEM : L::SMEM;
+  constexpr int smem = L::SMEM;
   dim3 block (32, L::TY);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + L::TY - 1) / L::TY, (ke - kb + p.kchunk - 1) / p.kchunk);
   /* the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute */
@@ -847,11 +861,11 @@ bool encode (CUtensorMap *out, void *base, int scalar_bytes, long long xs, long 
   return true;
 }
 
-template <typename T, int NC>
-bool prepare_t (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu, int pitch, int ny, int planes, int pitchM,
+template <typename T, int NC, bool ALT>
+bool prepare_tt (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu, int pitch, int ny, int planes, int pitchM,
                 int planesM, std::string *err)
 {
-  typedef Tile<T, NC, true> L; /* box shapes do not depend on PML */
+  typedef Tile<T, NC, true, ALT> L; /* box shapes do not depend on PML */
   static_assert (sizeof (TmaSet) <= sizeof (out->e), "TmaMaps3D too small");
   TmaSet *e = reinterpret_cast<TmaSet *> (out->e), *h = reinterpret_cast<TmaSet *> (out->h);
   const int sb = (int) sizeof (T);
@@ -878,26 +892,41 @@ bool prepare_t (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu
   return ok;
 }
 
+template <typename T, int NC>
+bool prepare_t (TmaMaps3D *out, bool pml, bool alt, void *const f[12], void *eps, void *mu, int pitch, int ny, int planes,
+                int pitchM, int planesM, std::string *err)
+{
+  return alt ? prepare_tt<T, NC, true> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err)
+             : prepare_tt<T, NC, false> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
+}
+
+template <typename T, int NC>
+void geometry_t (bool alt, int &txc, int &ty, int &qx)
+{
+  if (alt) { typedef Tile<T, NC, true, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+  else { typedef Tile<T, NC, true, false> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+}
+
 } /* namespace */
 
-bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, void *const f[12], void *eps, void *mu, int pitch,
-                     int ny, int planes, int pitchM, int planesM, std::string *err)
+bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, bool alt, void *const f[12], void *eps, void *mu,
+                     int pitch, int ny, int planes, int pitchM, int planesM, std::string *err)
 {
   out->valid = false;
   if (value_type == 4)
-    return nc == 2 ? prepare_t<float, 2> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err)
-                   : prepare_t<float, 1> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
-  return nc == 2 ? prepare_t<double, 2> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err)
-                 : prepare_t<double, 1> (out, pml, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
+    return nc == 2 ? prepare_t<float, 2> (out, pml, alt, f, eps, mu, pitch, ny, planes, pitchM, planesM, err)
+                   : prepare_t<float, 1> (out, pml, alt, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
+  return nc == 2 ? prepare_t<double, 2> (out, pml, alt, f, eps, mu, pitch, ny, planes, pitchM, planesM, err)
+                 : prepare_t<double, 1> (out, pml, alt, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
 }
 
-void tma_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *quarter_cells_x)
+void tma_tile_geometry (int value_type, int nc, bool alt, int *tile_cells_x, int *tile_rows, int *quarter_cells_x)
 {
   int txc, ty, qx;
-  if (value_type == 4 && nc == 1) { typedef Tile<float, 1, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
-  else if (value_type == 4) { typedef Tile<float, 2, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
-  else if (nc == 1) { typedef Tile<double, 1, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
-  else { typedef Tile<double, 2, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+  if (value_type == 4 && nc == 1) geometry_t<float, 1> (alt, txc, ty, qx);
+  else if (value_type == 4) geometry_t<float, 2> (alt, txc, ty, qx);
+  else if (nc == 1) geometry_t<double, 1> (alt, txc, ty, qx);
+  else geometry_t<double, 2> (alt, txc, ty, qx);
   if (tile_cells_x) *tile_cells_x = txc;
   if (tile_rows) *tile_rows = ty;
   if (quarter_cells_x) *quarter_cells_x = qx;

@@ -19,17 +19,18 @@ cudaError_t launch_phase_3d (bool e_phase, const StepParams<T> &p, bool cplx, bo
 
 /* TMA-staged 3D half steps (kernels3d_tma.cu).  TmaMaps3D holds the CUtensorMap descriptors (13 per phase,
  * 128 bytes each) of one solver's arrays; tma_prepare_3d encodes them once the arrays are allocated.
- * `core` selects the variants that skip D / B inside the box p.core_lo .. p.core_hi (fast mode with UPML only);
- * tma_tile_geometry gives the tile shape that box has to be aligned to. */
+ * `core` selects the variants that skip D / B inside the box p.core_lo .. p.core_hi (fast mode with UPML only).
+ * The CORE and EXACT variants use another tile height than the plain fast ones (kernels3d_tma.cu, TileRows): `alt`
+ * = exact || core tells tma_prepare_3d / tma_tile_geometry which; the maps must be encoded for the variant launched. */
 struct TmaMaps3D
 {
   alignas (64) unsigned char e[13 * 128];
   alignas (64) unsigned char h[13 * 128];
   bool valid;
 };
-void tma_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *quarter_cells_x);
-bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, void *const f[12], void *eps, void *mu, int pitch,
-                     int ny, int planes, int pitchM, int planesM, std::string *err);
+void tma_tile_geometry (int value_type, int nc, bool alt, int *tile_cells_x, int *tile_rows, int *quarter_cells_x);
+bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, bool alt, void *const f[12], void *eps, void *mu,
+                     int pitch, int ny, int planes, int pitchM, int planesM, std::string *err);
 template <typename T>
 cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
                                  bool exact, bool core, int kb, int ke, cudaStream_t stream);

@@ -101,6 +101,7 @@ struct fdtd_solver
   /* sigma-free core (kernels3d_tma.cu, CORE variants): box of cells whose D/B the time loop skips, and whether the
    * D/B arrays currently hold the folded representation D - eps eps0 E there (aux_kernels.cu, fold_aux_kernel) */
   bool core_allowed, core_on, folded;
+  bool tma_alt;         /* tile configuration the tensor maps and kchunk were set up for (exact || core_on) */
   int core_lo[3], core_hi[3];
 
   bool profiling;
@@ -308,7 +309,7 @@ static bool compute_core_box (int dims, int fp, int nc, const std::vector<double
 {
   for (int a = 0; a < 3; ++a) { lo_out[a] = 0; hi_out[a] = -1; }
   int txc = 0, ty = 0, qx = 0;
-  if (dims == 3) tma_tile_geometry (fp, nc, &txc, &ty, &qx);
+  if (dims == 3) tma_tile_geometry (fp, nc, true, &txc, &ty, &qx); /* the CORE variants' tiles */
   else { qx = 16 / (fp * nc); ty = 1; } /* TMz kernels decide per 16-byte vector and per row (kernels2d.cu) */
   int lo3[3], hi3[3];
   for (int a = 0; a < 3; ++a)
@@ -341,6 +342,45 @@ static void update_core (fdtd_solver *s)
   for (int a = 0; a < 3; ++a) { s->core_lo[a] = 0; s->core_hi[a] = -1; }
   if (!s->core_allowed) return;
   s->core_on = compute_core_box (s->cfg.dims, s->fp, s->nc, s->sigma, s->core_lo, s->core_hi);
+}
+
+/*
+ * Tensor maps and planes marched per CTA for the tile configuration of the kernels that will run (3D only): the CORE and
+ * EXACT variants use other tiles than the plain fast ones (kernels3d_tma.cu, TileRows), and whether the core is on
+ * depends on the sigma profiles, so this runs at creation and again when fdtd_set_sigma changes the answer.
+ */
+static int configure_3d (fdtd_solver *s, bool first)
+{
+  if (s->cfg.dims != 3) return FDTD_OK;
+  const bool alt = s->cfg.exact_mode == 1 || s->core_on;
+  if (!first && alt == s->tma_alt) return FDTD_OK;
+  s->tma_alt = alt;
+  int txc = 32 * (16 / s->cell), tyr = 8; /* cells per CTA tile row, rows per CTA tile (direct kernels) */
+  if (s->use_tma) tma_tile_geometry (s->fp, s->nc, alt, &txc, &tyr, NULL);
+  const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + tyr - 1) / tyr);
+  /* planes marched per CTA: measured best (profiles/r1_kchunk_sweep.log) when a launch has about 8192 CTAs
+   * (~55 per SM) -- short enough marches to keep the SMs evenly loaded to the end, long enough to amortise the
+   * pipeline fill; never more than 64 planes, and small grids still get at least two CTAs per SM */
+  long long kc_ll = (long long) s->nzl * tiles / 8192;
+  const long long kc_small = (long long) s->nzl * tiles / (2 * 148);
+  if (kc_ll > kc_small) kc_ll = kc_small;
+  int kc = (int) kc_ll;
+  if (kc > 64) kc = 64;
+  if (kc < 4) kc = 4;
+  s->kchunk = kc;
+  if (const char *kc_env = getenv ("FDTD3D_B200_KCHUNK")) /* tuning aid: planes marched per CTA */
+  {
+    const int v = atoi (kc_env);
+    if (v > 0) s->kchunk = v;
+  }
+  if (s->use_tma)
+  {
+    std::string err;
+    if (!tma_prepare_3d (&s->tma, s->fp, s->nc, s->cfg.use_pml != 0, alt, s->f, s->eps, s->mu, s->pitch, s->ny, s->nzl + 2,
+                         s->pitchM, s->nzm + 2, &err))
+      return fail (FDTD_ERROR, "TMA descriptor set-up failed: %s", err.c_str ());
+  }
+  return FDTD_OK;
 }
 
 static int fold_core (fdtd_solver *s, bool fold)
@@ -750,26 +790,18 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   CREATE_TRY (cudaMalloc ((void **) &s->red_out, sizeof (double)));
 #undef CREATE_TRY
 
-  /* kernel selection and z-chunk per CTA */
+  /* kernel selection; the TF/SF face tables of the TMA kernels */
   s->use_tma = false;
   s->kchunk = 8; /* 2D: rows marched per thread (profiles/r1_kchunk_sweep.log) */
+  if (const char *kc_env = getenv ("FDTD3D_B200_KCHUNK")) /* tuning aid; 3D: see configure_3d */
+  {
+    const int v = atoi (kc_env);
+    if (v > 0) s->kchunk = v;
+  }
   if (is3)
   {
     const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
     s->use_tma = !(sel && strcmp (sel, "direct") == 0);
-    int txc = 32 * (16 / s->cell), tyr = 8; /* cells per CTA tile row, rows per CTA tile */
-    if (s->use_tma) tma_tile_geometry (s->fp, s->nc, &txc, &tyr, NULL);
-    const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + tyr - 1) / tyr);
-    /* planes marched per CTA: measured best (profiles/r1_kchunk_sweep.log) when a launch has about 8192 CTAs
-     * (~55 per SM) -- short enough marches to keep the SMs evenly loaded to the end, long enough to amortise the
-     * pipeline fill; never more than 64 planes, and small grids still get at least two CTAs per SM */
-    long long kc_ll = (long long) s->nzl * tiles / 8192;
-    const long long kc_small = (long long) s->nzl * tiles / (2 * 148);
-    if (kc_ll > kc_small) kc_ll = kc_small;
-    int kc = (int) kc_ll;
-    if (kc > 64) kc = 64;
-    if (kc < 4) kc = 4;
-    s->kchunk = kc;
     if (s->use_tma && cfg->use_tfsf)
     {
       long long m = (long long) s->nx * s->ny;
@@ -785,17 +817,6 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
         return FDTD_ERROR;
       }
     }
-    if (s->use_tma)
-    {
-      std::string err;
-      if (!tma_prepare_3d (&s->tma, s->fp, s->nc, cfg->use_pml != 0, s->f, s->eps, s->mu, s->pitch, s->ny, s->nzl + 2, s->pitchM,
-                           s->nzm + 2, &err))
-      {
-        fail (FDTD_ERROR, "TMA descriptor set-up failed: %s", err.c_str ());
-        fdtd_destroy (s);
-        return FDTD_ERROR;
-      }
-    }
   }
 
   /* fast mode with UPML on the TMA kernels skips D / B where sigma = 0; exact_mode 2 (or FDTD3D_B200_CORE=0, for
@@ -803,11 +824,10 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   s->core_allowed = (is3 ? s->use_tma : true) && cfg->use_pml && cfg->exact_mode == 0;
   if (const char *ce = getenv ("FDTD3D_B200_CORE")) { if (atoi (ce) == 0) s->core_allowed = false; }
   update_core (s);
-
-  if (const char *kc_env = getenv ("FDTD3D_B200_KCHUNK")) /* tuning aid: planes (3D) / rows (2D) marched per CTA */
+  if ((rc = configure_3d (s, true)))
   {
-    const int kc = atoi (kc_env);
-    if (kc > 0) s->kchunk = kc;
+    fdtd_destroy (s);
+    return rc;
   }
 
   *out = s;
@@ -855,6 +875,7 @@ int fdtd_set_sigma (fdtd_handle s, int axis, const void *profile, int64_t count)
   for (int64_t i = 0; i < count; ++i)
     s->sigma[axis][(size_t) i] = s->fp == 4 ? (double) ((const float *) profile)[i] : ((const double *) profile)[i];
   update_core (s);
+  if ((rc = configure_3d (s, false))) return rc;
   return build_tables_any (s);
 }
 
