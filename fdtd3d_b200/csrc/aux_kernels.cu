@@ -1,5 +1,5 @@
 /*
- * Small kernels around the two half-step kernels: the 1-D incident-wave line, the step counter,
+ * Small kernels around the two half-step kernels: the 1-D incident-wave line,
  * host-order <-> device-layout conversion, fills, the eps sphere and the |field|^2 reduction.
  * Compiled with -fmad=false like the rest (exact mode relies on it).
  */
@@ -23,7 +23,7 @@ __global__ void incident_e (const StepParams<T> p)
   if (i >= p.ninc) return;
   if (i == 0)
   {
-    const long long s = *p.step;
+    const long long s = p.step;
 #pragma unroll
     for (int c = 0; c < NC; ++c) p.einc[c] = p.src[s * NC + c];
     return;
@@ -51,8 +51,6 @@ __global__ void incident_h (const StepParams<T> p)
     p.hinc[i * NC + c] = EXACT ? h + p.inc_ch * d : fma_t<T> (p.inc_ch, d, h);
   }
 }
-
-__global__ void tick_kernel (long long *step) { *step += 1; }
 
 /* ------------------------------------------------------------------ layout conversion */
 
@@ -445,12 +443,6 @@ cudaError_t launch_fold_aux (const StepParams<T> &p, bool tmz, bool cplx, bool t
 }
 template cudaError_t launch_fold_aux<float> (const StepParams<float> &, bool, bool, bool, bool, cudaStream_t);
 template cudaError_t launch_fold_aux<double> (const StepParams<double> &, bool, bool, bool, bool, cudaStream_t);
-
-cudaError_t launch_tick (long long *step, cudaStream_t stream)
-{
-  tick_kernel<<<1, 1, 0, stream>>> (step);
-  return cudaGetLastError ();
-}
 
 cudaError_t launch_reorder (bool to_device, void *dev, void *staged, int cellBytes, int ia, int ib, int ny, int nzb,
                             int pitch, long long ps, int kofs, int kmin, int kmax, cudaStream_t stream)

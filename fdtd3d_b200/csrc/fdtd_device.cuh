@@ -51,7 +51,7 @@ struct StepParams
   T *face_tab;          /* TF/SF incident values of the face cells, 24 tables (kernels3d_common.cuh, tfsf_curl_tab) */
   long long face_stride; /* cells per table */
   const T *src;         /* source samples for the steps of the current run, one cell per step */
-  long long *step;      /* device step counter: index into src of the step being computed */
+  long long step;       /* index into src of the step being computed (set per launch by the time loop) */
   long long ninc;       /* cells in einc / hinc */
 
   int nx, ny;           /* global x/y size */

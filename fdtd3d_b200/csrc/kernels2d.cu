@@ -111,7 +111,7 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
 
   FVec hx_jm = ldv<T, W> (Hx + o - row);
   long long step = 0;
-  if (!TFSF) step = *p.step;
+  if (!TFSF) step = p.step;
   const bool x_core = CORE && i0 >= p.core_lo[0] && i0 + V - 1 <= p.core_hi[0];
 
   for (int j = j0; j < j1; ++j, o += row, om += p.pitchM)

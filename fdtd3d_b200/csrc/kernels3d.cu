@@ -91,7 +91,7 @@ e_phase_3d (const __grid_constant__ StepParams<T> p, int kb, int ke)
   MVec eps_c = ldv<T, V> (p.eps + om);
 
   long long step = 0;
-  if (!TFSF) step = *p.step;
+  if (!TFSF) step = p.step;
 
   for (int k = k0; k < k1; ++k, o += pl, om += p.psM)
   {

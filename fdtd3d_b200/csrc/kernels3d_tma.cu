@@ -318,7 +318,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   }
 
   long long step = 0;
-  if (!TFSF) step = *p.step;
+  if (!TFSF) step = p.step;
 
   /* per-thread byte offsets inside a stage */
   const int xo = tx * 16;
@@ -901,10 +901,10 @@ bool prepare_t (TmaMaps3D *out, bool pml, bool alt, void *const f[12], void *eps
 }
 
 template <typename T, int NC>
-void geometry_t (bool alt, int &txc, int &ty, int &qx)
+void geometry_t (bool alt, int &txc, int &ty, int &qx, int &minb)
 {
-  if (alt) { typedef Tile<T, NC, true, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
-  else { typedef Tile<T, NC, true, false> L; txc = L::TXC; ty = L::TY; qx = L::QX; }
+  if (alt) { typedef Tile<T, NC, true, true> L; txc = L::TXC; ty = L::TY; qx = L::QX; minb = L::MINB; }
+  else { typedef Tile<T, NC, true, false> L; txc = L::TXC; ty = L::TY; qx = L::QX; minb = L::MINB; }
 }
 
 } /* namespace */
@@ -920,16 +920,18 @@ bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, bool alt,
                  : prepare_t<double, 1> (out, pml, alt, f, eps, mu, pitch, ny, planes, pitchM, planesM, err);
 }
 
-void tma_tile_geometry (int value_type, int nc, bool alt, int *tile_cells_x, int *tile_rows, int *quarter_cells_x)
+void tma_tile_geometry (int value_type, int nc, bool alt, int *tile_cells_x, int *tile_rows, int *quarter_cells_x,
+                        int *ctas_per_sm)
 {
-  int txc, ty, qx;
-  if (value_type == 4 && nc == 1) geometry_t<float, 1> (alt, txc, ty, qx);
-  else if (value_type == 4) geometry_t<float, 2> (alt, txc, ty, qx);
-  else if (nc == 1) geometry_t<double, 1> (alt, txc, ty, qx);
-  else geometry_t<double, 2> (alt, txc, ty, qx);
+  int txc, ty, qx, minb;
+  if (value_type == 4 && nc == 1) geometry_t<float, 1> (alt, txc, ty, qx, minb);
+  else if (value_type == 4) geometry_t<float, 2> (alt, txc, ty, qx, minb);
+  else if (nc == 1) geometry_t<double, 1> (alt, txc, ty, qx, minb);
+  else geometry_t<double, 2> (alt, txc, ty, qx, minb);
   if (tile_cells_x) *tile_cells_x = txc;
   if (tile_rows) *tile_rows = ty;
   if (quarter_cells_x) *quarter_cells_x = qx;
+  if (ctas_per_sm) *ctas_per_sm = minb;
 }
 
 template <typename T>

@@ -28,7 +28,8 @@ struct TmaMaps3D
   alignas (64) unsigned char h[13 * 128];
   bool valid;
 };
-void tma_tile_geometry (int value_type, int nc, bool alt, int *tile_cells_x, int *tile_rows, int *quarter_cells_x);
+void tma_tile_geometry (int value_type, int nc, bool alt, int *tile_cells_x, int *tile_rows, int *quarter_cells_x,
+                        int *ctas_per_sm);
 bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, bool alt, void *const f[12], void *eps, void *mu,
                      int pitch, int ny, int planes, int pitchM, int planesM, std::string *err);
 template <typename T>
@@ -60,9 +61,6 @@ cudaError_t launch_face_tables (bool e_phase, const StepParams<T> &p, bool cplx,
  * the post-processing of Scheme3D.cpp:2767-2921 */
 template <typename T>
 cudaError_t launch_scattered (const StepParams<T> &p, bool cplx, int comp, cudaStream_t stream);
-
-/* step counter += 1 (one thread) */
-cudaError_t launch_tick (long long *step, cudaStream_t stream);
 
 /*
  * Layout conversion between a staged host-order block and the device layout.

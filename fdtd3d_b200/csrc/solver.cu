@@ -83,7 +83,6 @@ struct fdtd_solver
   size_t tab_stride; /* bytes between tables */
   void *src;         /* source samples */
   long long src_capacity;
-  long long *step;
   void *staging;     /* layout-conversion scratch */
   size_t staging_bytes;
   double *red_partials, *red_out; /* reduction scratch */
@@ -144,7 +143,7 @@ static StepParams<T> make_params (const fdtd_solver *s)
   p.face_tab = (T *) s->face_tab;
   p.face_stride = s->face_stride;
   p.src = (const T *) s->src;
-  p.step = s->step;
+  p.step = 0;
   p.ninc = s->ninc;
   p.nx = s->nx; p.ny = s->ny; p.nzl = s->nzl; p.kz0 = s->kz0; p.nzg = s->nzg;
   p.pitch = s->pitch; p.pitchM = s->pitchM; p.ps = s->ps; p.psM = s->psM;
@@ -309,7 +308,7 @@ static bool compute_core_box (int dims, int fp, int nc, const std::vector<double
 {
   for (int a = 0; a < 3; ++a) { lo_out[a] = 0; hi_out[a] = -1; }
   int txc = 0, ty = 0, qx = 0;
-  if (dims == 3) tma_tile_geometry (fp, nc, true, &txc, &ty, &qx); /* the CORE variants' tiles */
+  if (dims == 3) tma_tile_geometry (fp, nc, true, &txc, &ty, &qx, NULL); /* the CORE variants' tiles */
   else { qx = 16 / (fp * nc); ty = 1; } /* TMz kernels decide per 16-byte vector and per row (kernels2d.cu) */
   int lo3[3], hi3[3];
   for (int a = 0; a < 3; ++a)
@@ -355,14 +354,14 @@ static int configure_3d (fdtd_solver *s, bool first)
   const bool alt = s->cfg.exact_mode == 1 || s->core_on;
   if (!first && alt == s->tma_alt) return FDTD_OK;
   s->tma_alt = alt;
-  int txc = 32 * (16 / s->cell), tyr = 8; /* cells per CTA tile row, rows per CTA tile (direct kernels) */
-  if (s->use_tma) tma_tile_geometry (s->fp, s->nc, alt, &txc, &tyr, NULL);
+  int txc = 32 * (16 / s->cell), tyr = 8, per_sm = 1; /* cells per CTA tile row, rows per CTA tile, resident CTAs per SM */
+  if (s->use_tma) tma_tile_geometry (s->fp, s->nc, alt, &txc, &tyr, NULL, &per_sm);
   const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((s->ny + tyr - 1) / tyr);
-  /* planes marched per CTA: measured best (profiles/r1_kchunk_sweep.log) when a launch has about 8192 CTAs
-   * (~55 per SM) -- short enough marches to keep the SMs evenly loaded to the end, long enough to amortise the
-   * pipeline fill; never more than 64 planes, and small grids still get at least two CTAs per SM */
-  long long kc_ll = (long long) s->nzl * tiles / 8192;
-  const long long kc_small = (long long) s->nzl * tiles / (2 * 148);
+  /* planes marched per CTA: measured best (profiles/r1_kchunk_sweep.log) when a launch has about 8192 CTAs per
+   * resident CTA of an SM (~55 rounds) -- short enough marches to keep the SMs evenly loaded to the end, long enough to
+   * amortise the pipeline fill; never more than 64 planes, and small grids still get at least two rounds */
+  long long kc_ll = (long long) s->nzl * tiles / (8192LL * per_sm);
+  const long long kc_small = (long long) s->nzl * tiles / (2LL * 148 * per_sm);
   if (kc_ll > kc_small) kc_ll = kc_small;
   int kc = (int) kc_ll;
   if (kc > 64) kc = 64;
@@ -416,7 +415,7 @@ template <typename T>
 static int enqueue_steps (fdtd_solver *s, long long nsteps)
 {
   const fdtd_config &c = s->cfg;
-  const StepParams<T> p = make_params<T> (s);
+  StepParams<T> p = make_params<T> (s);
   const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode == 1;
   const bool multi = c.nranks > 1;
   cudaStream_t S = s->s_compute, C = s->s_comm;
@@ -446,6 +445,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
   for (long long n = 0; n < nsteps; ++n)
   {
     /* Scheme3D::performNSteps, Scheme3D.cpp:1986-2069 (SchemeTMz.cpp:1336-1427) */
+    p.step = n; /* the parameter block is passed by value with every launch */
     if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, exact, S)); s->launches++; }
     if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (true, p, cplx, S)); s->launches++; }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
@@ -493,7 +493,6 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
       if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, false, p, 0, s->nzl - 1, S)); s->launches++; }
     }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
-    CUDA_TRY (launch_tick (s->step, S)); s->launches++;
   }
   if (multi) CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
   return FDTD_OK;
@@ -511,7 +510,6 @@ static int run_async (fdtd_solver *s, long long nsteps)
   if (nsteps == 0) { s->last_ms = 0; return FDTD_OK; }
   int rc = s->fp == 4 ? upload_source<float> (s, nsteps) : upload_source<double> (s, nsteps);
   if (rc) return rc;
-  CUDA_TRY (cudaMemsetAsync (s->step, 0, sizeof (long long), s->s_compute));
   CUDA_TRY (cudaEventRecord (s->ev_start, s->s_compute));
   if (s->core_on && !s->folded && (rc = fold_core (s, true))) return rc;
   rc = s->fp == 4 ? enqueue_steps<float> (s, nsteps) : enqueue_steps<double> (s, nsteps);
@@ -777,8 +775,6 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   if (tlen < s->pitchM + 128 / s->fp) tlen = s->pitchM + 128 / s->fp;
   s->tab_stride = (size_t) tlen * s->fp;
   CREATE_TRY (cudaMalloc (&s->tab_mem, (size_t) N_TABLES * s->tab_stride));
-  CREATE_TRY (cudaMalloc ((void **) &s->step, sizeof (long long)));
-  CREATE_TRY (cudaMemsetAsync (s->step, 0, sizeof (long long), s->s_compute));
   s->staging_bytes = (size_t) 64 << 20;
   {
     /* one i-row of the largest field must fit */
@@ -852,7 +848,7 @@ int fdtd_destroy (fdtd_handle s)
     if (nccl) nccl->CommDestroy (s->comm);
   }
   for (int f = 0; f < 12; ++f) if (s->f[f]) cudaFree (s->f[f]);
-  void *ptrs[] = { s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->step, s->staging, s->red_partials, s->red_out };
+  void *ptrs[] = { s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->staging, s->red_partials, s->red_out };
   for (void *p : ptrs) if (p) cudaFree (p);
   cudaEvent_t evs[] = { s->ev_start, s->ev_stop, s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx };
   for (cudaEvent_t e : evs) if (e) cudaEventDestroy (e);

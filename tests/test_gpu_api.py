@@ -95,6 +95,6 @@ def test_profiling_reports_both_half_steps():
         s.run(5)
         e_ms, h_ms, steps = s.phase_times()
         assert steps == 5 and e_ms > 0 and h_ms > 0
-        # per step: incident E, E face tables, E phase, incident H, H face tables, H phase, tick
-        assert s.launch_count - n0 == 5 * 7
+        # per step: incident E, E face tables, E phase, incident H, H face tables, H phase
+        assert s.launch_count - n0 == 5 * 6
         assert e_ms + h_ms <= s.last_run_ms * 1.05
