@@ -491,7 +491,13 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
 /* ------------------------------------------------------------------ H half step */
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
+/*
+ * UNIMU: mu holds one value everywhere (p.mu_const; the solver knows because the array was last set with fdtd_fill --
+ * the reference itself never initialises mu to anything but 1).  The material box is not loaded (FP bytes less per
+ * cell) and the averaged mu -- ((m + m) / 2 + (m + m) / 2) / 2 is m exactly, so also in exact mode -- and everything
+ * derived from it alone become loop invariants.
+ */
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE, bool UNIMU>
 __global__ void __launch_bounds__ ((Tile<T, NC, PML, (CORE || EXACT)>::NTHREADS), (Tile<T, NC, PML, (CORE || EXACT)>::MINB))
 h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__ TmaSet maps, int kb, int ke)
 {
@@ -529,7 +535,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
     unsigned char *base = smem + slot * L::STAGE;
     unsigned long long *bar = &full[slot];
     const int m = CORE ? d_mask (k) : 0;
-    mbar_expect_tx (bar, CORE ? L::TX_BASE + __popc (m) * 3 * L::SZ_Q : L::TX_BYTES);
+    mbar_expect_tx (bar, (CORE ? L::TX_BASE + __popc (m) * 3 * L::SZ_Q : L::TX_BYTES) - (UNIMU ? L::SZ_M : 0));
     tma_load_3d (base + L::OFF_A, &maps.m[0], bar, i0t * NC, j0t, k + 1);
     tma_load_3d (base + L::OFF_B, &maps.m[1], bar, i0t * NC, j0t, k + 2);
     tma_load_3d (base + L::OFF_C, &maps.m[2], bar, i0t * NC, j0t, k + 2);
@@ -546,7 +552,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
             tma_load_3d (base + L::OFF_OWN + (3 + a) * L::OWN_STRIDE + q * L::SZ_Q, &maps.m[10 + a], bar,
                          (i0t + q * L::QX) * NC, j0t, k + 1);
     }
-    tma_load_3d (base + L::OFF_M, &maps.m[9], bar, i0t, j0t, k + 2);
+    if (!UNIMU) tma_load_3d (base + L::OFF_M, &maps.m[9], bar, i0t, j0t, k + 2);
   };
 
   if (leader)
@@ -598,10 +604,13 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
     ey = ldv<T, W> (p.f[1] + o);
 #pragma unroll
     for (int c = 0; c < NC; ++c) ey_ip[c] = __ldg (p.f[1] + o + W + c);
-    mu_c = ldv<T, V> (p.mu + om);
-    mu_jp = ldv<T, V> (p.mu + om + p.pitchM);
-    mu_ip = __ldg (p.mu + om + V);
-    mu_ip_jp = __ldg (p.mu + om + p.pitchM + V);
+    if (!UNIMU)
+    {
+      mu_c = ldv<T, V> (p.mu + om);
+      mu_jp = ldv<T, V> (p.mu + om + p.pitchM);
+      mu_ip = __ldg (p.mu + om + V);
+      mu_ip_jp = __ldg (p.mu + om + p.pitchM + V);
+    }
   }
 
   const int xo = tx * 16;
@@ -646,9 +655,21 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
       by = lds<T, W> (sAux + so + 4 * L::OWN_STRIDE);
       bz = lds<T, W> (sAux + so + 5 * L::OWN_STRIDE);
     }
-    const MVec mu_kp = lds<T, V> (sM + so), mu_jp_kp = lds<T, V> (sM + so + L::ROW_M);
-    const T mu_ip_kp = *reinterpret_cast<const T *> (sM + so + V * sizeof (T));
-    const T mu_ip_jp_kp = *reinterpret_cast<const T *> (sM + so + L::ROW_M + V * sizeof (T));
+    MVec mu_kp, mu_jp_kp;
+    T mu_ip_kp, mu_ip_jp_kp;
+    if (UNIMU)
+    {
+#pragma unroll
+      for (int v = 0; v < V; ++v) mu_kp.v[v] = mu_jp_kp.v[v] = mu_c.v[v] = mu_jp.v[v] = p.mu_const;
+      mu_ip_kp = mu_ip_jp_kp = mu_ip = mu_ip_jp = p.mu_const;
+    }
+    else
+    {
+      mu_kp = lds<T, V> (sM + so);
+      mu_jp_kp = lds<T, V> (sM + so + L::ROW_M);
+      mu_ip_kp = *reinterpret_cast<const T *> (sM + so + V * sizeof (T));
+      mu_ip_jp_kp = *reinterpret_cast<const T *> (sM + so + L::ROW_M + V * sizeof (T));
+    }
 
     if (active)
     {
@@ -760,61 +781,68 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
 /* ------------------------------------------------------------------ dispatch */
 
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE, bool UNIMU>
+cudaError_t launch_h (const StepParams<T> &p, const TmaSet &maps, dim3 grid, dim3 block, int smem, int kb, int ke, cudaStream_t stream)
+{
+  /* the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute */
+  static bool attr_dev[64] = {};
+  int dev = 0;
+  cudaError_t de = cudaGetDevice (&dev);
+  if (de != cudaSuccess) return de;
+  if (!attr_dev[dev & 63])
+  {
+    cudaError_t e = cudaFuncSetAttribute (h_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE, UNIMU>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_dev[dev & 63] = true;
+  }
+  h_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE, UNIMU><<<grid, block, smem, stream>>> (p, maps, kb, ke);
+  return cudaGetLastError ();
+}
+
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE = false>
-cudaError_t launch_t (bool e_phase, const StepParams<T> &p, const TmaSet &maps, int kb, int ke, cudaStream_t stream)
+cudaError_t launch_t (bool e_phase, bool unimu, const StepParams<T> &p, const TmaSet &maps, int kb, int ke, cudaStream_t stream)
 {
   typedef Tile<T, NC, PML, (CORE || EXACT)> L;
   if (ke <= kb) return cudaSuccess;
   constexpr int smem = L::SMEM;
   dim3 block (32, L::TY);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + L::TY - 1) / L::TY, (ke - kb + p.kchunk - 1) / p.kchunk);
+  if (!e_phase)
+    return unimu ? launch_h<T, NC, PML, TFSF, EXACT, CORE, true> (p, maps, grid, block, smem, kb, ke, stream)
+                 : launch_h<T, NC, PML, TFSF, EXACT, CORE, false> (p, maps, grid, block, smem, kb, ke, stream);
   /* the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute */
-  static bool attr_e_dev[64] = {}, attr_h_dev[64] = {};
+  static bool attr_e_dev[64] = {};
   int dev = 0;
   cudaError_t de = cudaGetDevice (&dev);
   if (de != cudaSuccess) return de;
-  bool &attr_e = attr_e_dev[dev & 63], &attr_h = attr_h_dev[dev & 63];
-  if (e_phase)
+  if (!attr_e_dev[dev & 63])
   {
-    if (!attr_e)
-    {
-      cudaError_t e = cudaFuncSetAttribute (e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-      if (e != cudaSuccess) return e;
-      attr_e = true;
-    }
-    e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, smem, stream>>> (p, maps, kb, ke);
+    cudaError_t e = cudaFuncSetAttribute (e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_e_dev[dev & 63] = true;
   }
-  else
-  {
-    if (!attr_h)
-    {
-      cudaError_t e = cudaFuncSetAttribute (h_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-      if (e != cudaSuccess) return e;
-      attr_h = true;
-    }
-    h_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, smem, stream>>> (p, maps, kb, ke);
-  }
+  e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, smem, stream>>> (p, maps, kb, ke);
   return cudaGetLastError ();
 }
 
 template <typename T, int NC>
-cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, const TmaSet &maps, bool pml, bool tfsf, bool exact, bool core,
-                       int kb, int ke, cudaStream_t s)
+cudaError_t launch_nc (bool e_phase, bool unimu, const StepParams<T> &p, const TmaSet &maps, bool pml, bool tfsf, bool exact,
+                       bool core, int kb, int ke, cudaStream_t s)
 {
   if (core && pml && !exact)
-    return tfsf ? launch_t<T, NC, true, true, false, true> (e_phase, p, maps, kb, ke, s)
-                : launch_t<T, NC, true, false, false, true> (e_phase, p, maps, kb, ke, s);
+    return tfsf ? launch_t<T, NC, true, true, false, true> (e_phase, unimu, p, maps, kb, ke, s)
+                : launch_t<T, NC, true, false, false, true> (e_phase, unimu, p, maps, kb, ke, s);
   const int key = (pml ? 4 : 0) | (tfsf ? 2 : 0) | (exact ? 1 : 0);
   switch (key)
   {
-    case 0: return launch_t<T, NC, false, false, false> (e_phase, p, maps, kb, ke, s);
-    case 1: return launch_t<T, NC, false, false, true> (e_phase, p, maps, kb, ke, s);
-    case 2: return launch_t<T, NC, false, true, false> (e_phase, p, maps, kb, ke, s);
-    case 3: return launch_t<T, NC, false, true, true> (e_phase, p, maps, kb, ke, s);
-    case 4: return launch_t<T, NC, true, false, false> (e_phase, p, maps, kb, ke, s);
-    case 5: return launch_t<T, NC, true, false, true> (e_phase, p, maps, kb, ke, s);
-    case 6: return launch_t<T, NC, true, true, false> (e_phase, p, maps, kb, ke, s);
-    default: return launch_t<T, NC, true, true, true> (e_phase, p, maps, kb, ke, s);
+    case 0: return launch_t<T, NC, false, false, false> (e_phase, unimu, p, maps, kb, ke, s);
+    case 1: return launch_t<T, NC, false, false, true> (e_phase, unimu, p, maps, kb, ke, s);
+    case 2: return launch_t<T, NC, false, true, false> (e_phase, unimu, p, maps, kb, ke, s);
+    case 3: return launch_t<T, NC, false, true, true> (e_phase, unimu, p, maps, kb, ke, s);
+    case 4: return launch_t<T, NC, true, false, false> (e_phase, unimu, p, maps, kb, ke, s);
+    case 5: return launch_t<T, NC, true, false, true> (e_phase, unimu, p, maps, kb, ke, s);
+    case 6: return launch_t<T, NC, true, true, false> (e_phase, unimu, p, maps, kb, ke, s);
+    default: return launch_t<T, NC, true, true, true> (e_phase, unimu, p, maps, kb, ke, s);
   }
 }
 
@@ -936,14 +964,14 @@ void tma_tile_geometry (int value_type, int nc, bool alt, int *tile_cells_x, int
 
 template <typename T>
 cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
-                                 bool exact, bool core, int kb, int ke, cudaStream_t stream)
+                                 bool exact, bool core, bool uniform_mu, int kb, int ke, cudaStream_t stream)
 {
   const TmaSet &set = *reinterpret_cast<const TmaSet *> (e_phase ? maps.e : maps.h);
-  if (cplx) return launch_nc<T, 2> (e_phase, p, set, pml, tfsf, exact, core, kb, ke, stream);
-  return launch_nc<T, 1> (e_phase, p, set, pml, tfsf, exact, core, kb, ke, stream);
+  if (cplx) return launch_nc<T, 2> (e_phase, uniform_mu, p, set, pml, tfsf, exact, core, kb, ke, stream);
+  return launch_nc<T, 1> (e_phase, uniform_mu, p, set, pml, tfsf, exact, core, kb, ke, stream);
 }
 
-template cudaError_t launch_phase_3d_tma<float> (bool, const StepParams<float> &, const TmaMaps3D &, bool, bool, bool, bool, bool, int, int, cudaStream_t);
-template cudaError_t launch_phase_3d_tma<double> (bool, const StepParams<double> &, const TmaMaps3D &, bool, bool, bool, bool, bool, int, int, cudaStream_t);
+template cudaError_t launch_phase_3d_tma<float> (bool, const StepParams<float> &, const TmaMaps3D &, bool, bool, bool, bool, bool, bool, int, int, cudaStream_t);
+template cudaError_t launch_phase_3d_tma<double> (bool, const StepParams<double> &, const TmaMaps3D &, bool, bool, bool, bool, bool, bool, int, int, cudaStream_t);
 
 } /* namespace fdtd */

@@ -21,7 +21,8 @@ cudaError_t launch_phase_3d (bool e_phase, const StepParams<T> &p, bool cplx, bo
  * 128 bytes each) of one solver's arrays; tma_prepare_3d encodes them once the arrays are allocated.
  * `core` selects the variants that skip D / B inside the box p.core_lo .. p.core_hi (fast mode with UPML only).
  * The CORE and EXACT variants use another tile height than the plain fast ones (kernels3d_tma.cu, TileRows): `alt`
- * = exact || core tells tma_prepare_3d / tma_tile_geometry which; the maps must be encoded for the variant launched. */
+ * = exact || core tells tma_prepare_3d / tma_tile_geometry which; the maps must be encoded for the variant launched.
+ * `uniform_mu`: the mu array holds p.mu_const everywhere; the H kernels then do not load it. */
 struct TmaMaps3D
 {
   alignas (64) unsigned char e[13 * 128];
@@ -34,7 +35,7 @@ bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, bool alt,
                      int pitch, int ny, int planes, int pitchM, int planesM, std::string *err);
 template <typename T>
 cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
-                                 bool exact, bool core, int kb, int ke, cudaStream_t stream);
+                                 bool exact, bool core, bool uniform_mu, int kb, int ke, cudaStream_t stream);
 
 /* D (B) -= / += eps eps0 E (mu mu0 H) over the core box, for the six components (aux_kernels.cu): `fold` before
  * running the CORE variants, unfold before anything else reads or replaces D / B / E / H / eps / mu */

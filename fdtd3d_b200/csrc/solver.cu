@@ -99,6 +99,8 @@ struct fdtd_solver
 
   /* sigma-free core (kernels3d_tma.cu, CORE variants): box of cells whose D/B the time loop skips, and whether the
    * D/B arrays currently hold the folded representation D - eps eps0 E there (aux_kernels.cu, fold_aux_kernel) */
+  bool mu_uniform;      /* the mu array was last set with fdtd_fill: one value everywhere (UNIMU H kernels) */
+  double mu_value;
   bool core_allowed, core_on, folded;
   bool tma_alt;         /* tile configuration the tensor maps and kchunk were set up for (exact || core_on) */
   int core_lo[3], core_hi[3];
@@ -128,6 +130,7 @@ static StepParams<T> make_params (const fdtd_solver *s)
   for (int i = 0; i < 12; ++i) p.f[i] = (T *) s->f[i];
   p.eps = (const T *) s->eps;
   p.mu = (const T *) s->mu;
+  p.mu_const = (T) s->mu_value;
   for (int a = 0; a < 3; ++a)
     for (int k = 0; k < 2; ++k)
     {
@@ -407,7 +410,7 @@ static cudaError_t phase_3d (fdtd_solver *s, bool e_phase, const StepParams<T> &
 {
   const fdtd_config &c = s->cfg;
   const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode == 1;
-  if (s->use_tma) return launch_phase_3d_tma<T> (e_phase, p, s->tma, cplx, pml, tfsf, exact, s->core_on, kb, ke, S);
+  if (s->use_tma) return launch_phase_3d_tma<T> (e_phase, p, s->tma, cplx, pml, tfsf, exact, s->core_on, s->mu_uniform, kb, ke, S);
   return launch_phase_3d<T> (e_phase, p, cplx, pml, tfsf, exact, kb, ke, S);
 }
 
@@ -590,6 +593,7 @@ static int transfer (fdtd_solver *s, int field, void *host, int order, long long
   FieldInfo fi;
   rc = field_info (s, field, &fi);
   if (rc) return rc;
+  if (to_device && field == FDTD_MU) s->mu_uniform = false;
   /* uploads of anything the folded representation depends on, and reads of D / B, need the plain arrays */
   if (!fi.is_inc && (to_device || (field >= FDTD_DX && field <= FDTD_BZ)) && (rc = ensure_unfolded (s))) return rc;
   cudaStream_t S = s->s_compute;
@@ -910,6 +914,12 @@ int fdtd_fill (fdtd_handle s, int field, double re, double im)
   {
     double v[2] = { re, im };
     memcpy (pat, v, material || s->nc == 1 ? 8 : 16);
+  }
+  if (field == FDTD_MU)
+  {
+    /* the value as the array holds it (FPValue) */
+    s->mu_uniform = true;
+    s->mu_value = s->fp == 4 ? (double) (float) re : re;
   }
   CUDA_TRY (launch_fill (fi.dev, count, fi.cell, pat, s->s_compute));
   s->launches++;

@@ -5,11 +5,14 @@ import fdtd3d_b200 as F
 import oracle_lib as O
 
 
-def run_gpu(cfg, nsteps, inputs=None, fields=None, order=F.ORDER_REFERENCE, chunks=None):
-    """Mirror of oracle_lib.run(): same inputs, same output dict, computed by libfdtd3d_b200."""
+def run_gpu(cfg, nsteps, inputs=None, fields=None, order=F.ORDER_REFERENCE, chunks=None, fills=None):
+    """Mirror of oracle_lib.run(): same inputs, same output dict, computed by libfdtd3d_b200.
+    `fills`: {field: value} set with fdtd_fill instead of an upload (e.g. a homogeneous Mu)."""
     inputs = inputs or {}
     fields = fields or {}
     with F.Solver(cfg) as s:
+        for key, value in (fills or {}).items():
+            s.fill(key, value)
         for a in range(cfg.dims):
             key = "Sigma" + "XYZ"[a]
             if key in inputs:

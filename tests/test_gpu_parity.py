@@ -370,3 +370,32 @@ def test_sigma_free_core_with_all_zero_sigma():
     out = run_gpu(cfg, 8, inputs, fields)
     errs = family_rel_errs(out, ref, _keys(cfg))
     assert max(errs.values()) <= TOL[8], errs
+
+
+# ----------------------------------------------------------------------------- homogeneous mu (fdtd_fill): H kernels without the mu box
+
+@pytest.mark.parametrize("vt,cplx,use_tfsf", [(8, False, True), (8, True, True), (4, False, False), (4, True, True)])
+@pytest.mark.parametrize("mode", [1, 0, 2])
+def test_homogeneous_mu_set_with_fill(vt, cplx, use_tfsf, mode):
+    """A mu array set with fdtd_fill is known to hold one value: the H kernels then skip the material box.  Same
+    results as the oracle fed a full array of that value -- bit for bit in exact mode (the 4-point average of equal
+    values is exact) -- and the general path returns once mu is uploaded."""
+    size = (140, 40, 22) if (vt == 4 and not cplx) else (70, 26, 18)
+    cfg = O.make_config(size=size, pml=4, tfsf=6, use_pml=True, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx,
+                        theta=60, phi=30, psi=20, exact_mode=mode, source_pos=(size[0] // 2, size[1] // 2, size[2] // 2))
+    inputs, fields = random_inputs(cfg, seed=21)
+    mu = 1.5
+    inputs_ref = dict(inputs, Mu=np.full_like(inputs["Mu"], mu))
+    ref = O.run(cfg, 9, inputs_ref, fields)
+    out = run_gpu(cfg, 9, {k: v for k, v in inputs.items() if k != "Mu"}, fields, fills={"Mu": mu})
+    errs = family_rel_errs(out, ref, _keys(cfg))
+    for key in _keys(cfg):
+        if mode == 1 and (vt == 8 or not cplx):
+            assert np.array_equal(out[key], ref[key]), "%s not bit-exact: rel err %g" % (key, errs[key])
+        else:
+            assert errs[key] <= TOL[vt], (key, errs)
+    # fill, then upload a non-uniform mu: the general kernels must be back
+    ref2 = O.run(cfg, 5, inputs, fields)
+    out2 = run_gpu(cfg, 5, inputs, fields, fills={"Mu": mu})
+    errs2 = family_rel_errs(out2, ref2, _keys(cfg))
+    assert max(errs2.values()) <= (0 if mode == 1 and (vt == 8 or not cplx) else TOL[vt]), errs2
