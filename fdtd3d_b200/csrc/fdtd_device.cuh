@@ -47,6 +47,7 @@ struct StepParams
   T *f[12];
   const T *eps, *mu;
   T mu_const;           /* the value of mu when the whole array holds one value (UNIMU variants of the H kernels) */
+  T eps_const;          /* likewise for eps (TMz kernels) */
   CoefTab<T> tab[3][2]; /* [axis][kind] */
   T *einc, *hinc;       /* 1-D incident line, cells */
   T *face_tab;          /* TF/SF incident values of the face cells, 24 tables (kernels3d_common.cuh, tfsf_curl_tab) */

@@ -76,7 +76,9 @@ __device__ __forceinline__ T plain_coef (T m, const StepParams<T> &p)
 
 /* ------------------------------------------------------------------ Ez half step */
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
+/* UNI: the material array of the phase (eps for Ez, mu for Hx/Hy) holds one value (p.eps_const / p.mu_const, set with
+ * fdtd_fill): it is not loaded; (m + m) / 2 == m exactly, so exact mode is unaffected. */
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE, bool UNI>
 __global__ void __launch_bounds__ (TX)
 ez_phase_tmz (const __grid_constant__ StepParams<T> p)
 {
@@ -122,7 +124,13 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
     T hy_im[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) hy_im[c] = __ldg (Hy + o - NC + c);
-    MVec eps = ldv<T, V> (p.eps + om);
+    MVec eps;
+    if (UNI)
+    {
+#pragma unroll
+      for (int v = 0; v < V; ++v) eps.v[v] = p.eps_const;
+    }
+    else eps = ldv<T, V> (p.eps + om);
     FVec ez = ldv_rw<T, W> (Ez + o);
     FVec dz;
     if (PML && shell) dz = ldv_rw<T, W> (Dz + o);
@@ -268,7 +276,7 @@ __device__ __forceinline__ T tmz_first (bool plain, bool hx_form, T old, T ez1, 
   return fma_t<T> (cb, curl, plain ? old : ca * old);
 }
 
-template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
+template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE, bool UNI>
 __global__ void __launch_bounds__ (TX)
 h_phase_tmz (const __grid_constant__ StepParams<T> p)
 {
@@ -305,7 +313,13 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
   }
 
   FVec ez = ldv<T, W> (Ez + o);
-  MVec mu_c = ldv<T, V> (p.mu + om);
+  MVec mu_c;
+  if (UNI)
+  {
+#pragma unroll
+    for (int v = 0; v < V; ++v) mu_c.v[v] = p.mu_const;
+  }
+  else mu_c = ldv<T, V> (p.mu + om);
   const bool x_core = CORE && i0 >= p.core_lo[0] && i0 + V - 1 <= p.core_hi[0];
 
   for (int j = j0; j < j1; ++j, o += row, om += p.pitchM)
@@ -316,8 +330,13 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
     T ez_ip[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) ez_ip[c] = __ldg (Ez + o + W + c);
-    MVec mu_jp = ldv<T, V> (p.mu + om + p.pitchM);
-    T mu_ip = __ldg (p.mu + om + V);
+    MVec mu_jp = mu_c;
+    T mu_ip = p.mu_const;
+    if (!UNI)
+    {
+      mu_jp = ldv<T, V> (p.mu + om + p.pitchM);
+      mu_ip = __ldg (p.mu + om + V);
+    }
 
     FVec hx = ldv_rw<T, W> (Hx + o), hy = ldv_rw<T, W> (Hy + o);
     FVec bx, by;
@@ -423,32 +442,40 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
 }
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE = false>
-cudaError_t launch_t (bool e_phase, const StepParams<T> &p, cudaStream_t stream)
+cudaError_t launch_t (bool e_phase, bool uni, const StepParams<T> &p, cudaStream_t stream)
 {
   constexpr int V = 16 / (NC * (int) sizeof (T));
   dim3 block (TX);
   dim3 grid ((p.nx + TX * V - 1) / (TX * V), (p.ny + p.kchunk - 1) / p.kchunk);
-  if (e_phase) ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, 0, stream>>> (p);
-  else h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, 0, stream>>> (p);
+  if (e_phase)
+  {
+    if (uni) ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (p);
+    else ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (p);
+  }
+  else
+  {
+    if (uni) h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (p);
+    else h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (p);
+  }
   return cudaGetLastError ();
 }
 
 template <typename T, int NC>
-cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, bool pml, bool tfsf, bool exact, bool core, cudaStream_t s)
+cudaError_t launch_nc (bool e_phase, bool uni, const StepParams<T> &p, bool pml, bool tfsf, bool exact, bool core, cudaStream_t s)
 {
   if (core && pml && !exact)
-    return tfsf ? launch_t<T, NC, true, true, false, true> (e_phase, p, s) : launch_t<T, NC, true, false, false, true> (e_phase, p, s);
+    return tfsf ? launch_t<T, NC, true, true, false, true> (e_phase, uni, p, s) : launch_t<T, NC, true, false, false, true> (e_phase, uni, p, s);
   const int key = (pml ? 4 : 0) | (tfsf ? 2 : 0) | (exact ? 1 : 0);
   switch (key)
   {
-    case 0: return launch_t<T, NC, false, false, false> (e_phase, p, s);
-    case 1: return launch_t<T, NC, false, false, true> (e_phase, p, s);
-    case 2: return launch_t<T, NC, false, true, false> (e_phase, p, s);
-    case 3: return launch_t<T, NC, false, true, true> (e_phase, p, s);
-    case 4: return launch_t<T, NC, true, false, false> (e_phase, p, s);
-    case 5: return launch_t<T, NC, true, false, true> (e_phase, p, s);
-    case 6: return launch_t<T, NC, true, true, false> (e_phase, p, s);
-    default: return launch_t<T, NC, true, true, true> (e_phase, p, s);
+    case 0: return launch_t<T, NC, false, false, false> (e_phase, uni, p, s);
+    case 1: return launch_t<T, NC, false, false, true> (e_phase, uni, p, s);
+    case 2: return launch_t<T, NC, false, true, false> (e_phase, uni, p, s);
+    case 3: return launch_t<T, NC, false, true, true> (e_phase, uni, p, s);
+    case 4: return launch_t<T, NC, true, false, false> (e_phase, uni, p, s);
+    case 5: return launch_t<T, NC, true, false, true> (e_phase, uni, p, s);
+    case 6: return launch_t<T, NC, true, true, false> (e_phase, uni, p, s);
+    default: return launch_t<T, NC, true, true, true> (e_phase, uni, p, s);
   }
 }
 
@@ -456,13 +483,13 @@ cudaError_t launch_nc (bool e_phase, const StepParams<T> &p, bool pml, bool tfsf
 
 template <typename T>
 cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact, bool core,
-                              cudaStream_t stream)
+                              bool uniform_material, cudaStream_t stream)
 {
-  if (cplx) return launch_nc<T, 2> (e_phase, p, pml, tfsf, exact, core, stream);
-  return launch_nc<T, 1> (e_phase, p, pml, tfsf, exact, core, stream);
+  if (cplx) return launch_nc<T, 2> (e_phase, uniform_material, p, pml, tfsf, exact, core, stream);
+  return launch_nc<T, 1> (e_phase, uniform_material, p, pml, tfsf, exact, core, stream);
 }
 
-template cudaError_t launch_phase_tmz<float> (bool, const StepParams<float> &, bool, bool, bool, bool, bool, cudaStream_t);
-template cudaError_t launch_phase_tmz<double> (bool, const StepParams<double> &, bool, bool, bool, bool, bool, cudaStream_t);
+template cudaError_t launch_phase_tmz<float> (bool, const StepParams<float> &, bool, bool, bool, bool, bool, bool, cudaStream_t);
+template cudaError_t launch_phase_tmz<double> (bool, const StepParams<double> &, bool, bool, bool, bool, bool, bool, cudaStream_t);
 
 } /* namespace fdtd */

@@ -45,7 +45,7 @@ cudaError_t launch_fold_aux (const StepParams<T> &p, bool tmz, bool cplx, bool t
 /* 2D TMz half steps (kernels2d.cu) */
 template <typename T>
 cudaError_t launch_phase_tmz (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact, bool core,
-                              cudaStream_t stream);
+                              bool uniform_material, cudaStream_t stream);
 
 /* 1-D incident line: E update + source sample at cell 0, H update (aux_kernels.cu);
  * Scheme3D::performPlaneWaveESteps / HSteps, Scheme3D.cpp:24-82 */

@@ -101,6 +101,8 @@ struct fdtd_solver
    * D/B arrays currently hold the folded representation D - eps eps0 E there (aux_kernels.cu, fold_aux_kernel) */
   bool mu_uniform;      /* the mu array was last set with fdtd_fill: one value everywhere (UNIMU H kernels) */
   double mu_value;
+  bool eps_uniform;     /* likewise eps (TMz E kernel) */
+  double eps_value;
   bool core_allowed, core_on, folded;
   bool tma_alt;         /* tile configuration the tensor maps and kchunk were set up for (exact || core_on) */
   int core_lo[3], core_hi[3];
@@ -131,6 +133,7 @@ static StepParams<T> make_params (const fdtd_solver *s)
   p.eps = (const T *) s->eps;
   p.mu = (const T *) s->mu;
   p.mu_const = (T) s->mu_value;
+  p.eps_const = (T) s->eps_value;
   for (int a = 0; a < 3; ++a)
     for (int k = 0; k < 2; ++k)
     {
@@ -454,7 +457,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
     if (c.dims == 2)
     {
-      CUDA_TRY (launch_phase_tmz<T> (true, p, cplx, pml, tfsf, exact, s->core_on, S)); s->launches++;
+      CUDA_TRY (launch_phase_tmz<T> (true, p, cplx, pml, tfsf, exact, s->core_on, s->eps_uniform, S)); s->launches++;
     }
     else if (!multi)
     {
@@ -478,7 +481,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
     if (c.dims == 2)
     {
-      CUDA_TRY (launch_phase_tmz<T> (false, p, cplx, pml, tfsf, exact, s->core_on, S)); s->launches++;
+      CUDA_TRY (launch_phase_tmz<T> (false, p, cplx, pml, tfsf, exact, s->core_on, s->mu_uniform, S)); s->launches++;
     }
     else if (!multi)
     {
@@ -594,6 +597,7 @@ static int transfer (fdtd_solver *s, int field, void *host, int order, long long
   rc = field_info (s, field, &fi);
   if (rc) return rc;
   if (to_device && field == FDTD_MU) s->mu_uniform = false;
+  if (to_device && field == FDTD_EPS) s->eps_uniform = false;
   /* uploads of anything the folded representation depends on, and reads of D / B, need the plain arrays */
   if (!fi.is_inc && (to_device || (field >= FDTD_DX && field <= FDTD_BZ)) && (rc = ensure_unfolded (s))) return rc;
   cudaStream_t S = s->s_compute;
@@ -915,11 +919,12 @@ int fdtd_fill (fdtd_handle s, int field, double re, double im)
     double v[2] = { re, im };
     memcpy (pat, v, material || s->nc == 1 ? 8 : 16);
   }
-  if (field == FDTD_MU)
+  if (field == FDTD_MU || field == FDTD_EPS)
   {
     /* the value as the array holds it (FPValue) */
-    s->mu_uniform = true;
-    s->mu_value = s->fp == 4 ? (double) (float) re : re;
+    const double v = s->fp == 4 ? (double) (float) re : re;
+    if (field == FDTD_MU) { s->mu_uniform = true; s->mu_value = v; }
+    else { s->eps_uniform = true; s->eps_value = v; }
   }
   CUDA_TRY (launch_fill (fi.dev, count, fi.cell, pat, s->s_compute));
   s->launches++;
@@ -935,6 +940,7 @@ int fdtd_init_eps_sphere (fdtd_handle s, double cx, double cy, double cz, double
   int rc = sync_run (s);
   if (rc) return rc;
   if ((rc = ensure_unfolded (s))) return rc;
+  s->eps_uniform = false;
   if (s->fp == 4)
     CUDA_TRY (launch_eps_sphere<float> ((float *) s->eps, s->nx + 1, s->ny + 1, s->nzm, s->kz0, s->pitchM, s->psM, (float) cx, (float) cy, (float) cz, (float) radius, (float) eps_inside, s->s_compute));
   else

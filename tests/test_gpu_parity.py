@@ -399,3 +399,23 @@ def test_homogeneous_mu_set_with_fill(vt, cplx, use_tfsf, mode):
     out2 = run_gpu(cfg, 5, inputs, fields, fills={"Mu": mu})
     errs2 = family_rel_errs(out2, ref2, _keys(cfg))
     assert max(errs2.values()) <= (0 if mode == 1 and (vt == 8 or not cplx) else TOL[vt]), errs2
+
+
+@pytest.mark.parametrize("vt,cplx,use_tfsf", [(8, False, True), (4, False, False), (8, True, False)])
+@pytest.mark.parametrize("mode", [1, 0, 2])
+def test_homogeneous_materials_tmz(vt, cplx, use_tfsf, mode):
+    """2D TMz: eps and mu set with fdtd_fill (the reference's own TMz set-up is eps = mu = 1): neither array is loaded."""
+    size = (131, 47)
+    cfg = O.make_config(dims=2, size=size, pml=6, tfsf=9, use_pml=True, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx,
+                        exact_mode=mode, source_pos=(size[0] // 2, size[1] // 2, 0))
+    inputs, fields = random_inputs(cfg, seed=22)
+    eps, mu = 2.25, 1.5
+    inputs_ref = dict(inputs, Eps=np.full_like(inputs["Eps"], eps), Mu=np.full_like(inputs["Mu"], mu))
+    ref = O.run(cfg, 15, inputs_ref, fields)
+    out = run_gpu(cfg, 15, {k: v for k, v in inputs.items() if k not in ("Eps", "Mu")}, fields, fills={"Eps": eps, "Mu": mu})
+    errs = family_rel_errs(out, ref, _keys(cfg))
+    for key in _keys(cfg):
+        if mode == 1 and (vt == 8 or not cplx):
+            assert np.array_equal(out[key], ref[key]), "%s not bit-exact: rel err %g" % (key, errs[key])
+        else:
+            assert errs[key] <= TOL[vt], (key, errs)
