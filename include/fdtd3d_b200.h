@@ -146,7 +146,9 @@ int fdtd_set_sigma (fdtd_handle h, int axis, const void *profile, int64_t count)
 int fdtd_upload (fdtd_handle h, int field, const void *host, int order, int64_t z0, int64_t nz);
 int fdtd_download (fdtd_handle h, int field, void *host, int order, int64_t z0, int64_t nz);
 
-/* Sets every cell of a field to (re, im). */
+/* Sets every cell of a field to (re, im).  For FDTD_MU (and, with dims == 2, FDTD_EPS) this also tells the library that
+ * the material is homogeneous: until the array is uploaded again the kernels take the value from here instead of
+ * reading the array (same results, less memory traffic).  fdtd_create fills eps and mu with 1. */
 int fdtd_fill (fdtd_handle h, int field, double re, double im);
 
 /* eps := Approximation::approximateSphere (Source/Layout/Approximation.cpp:303-331) evaluated on
