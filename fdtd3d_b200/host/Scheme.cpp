@@ -34,7 +34,7 @@ void DeviceScheme::fail (const char *what) const
 }
 
 DeviceScheme::DeviceScheme (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType,
-                            bool complexValues, bool exactMode, int device)
+                            bool complexValues, int exactMode, int device)
   : yeeLayout (layout), handle (NULL), totalStep (tStep), lastRunMs (0)
 {
   memset (&cfg, 0, sizeof (cfg));
@@ -179,13 +179,13 @@ void DeviceScheme::dumpDat (const std::string &dir, const std::string &prefix)
 }
 
 Scheme3D::Scheme3D (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
-                    bool exactMode, int device)
+                    int exactMode, int device)
   : DeviceScheme (layout, tStep, doUsePML, doUseTFSF, valueType, complexValues, exactMode, device)
 {
 }
 
 SchemeTMz::SchemeTMz (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
-                      bool exactMode, int device)
+                      int exactMode, int device)
   : DeviceScheme (layout, tStep, doUsePML, doUseTFSF, valueType, complexValues, exactMode, device)
 {
   /* SchemeTMz.h:241-246: only phi = 0 and phi = 45 degrees are implemented for the TMz incident wave */

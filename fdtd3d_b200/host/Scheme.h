@@ -44,7 +44,7 @@ protected:
 
 public:
   DeviceScheme (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
-                bool exactMode, int device);
+                int exactMode, int device);
   ~DeviceScheme ();
 
   /* Scheme3D::initScheme (dx, sourceFreq) / SchemeTMz::initScheme: dt, frequency, relative phase velocity */
@@ -73,14 +73,14 @@ class Scheme3D : public DeviceScheme
 {
 public:
   Scheme3D (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
-            bool exactMode, int device);
+            int exactMode, int device);
 };
 
 class SchemeTMz : public DeviceScheme
 {
 public:
   SchemeTMz (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
-             bool exactMode, int device);
+             int exactMode, int device);
 };
 
 #endif /* FDTD3D_B200_HOST_SCHEME_H */

@@ -20,7 +20,7 @@ Settings::Settings ()
     doUseMetamaterials (false), doUseAmplitudeMode (false), gridStep (0.0005), sourceWaveLength (0.02),
     doSaveRes (false), doSaveMaterials (false), doSaveIntermediateRes (false), intermediateSaveStep (100),
     doSaveScatteredFieldRes (false), doSaveScatteredFieldIntermediate (false),
-    valueType ("d"), complexValues (false), exactMode (false), fastMode (false), printSettings (false), cudaDevice (0), startStep (0)
+    valueType ("d"), complexValues (false), exactMode (false), fastMode (false), keepAux (false), printSettings (false), cudaDevice (0), startStep (0)
 {
   buildTable ();
 }
@@ -94,7 +94,8 @@ void Settings::buildTable ()
   str ("--value-type", &valueType, "[fdtd3d_b200] floating point type of values: f or d (VALUE_TYPE of the reference's cmake)");
   flag ("--complex-values", &complexValues, "[fdtd3d_b200] complex field values (COMPLEX_FIELD_VALUES of the reference's cmake)");
   flag ("--exact", &exactMode, "[fdtd3d_b200] reference operand order, IEEE division, no FMA: bit-for-bit with the CPU solver");
-  flag ("--fast", &fastMode, "[fdtd3d_b200] reciprocal tables and FMA (default)");
+  flag ("--fast", &fastMode, "[fdtd3d_b200] reciprocal tables and FMA; D/B are not carried where all sigma are zero (default)");
+  flag ("--keep-aux", &keepAux, "[fdtd3d_b200] with --fast: carry D/B through every cell as the reference does");
   integer ("--cuda-device", &cudaDevice, "[fdtd3d_b200] CUDA device ordinal");
   flag ("--print-settings", &printSettings, "[fdtd3d_b200] print the parsed settings and exit");
   str ("--load-dat", &loadDatDir, "[fdtd3d_b200] directory with DAT dumps (current[<start-step>]_rank-0_<name>.dat) to resume from");

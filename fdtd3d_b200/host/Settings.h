@@ -76,7 +76,7 @@ public:
 
   /* additions */
   std::string valueType; /* "d" or "f" */
-  bool complexValues, exactMode, fastMode, printSettings;
+  bool complexValues, exactMode, fastMode, keepAux, printSettings;
   long long cudaDevice;
   std::string dumpDatDir, loadDatDir;
   long long startStep;

@@ -52,7 +52,7 @@ int main (int argc, char **argv)
   printf ("%s\n", info);
 
   const int vt = s.valueType == "f" ? 4 : 8;
-  const bool exact = s.exactMode && !s.fastMode;
+  const int exact = (s.exactMode && !s.fastMode) ? 1 : (s.keepAux ? 2 : 0); /* fdtd_config.exact_mode */
   DeviceScheme *scheme;
   if (dims == 2) scheme = new SchemeTMz (&yeeLayout, s.numTimeSteps, s.doUsePML, s.doUseTFSF, vt, s.complexValues, exact, (int) s.cudaDevice);
   else scheme = new Scheme3D (&yeeLayout, s.numTimeSteps, s.doUsePML, s.doUseTFSF, vt, s.complexValues, exact, (int) s.cudaDevice);

@@ -16,9 +16,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(ROOT, "fdtd3d_b200", "bin", "fdtd3d")
 
 
-@pytest.mark.parametrize("name", ["3d_d_pml_tfsf", "3d_d_pml_tfsf_angled", "3d_d_vacuum_src", "3d_dc_pml_tfsf", "3d_f_pml_tfsf",
-                                  "tmz_d_pml_src", "tmz_d_pml_tfsf", "tmz_f_pml_src"])
-def test_cli_run_matches_reference_dump(name, tmp_path):
+def _run_cli(name, tmp_path, mode_flags):
+    """Runs the binary on a golden case; returns (cfg, dumped fields, reference dump)."""
     meta, data = G.load(name)
     dims, vt, cplx = G.VARIANT[meta["variant"]]
     n = meta["size"]
@@ -27,7 +26,7 @@ def test_cli_run_matches_reference_dump(name, tmp_path):
         argv += ["--sizez", str(n[2])]
     argv += ["--pml-sizex", str(meta["pml"]), "--same-size-pml", "--tfsf-sizex", str(meta["tfsf"]), "--same-size-tfsf",
              "--time-steps", str(meta["steps"]), "--angle-teta", str(meta["theta"]), "--angle-phi", str(meta["phi"]),
-             "--angle-psi", str(meta["psi"]), "--value-type", "d" if vt == 8 else "f", "--exact", "--dump-dat", str(tmp_path)]
+             "--angle-psi", str(meta["psi"]), "--value-type", "d" if vt == 8 else "f", "--dump-dat", str(tmp_path)] + mode_flags
     if meta["use_pml"]:
         argv.append("--use-pml")
     if meta["use_tfsf"]:
@@ -38,14 +37,32 @@ def test_cli_run_matches_reference_dump(name, tmp_path):
     assert r.returncode == 0, r.stdout
     assert "Total time =" in r.stdout and "Grid size:" in r.stdout
     cfg = G.config_from_meta(meta)
-    keys = O.field_names(cfg)
     out = {}
-    for key in keys:
+    for key in O.field_names(cfg):
         path = tmp_path / ("current[%d]_rank-0_%s.dat" % (meta["steps"], key))
         out[key] = np.fromfile(str(path), dtype=O.field_dtype(cfg))
+    return cfg, out, data
+
+
+@pytest.mark.parametrize("name", ["3d_d_pml_tfsf", "3d_d_pml_tfsf_angled", "3d_d_vacuum_src", "3d_dc_pml_tfsf", "3d_f_pml_tfsf",
+                                  "tmz_d_pml_src", "tmz_d_pml_tfsf", "tmz_f_pml_src"])
+def test_cli_run_matches_reference_dump(name, tmp_path):
+    cfg, out, data = _run_cli(name, tmp_path, ["--exact"])
+    keys = O.field_names(cfg)
     errs = family_rel_errs(out, data, keys)
     for key in keys:
         assert np.array_equal(out[key], data[key]), (key, errs[key])  # exact mode: double and real float alike
+
+
+@pytest.mark.parametrize("name", ["3d_dc_pml_tfsf", "tmz_d_pml_tfsf", "tmz_f_pml_src"])
+@pytest.mark.parametrize("flags", [["--fast"], ["--fast", "--keep-aux"], []])
+def test_cli_fast_modes_within_tolerance_of_reference_dump(name, flags, tmp_path):
+    """The default (fast) arithmetic through the binary: D/B are not carried where sigma = 0 (these grids have such a
+    core) unless --keep-aux is given; every dumped field, D and B included, is within tolerance of the reference's dump."""
+    cfg, out, data = _run_cli(name, tmp_path, flags)
+    keys = O.field_names(cfg)
+    errs = family_rel_errs(out, data, keys)
+    assert max(errs.values()) <= (1e-12 if cfg.value_type == 8 else 1e-5), errs
 
 
 def test_cli_save_res_writes_the_scattered_field(tmp_path):
