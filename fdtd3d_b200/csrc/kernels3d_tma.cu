@@ -7,16 +7,18 @@
  *
  * The direct version keeps every in-flight byte in registers (19 x 16-byte loads per thread, > 200
  * registers, one 8-warp CTA per SM) and tops out at about two thirds of the HBM roofline because too few
- * bytes are in flight (profiles/r1_direct_*).  Here a CTA owns an (x, y) tile of 32*V x 8 cells and marches
+ * bytes are in flight (profiles/r1_direct_*).  Here a CTA owns an (x, y) tile of 32*V x TY cells and marches
  * along z; for each plane ONE elected thread issues one TMA box copy (cp.async.bulk.tensor.3d) per array
- * into a 4-deep ring of shared-memory stages (about 42 KB each), each stage completing on its own
- * mbarrier.  The boxes of the arrays whose neighbours the stencil needs carry a one-vector x halo and / or
- * a one-row y halo, so the y and x neighbours are read from shared memory and no value is fetched twice by
- * a CTA; the z neighbour is carried in registers from plane to plane.  Three stages (~125 KB per SM) are
- * in flight while one is being consumed, independent of register pressure.  Out-of-range parts of a box
- * (grid edges) are zero-filled by the TMA unit; results are written back with coalesced 128-bit stores.
+ * into a ring of shared-memory stages, each stage completing on its own mbarrier.  The boxes of the arrays
+ * whose neighbours the stencil needs carry a one-vector x halo and / or a one-row y halo, so the y and x
+ * neighbours are read from shared memory and no value is fetched twice by a CTA; the z neighbour is carried
+ * in registers from plane to plane.  All stages but the one being consumed are in flight, independent of
+ * register pressure.  Out-of-range parts of a box (grid edges) are zero-filled by the TMA unit; results are
+ * written back with coalesced 128-bit stores.  Tile height TY, ring depth and CTAs per SM depend on the
+ * variant (TileRows / Tile below): 8 rows x 4 stages x 1 CTA for the HBM-bound plain fast variants, 4 rows x
+ * 3 stages x 3 CTAs for the CORE and EXACT variants, 16 rows x 2 stages for real float.
  *
- * Tile geometry (V = cells per 16 bytes = 16 / sizeof(FieldValue)):
+ * Tile geometry (V = cells per 16 bytes = 16 / sizeof(FieldValue)), written for TY = 8:
  *   thread (tx, ty) owns cells [i0t + tx*V, +V) of row j0t + ty;  TXC = 32*V cells = 512 bytes per row.
  *   E phase stage for plane k:  Hz  (TXC+V) x 9 from (i0t-V, j0t-1)   Hy  (TXC+V) x 8 from (i0t-V, j0t)
  *                               Hx  TXC x 9 from (i0t, j0t-1)         D*, E*  TXC x 8
