@@ -58,7 +58,8 @@ def main():
         lines.append("")
         base = short.replace("_tma", "")
         targs = re.search(r"<(.*?)>\(", name)
-        if targs and len(targs.group(1).split(",")) == 6 and targs.group(1).split(",")[5].strip() in ("1", "(bool)1", "true"):
+        targ = [a.strip() for a in targs.group(1).split(",")] if targs else []
+        if len(targ) >= 6 and targ[5] in ("1", "(bool)1", "true"):  # <T, NC, PML, TFSF, EXACT, CORE[, UNIMU]>
             base += "_core"  # the variants that skip D/B in the sigma-free core
         js[base] = {"dram_bytes_per_launch": dram, "tag": tag, "kernel": name}
     open(os.path.join(ROOT, "profiles", tag + "_ncu_summary.md"), "w").write("\n".join(lines))
