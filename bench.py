@@ -304,7 +304,9 @@ def main():
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
             key = name + ("_core" if box else "")
-            traffic = prof.get(key, {}).get("dram_bytes_per_launch") if args.workload == "c3" and args.exact != 1 else None
+            # ncu captures exist for c3 (default mode and exact_mode 2) and for c2's default mode
+            have = (args.workload == "c3" and args.exact != 1) or (args.workload == "c2" and args.exact == 0)
+            traffic = prof.get(key, {}).get("dram_bytes_per_launch") if have else None
         except Exception:
             pass
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
