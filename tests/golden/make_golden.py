@@ -44,6 +44,11 @@ CASES = {
     "tmz_dc_pml_tfsf":      ("tmz_dc", 96, 80, 1, 8, 14, 60, 1, 1, 90, 0, 90),
     "tmz_f_pml_src":        ("tmz_f", 96, 80, 1, 8, 14, 60, 1, 0, 90, 0, 90),
     "tmz_f_pml_tfsf":       ("tmz_f", 96, 80, 1, 8, 14, 60, 1, 1, 90, 0, 90),
+    # large enough for a sigma-free core box in the kernels' tile granularity: fast mode is then compared
+    # with the reference itself where it skips D/B, not only with the oracle
+    "3d_d_pml_tfsf_core":   ("3d_d", 48, 36, 28, 5, 9, 30, 1, 1, 60, 30, 45),
+    "3d_d_pml_src_core":    ("3d_d", 48, 36, 28, 5, 9, 30, 1, 0, 90, 0, 90),
+    "3d_f_pml_src_core":    ("3d_f", 72, 40, 20, 4, 8, 30, 1, 0, 90, 0, 90),
     # --save-res: the reference subtracts the incident field inside the TF/SF box before saving (Scheme3D.cpp:2767-2921)
     "3d_d_pml_tfsf_saveres": ("3d_d", 30, 28, 26, 5, 8, 40, 1, 1, 70, 40, 55, "saveres"),
 }
