@@ -11,3 +11,13 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _built_artefacts():
+    """The built artefacts are not in the repository: build what is missing (nvcc cross-compiles without a GPU).
+    The oracle library builds itself on first use (tests/oracle_lib.py)."""
+    need = [os.path.join(ROOT, "fdtd3d_b200", "libfdtd3d_b200.so"), os.path.join(ROOT, "fdtd3d_b200", "bin", "fdtd3d")]
+    if not all(os.path.exists(p) for p in need):
+        from fdtd3d_b200 import build as b
+        b.build()
