@@ -204,6 +204,13 @@ class Solver:
         _check(lib().fdtd_sync(self._h))
 
     @property
+    def busy(self):
+        """True while queued steps are still running (fdtd_busy; does not wait)."""
+        b = C.c_int()
+        _check(lib().fdtd_busy(self._h, C.byref(b)))
+        return bool(b.value)
+
+    @property
     def last_run_ms(self):
         ms = C.c_float()
         _check(lib().fdtd_last_run_ms(self._h, C.byref(ms)))

@@ -109,7 +109,7 @@ __device__ __forceinline__ T plain_cell (T old, T curl, T cb)
  *   H_a: own axis in [L, R-1];   normal: low = L-1, high = R-1; remaining axis in [L-1, R-1]
  */
 template <typename T>
-__device__ __forceinline__ int tfsf_e_faces (const StepParams<T> &p, int a, int i, int j, int k)
+__host__ __device__ __forceinline__ int tfsf_e_faces (const StepParams<T> &p, int a, int i, int j, int k)
 {
   const int pos[3] = { i, j, k };
   const int b = (a + 1) % 3, c = (a + 2) % 3;
@@ -120,7 +120,7 @@ __device__ __forceinline__ int tfsf_e_faces (const StepParams<T> &p, int a, int 
   return f;
 }
 template <typename T>
-__device__ __forceinline__ int tfsf_h_faces (const StepParams<T> &p, int a, int i, int j, int k)
+__host__ __device__ __forceinline__ int tfsf_h_faces (const StepParams<T> &p, int a, int i, int j, int k)
 {
   const int pos[3] = { i, j, k };
   const int b = (a + 1) % 3, c = (a + 2) % 3;

@@ -32,37 +32,39 @@ struct NcclApi
 
 enum { NCCL_INT8 = 0 }; /* ncclInt8 / ncclChar */
 
-/* Returns NULL (and sets *why) if NCCL cannot be loaded. */
-inline const NcclApi *nccl_api (const char **why)
+struct NcclLoad
 {
-  static NcclApi api;
-  static bool tried = false, ok = false;
-  static const char *err = "";
-  if (!tried)
+  NcclApi api;
+  const char *err;
+  bool ok;
+  NcclLoad () : err (""), ok (false)
   {
-    tried = true;
     api.lib = dlopen ("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!api.lib) api.lib = dlopen ("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
-    if (!api.lib) err = "cannot dlopen libnccl.so.2";
-    else
-    {
+    if (!api.lib) { err = "cannot dlopen libnccl.so.2"; return; }
 #define FDTD_NCCL_SYM(field, name) \
   *(void **) (&api.field) = dlsym (api.lib, name); \
   if (!api.field) err = "libnccl lacks " name;
-      FDTD_NCCL_SYM (GetUniqueId, "ncclGetUniqueId")
-      FDTD_NCCL_SYM (CommInitRank, "ncclCommInitRank")
-      FDTD_NCCL_SYM (CommDestroy, "ncclCommDestroy")
-      FDTD_NCCL_SYM (Send, "ncclSend")
-      FDTD_NCCL_SYM (Recv, "ncclRecv")
-      FDTD_NCCL_SYM (GroupStart, "ncclGroupStart")
-      FDTD_NCCL_SYM (GroupEnd, "ncclGroupEnd")
-      FDTD_NCCL_SYM (GetErrorString, "ncclGetErrorString")
+    FDTD_NCCL_SYM (GetUniqueId, "ncclGetUniqueId")
+    FDTD_NCCL_SYM (CommInitRank, "ncclCommInitRank")
+    FDTD_NCCL_SYM (CommDestroy, "ncclCommDestroy")
+    FDTD_NCCL_SYM (Send, "ncclSend")
+    FDTD_NCCL_SYM (Recv, "ncclRecv")
+    FDTD_NCCL_SYM (GroupStart, "ncclGroupStart")
+    FDTD_NCCL_SYM (GroupEnd, "ncclGroupEnd")
+    FDTD_NCCL_SYM (GetErrorString, "ncclGetErrorString")
 #undef FDTD_NCCL_SYM
-      ok = err[0] == 0;
-    }
+    ok = err[0] == 0;
   }
-  if (why) *why = err;
-  return ok ? &api : NULL;
+};
+
+/* Returns NULL (and sets *why) if NCCL cannot be loaded.  The function-local static is initialised exactly once, also
+ * when several threads create solvers at the same time (C++11 guarantees it). */
+inline const NcclApi *nccl_api (const char **why)
+{
+  static const NcclLoad load;
+  if (why) *why = load.err;
+  return load.ok ? &load.api : NULL;
 }
 
 } /* namespace fdtd */

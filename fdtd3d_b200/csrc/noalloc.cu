@@ -88,7 +88,10 @@ sumsq_combine (const double *partials, int n, double *out)
 /* Device address of g_partials on the CURRENT device, looked up once per device and remembered.  The name
  * g_partials cannot be handed to a kernel from host code: there it stands for the host-side shadow of the
  * symbol, so a kernel would fault on it or, on systems where the GPU can reach host memory, quietly use
- * the wrong storage.  cudaGetSymbolAddress translates it for the device that is current when it is called. */
+ * the wrong storage.  cudaGetSymbolAddress translates it for the device that is current when it is called.
+ * The remembered address belongs to the device's current primary context: cudaDeviceReset (or anything else that
+ * tears that context down) unloads the module, and the address is then stale -- this entry point must not be used
+ * across such a reset (include/fdtd3d_b200.h says so). */
 cudaError_t scratch_for_device (int device, double **out)
 {
   static std::mutex lock;
@@ -142,19 +145,32 @@ extern "C" int fdtd_sumsq_noalloc (const void *dev_in, int value_type, int64_t c
     return FDTD_ERROR;
   }
 
+  /* cudaLaunchKernel hands back the status of THIS launch, so an older, unrelated error that the application has
+   * not yet collected with cudaGetLastError is neither blamed on this call nor cleared by it, and a failure of the
+   * first pass is seen before the second pass is queued. */
   cudaStream_t stream = (cudaStream_t) cuda_stream;
-  const int nblocks = (int) ((count + CHUNK - 1) / CHUNK);
+  int nblocks = (int) ((count + CHUNK - 1) / CHUNK);
+  long long n = count;
   if (nblocks > 0)
   {
-    if (value_type == 4) sumsq_chunks<float><<<nblocks, THREADS, 0, stream>>> ((const float *) dev_in, count, partials);
-    else sumsq_chunks<double><<<nblocks, THREADS, 0, stream>>> ((const double *) dev_in, count, partials);
+    void *args[] = { (void *) &dev_in, (void *) &n, (void *) &partials };
+    const void *fn = value_type == 4 ? (const void *) sumsq_chunks<float> : (const void *) sumsq_chunks<double>;
+    e = cudaLaunchKernel (fn, dim3 (nblocks), dim3 (THREADS), args, 0, stream);
+    if (e != cudaSuccess)
+    {
+      if (errbuf && errbuf_len > 0) snprintf (errbuf, (size_t) errbuf_len, "fdtd_sumsq_noalloc: launch of the partial-sum pass failed: %s", cudaGetErrorString (e));
+      return FDTD_ERROR;
+    }
   }
-  sumsq_combine<<<1, THREADS, 0, stream>>> (partials, nblocks, dev_out);
-  e = cudaGetLastError ();
-  if (e != cudaSuccess)
   {
-    if (errbuf && errbuf_len > 0) snprintf (errbuf, (size_t) errbuf_len, "fdtd_sumsq_noalloc: kernel launch failed: %s", cudaGetErrorString (e));
-    return FDTD_ERROR;
+    const double *cpartials = partials;
+    void *args[] = { (void *) &cpartials, (void *) &nblocks, (void *) &dev_out };
+    e = cudaLaunchKernel ((const void *) sumsq_combine, dim3 (1), dim3 (THREADS), args, 0, stream);
+    if (e != cudaSuccess)
+    {
+      if (errbuf && errbuf_len > 0) snprintf (errbuf, (size_t) errbuf_len, "fdtd_sumsq_noalloc: launch of the combining pass failed: %s", cudaGetErrorString (e));
+      return FDTD_ERROR;
+    }
   }
   return FDTD_OK;
 }

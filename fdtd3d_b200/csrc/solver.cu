@@ -20,6 +20,7 @@
 
 #include "../../include/fdtd3d_b200.h"
 #include "fdtd_device.cuh"
+#include "kernels3d_common.cuh"
 #include "launch.h"
 #include "nccl_dl.h"
 
@@ -81,8 +82,11 @@ struct fdtd_solver
   long long face_stride;
   void *tab_mem;     /* all coefficient tables, one allocation */
   size_t tab_stride; /* bytes between tables */
-  void *src;         /* source samples */
+  void *src;         /* source samples of the run being executed (device) */
   long long src_capacity;
+  char *src_ring;    /* pinned host ring the samples of queued runs are copied from (fdtd_run_async never waits for it
+                        unless more samples are queued than it holds) */
+  size_t src_ring_bytes, src_ring_head, src_ring_used;
   void *staging;     /* layout-conversion scratch */
   size_t staging_bytes;
   double *red_partials, *red_out; /* reduction scratch */
@@ -90,8 +94,11 @@ struct fdtd_solver
   std::vector<double> sigma[3]; /* profiles as given (FPValue-valued) */
 
   cudaStream_t s_compute, s_comm;
-  cudaEvent_t ev_start, ev_stop, ev_eb, ev_ex, ev_hb, ev_hx;
+  cudaEvent_t ev_eb, ev_ex, ev_hb, ev_hx;
+  std::vector<cudaEvent_t> run_ev; /* a (start, stop) pair per run queued since the last synchronisation */
+  int runs_pending;
   NcclComm comm;
+  bool comm_failed;   /* a send / recv of the halo exchange failed: the handle refuses further multi-rank runs */
 
   TmaMaps3D tma;        /* tensor maps of the TMA-staged 3D kernels */
   bool use_tma;
@@ -115,7 +122,6 @@ struct fdtd_solver
   long long t;          /* next time step index */
   long long launches;
   float last_ms;
-  bool run_pending;
 };
 
 namespace fdtd
@@ -247,15 +253,43 @@ template <typename T>
 static int upload_source (fdtd_solver *s, long long n)
 {
   const fdtd_config &c = s->cfg;
+  const size_t bytes = (size_t) n * s->cell;
+  /* The samples are written into a pinned ring and copied from there in stream order, so queueing a run does not
+   * wait for the runs before it.  Only when the ring cannot take the new samples beside those of the runs still
+   * queued, or the device table has to grow, the stream is drained first. */
+  if (n > s->src_capacity || bytes > s->src_ring_bytes - s->src_ring_used)
+  {
+    CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+    s->src_ring_head = s->src_ring_used = 0;
+  }
   if (n > s->src_capacity)
   {
     if (s->src) cudaFree (s->src);
     s->src = NULL;
     s->src_capacity = 0;
-    CUDA_TRY (cudaMalloc (&s->src, (size_t) n * s->cell));
+    CUDA_TRY (cudaMalloc (&s->src, bytes));
     s->src_capacity = n;
   }
-  std::vector<T> host ((size_t) n * s->nc);
+  if (bytes > s->src_ring_bytes)
+  {
+    if (s->src_ring) cudaFreeHost (s->src_ring);
+    s->src_ring = NULL;
+    s->src_ring_bytes = 0;
+    CUDA_TRY (cudaHostAlloc ((void **) &s->src_ring, bytes, cudaHostAllocDefault));
+    s->src_ring_bytes = bytes;
+  }
+  if (s->src_ring_head + bytes > s->src_ring_bytes)
+  {
+    /* no wrap inside one run: skip the tail (it counts as used until the next drain) */
+    s->src_ring_used += s->src_ring_bytes - s->src_ring_head;
+    s->src_ring_head = 0;
+    if (bytes > s->src_ring_bytes - s->src_ring_used)
+    {
+      CUDA_TRY (cudaStreamSynchronize (s->s_compute));
+      s->src_ring_used = 0;
+    }
+  }
+  T *host = reinterpret_cast<T *> (s->src_ring + s->src_ring_head);
   const T dt = (T) c.dt, freq = (T) c.source_frequency;
   for (long long i = 0; i < n; ++i)
   {
@@ -264,8 +298,9 @@ static int upload_source (fdtd_solver *s, long long n)
     host[(size_t) i * s->nc] = (T) ::sin ((double) arg);
     if (s->nc == 2) host[(size_t) i * 2 + 1] = (T) ::cos ((double) arg);
   }
-  CUDA_TRY (cudaMemcpyAsync (s->src, host.data (), host.size () * sizeof (T), cudaMemcpyHostToDevice, s->s_compute));
-  CUDA_TRY (cudaStreamSynchronize (s->s_compute)); /* host vector goes out of scope */
+  CUDA_TRY (cudaMemcpyAsync (s->src, host, bytes, cudaMemcpyHostToDevice, s->s_compute));
+  s->src_ring_head += bytes;
+  s->src_ring_used += bytes;
   return FDTD_OK;
 }
 
@@ -278,16 +313,20 @@ static int exchange (fdtd_solver *s, bool h_fields)
   const char *why = NULL;
   const NcclApi *nccl = nccl_api (&why);
   if (!nccl || !s->comm) return fail (FDTD_COMM_ERROR, "halo exchange without a communicator (%s)", why ? why : "");
+  if (s->comm_failed) return fail (FDTD_COMM_ERROR, "an earlier halo exchange of this handle failed: destroy it");
   const size_t plane_bytes = (size_t) s->ps * s->cell;
   const int r = s->cfg.rank, n = s->cfg.nranks;
   NCCL_TRY (nccl->GroupStart ());
+  /* a failure inside the group must still close it, or the group stays open on this thread */
+  int rc = 0;
+#define IN_GROUP(expr) do { if (!rc) rc = (expr); } while (0)
   if (h_fields)
   {
     for (int f = FDTD_HX; f <= FDTD_HY; ++f)
     {
       char *base = (char *) s->f[f];
-      if (r + 1 < n) NCCL_TRY (nccl->Send (base + (size_t) s->nzl * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
-      if (r > 0) NCCL_TRY (nccl->Recv (base, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
+      if (r + 1 < n) IN_GROUP (nccl->Send (base + (size_t) s->nzl * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
+      if (r > 0) IN_GROUP (nccl->Recv (base, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
     }
   }
   else
@@ -295,11 +334,18 @@ static int exchange (fdtd_solver *s, bool h_fields)
     for (int f = FDTD_EX; f <= FDTD_EY; ++f)
     {
       char *base = (char *) s->f[f];
-      if (r > 0) NCCL_TRY (nccl->Send (base + plane_bytes, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
-      if (r + 1 < n) NCCL_TRY (nccl->Recv (base + (size_t) (s->nzl + 1) * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
+      if (r > 0) IN_GROUP (nccl->Send (base + plane_bytes, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
+      if (r + 1 < n) IN_GROUP (nccl->Recv (base + (size_t) (s->nzl + 1) * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
     }
   }
-  NCCL_TRY (nccl->GroupEnd ());
+#undef IN_GROUP
+  const int rc_end = nccl->GroupEnd ();
+  if (!rc) rc = rc_end;
+  if (rc)
+  {
+    s->comm_failed = true; /* later runs refuse cleanly instead of waiting on half-wired events */
+    return fail (FDTD_COMM_ERROR, "halo exchange failed: %s", nccl->GetErrorString (rc));
+  }
   return FDTD_OK;
 }
 
@@ -508,21 +554,23 @@ static int run_async (fdtd_solver *s, long long nsteps)
 {
   if (nsteps < 0) return fail (FDTD_INVALID_ARGUMENT, "nsteps < 0");
   CUDA_TRY (cudaSetDevice (s->cfg.device));
-  if (s->run_pending)
-  {
-    CUDA_TRY (cudaStreamSynchronize (s->s_compute));
-    s->run_pending = false;
-  }
-  if (nsteps == 0) { s->last_ms = 0; return FDTD_OK; }
+  if (nsteps == 0) { if (!s->runs_pending) s->last_ms = 0; return FDTD_OK; }
   int rc = s->fp == 4 ? upload_source<float> (s, nsteps) : upload_source<double> (s, nsteps);
   if (rc) return rc;
-  CUDA_TRY (cudaEventRecord (s->ev_start, s->s_compute));
+  /* every queued run has its own (start, stop) events, so runs can be queued back to back */
+  while ((int) s->run_ev.size () < 2 * (s->runs_pending + 1))
+  {
+    cudaEvent_t e;
+    CUDA_TRY (cudaEventCreate (&e));
+    s->run_ev.push_back (e);
+  }
+  CUDA_TRY (cudaEventRecord (s->run_ev[2 * s->runs_pending], s->s_compute));
   if (s->core_on && !s->folded && (rc = fold_core (s, true))) return rc;
   rc = s->fp == 4 ? enqueue_steps<float> (s, nsteps) : enqueue_steps<double> (s, nsteps);
   if (rc) return rc;
-  CUDA_TRY (cudaEventRecord (s->ev_stop, s->s_compute));
+  CUDA_TRY (cudaEventRecord (s->run_ev[2 * s->runs_pending + 1], s->s_compute));
   s->t += nsteps;
-  s->run_pending = true;
+  s->runs_pending++;
   return FDTD_OK;
 }
 
@@ -530,10 +578,13 @@ static int sync_run (fdtd_solver *s)
 {
   CUDA_TRY (cudaSetDevice (s->cfg.device));
   CUDA_TRY (cudaStreamSynchronize (s->s_compute));
-  if (s->run_pending)
+  s->src_ring_head = s->src_ring_used = 0;
+  if (s->runs_pending)
   {
-    CUDA_TRY (cudaEventElapsedTime (&s->last_ms, s->ev_start, s->ev_stop));
-    s->run_pending = false;
+    /* the time of the run queued last; with several runs queued, also what they took together */
+    const int last = s->runs_pending - 1;
+    CUDA_TRY (cudaEventElapsedTime (&s->last_ms, s->run_ev[2 * last], s->run_ev[2 * last + 1]));
+    s->runs_pending = 0;
     s->prof_e_ms = s->prof_h_ms = 0;
     for (long long n = 0; n < s->prof_steps; ++n)
     {
@@ -618,23 +669,38 @@ static int transfer (fdtd_solver *s, int field, void *host, int order, long long
   char *h = (char *) host;
   if (order == FDTD_ORDER_REFERENCE)
   {
+    /* Only the planes of [z0, z0 + nz) that this rank owns move, in either direction: the host block may be a
+     * whole-grid buffer that other ranks fill beside this one, so nothing outside the slab is read or written.
+     * Buffer planes [ka, kb) are the owned ones; they are staged as a compact k-fastest block of kb - ka planes. */
+    long long ka = s->kz0 - z0, kb = (long long) s->kz0 + fi.nzl_planes - z0;
+    if (ka < 0) ka = 0;
+    if (kb > nz) kb = nz;
+    if (kb <= ka) return FDTD_OK;
+    const long long nzo = kb - ka;
+    const bool whole = nzo == nz;
     /* chunks of i-rows of the k-fastest host block */
-    const size_t row_bytes = (size_t) fi.ny * nz * fi.cell;
+    const size_t row_bytes = (size_t) fi.ny * nzo * fi.cell;   /* staged */
+    const size_t host_row = (size_t) fi.ny * nz * fi.cell;     /* in the caller's block */
     long long rows_per_chunk = (long long) (s->staging_bytes / row_bytes);
     if (rows_per_chunk < 1) return fail (FDTD_INVALID_ARGUMENT, "one i-row (%zu bytes) exceeds the staging buffer", row_bytes);
+    const int kofs_o = kofs + (int) ka;
     for (long long ia = 0; ia < fi.nx; ia += rows_per_chunk)
     {
       const long long ib = ia + rows_per_chunk < fi.nx ? ia + rows_per_chunk : fi.nx;
       const size_t bytes = (size_t) (ib - ia) * row_bytes;
+      char *hp = h + (size_t) ia * host_row + (size_t) ka * fi.cell;
+      const size_t w = (size_t) nzo * fi.cell, hpitch = (size_t) nz * fi.cell, lines = (size_t) (ib - ia) * fi.ny;
       if (to_device)
       {
-        CUDA_TRY (cudaMemcpyAsync (s->staging, h + (size_t) ia * row_bytes, bytes, cudaMemcpyHostToDevice, S));
-        CUDA_TRY (launch_reorder (true, fi.dev, s->staging, fi.cell, (int) ia, (int) ib, fi.ny, (int) nz, fi.pitch, fi.ps, kofs, kmin, kmax, S));
+        if (whole) CUDA_TRY (cudaMemcpyAsync (s->staging, hp, bytes, cudaMemcpyHostToDevice, S));
+        else CUDA_TRY (cudaMemcpy2DAsync (s->staging, w, hp, hpitch, w, lines, cudaMemcpyHostToDevice, S));
+        CUDA_TRY (launch_reorder (true, fi.dev, s->staging, fi.cell, (int) ia, (int) ib, fi.ny, (int) nzo, fi.pitch, fi.ps, kofs_o, kmin, kmax, S));
       }
       else
       {
-        CUDA_TRY (launch_reorder (false, fi.dev, s->staging, fi.cell, (int) ia, (int) ib, fi.ny, (int) nz, fi.pitch, fi.ps, kofs, kmin, kmax, S));
-        CUDA_TRY (cudaMemcpyAsync (h + (size_t) ia * row_bytes, s->staging, bytes, cudaMemcpyDeviceToHost, S));
+        CUDA_TRY (launch_reorder (false, fi.dev, s->staging, fi.cell, (int) ia, (int) ib, fi.ny, (int) nzo, fi.pitch, fi.ps, kofs_o, kmin, kmax, S));
+        if (whole) CUDA_TRY (cudaMemcpyAsync (hp, s->staging, bytes, cudaMemcpyDeviceToHost, S));
+        else CUDA_TRY (cudaMemcpy2DAsync (hp, hpitch, s->staging, w, w, lines, cudaMemcpyDeviceToHost, S));
       }
       s->launches++;
       CUDA_TRY (cudaStreamSynchronize (S));
@@ -751,8 +817,8 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
 
   CREATE_TRY (cudaStreamCreateWithFlags (&s->s_compute, cudaStreamNonBlocking));
   CREATE_TRY (cudaStreamCreateWithFlags (&s->s_comm, cudaStreamNonBlocking));
-  CREATE_TRY (cudaEventCreate (&s->ev_start));
-  CREATE_TRY (cudaEventCreate (&s->ev_stop));
+  s->src_ring_bytes = (size_t) 1 << 20; /* 65536 complex-double samples queued at a time */
+  CREATE_TRY (cudaHostAlloc ((void **) &s->src_ring, s->src_ring_bytes, cudaHostAllocDefault));
   CREATE_TRY (cudaEventCreateWithFlags (&s->ev_eb, cudaEventDisableTiming));
   CREATE_TRY (cudaEventCreateWithFlags (&s->ev_ex, cudaEventDisableTiming));
   CREATE_TRY (cudaEventCreateWithFlags (&s->ev_hb, cudaEventDisableTiming));
@@ -858,8 +924,10 @@ int fdtd_destroy (fdtd_handle s)
   for (int f = 0; f < 12; ++f) if (s->f[f]) cudaFree (s->f[f]);
   void *ptrs[] = { s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->staging, s->red_partials, s->red_out };
   for (void *p : ptrs) if (p) cudaFree (p);
-  cudaEvent_t evs[] = { s->ev_start, s->ev_stop, s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx };
+  cudaEvent_t evs[] = { s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx };
   for (cudaEvent_t e : evs) if (e) cudaEventDestroy (e);
+  for (cudaEvent_t e : s->run_ev) cudaEventDestroy (e);
+  if (s->src_ring) cudaFreeHost (s->src_ring);
   for (cudaEvent_t e : s->prof_ev) cudaEventDestroy (e);
   if (s->s_compute) cudaStreamDestroy (s->s_compute);
   if (s->s_comm) cudaStreamDestroy (s->s_comm);
@@ -974,6 +1042,16 @@ int fdtd_run_async (fdtd_handle s, int64_t nsteps)
   return run_async (s, nsteps);
 }
 
+int fdtd_busy (fdtd_handle s, int *busy)
+{
+  if (!s || !busy) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  const cudaError_t q = cudaStreamQuery (s->s_compute);
+  if (q != cudaSuccess && q != cudaErrorNotReady) return fail (FDTD_ERROR, "cudaStreamQuery failed: %s", cudaGetErrorString (q));
+  *busy = q == cudaErrorNotReady;
+  return FDTD_OK;
+}
+
 int fdtd_sync (fdtd_handle s)
 {
   if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
@@ -1046,6 +1124,37 @@ int fdtd_plan_core_box (const fdtd_config *cfg, const void *const sigma[3], int6
   const bool on = cfg->use_pml && cfg->exact_mode == 0
                   && compute_core_box (cfg->dims, cfg->value_type, cfg->complex_values ? 2 : 1, sg, l, h);
   for (int a = 0; a < 3; ++a) { lo[a] = on ? l[a] : 0; hi[a] = on ? h[a] : -1; }
+  return FDTD_OK;
+}
+
+int fdtd_tfsf_face_masks (const fdtd_config *cfg, int field, uint8_t *out, int64_t count)
+{
+  if (!out) return fail (FDTD_INVALID_ARGUMENT, "NULL output");
+  int rc = validate (cfg);
+  if (rc) return rc;
+  if (cfg->dims != 3 || !cfg->use_tfsf) return fail (FDTD_INVALID_ARGUMENT, "the face boxes belong to a 3D scheme with use_tfsf");
+  if (field < FDTD_EX || field > FDTD_HZ) return fail (FDTD_INVALID_ARGUMENT, "field %d is not one of Ex..Hz", field);
+  const int nx = (int) cfg->size[0], ny = (int) cfg->size[1], nz = (int) cfg->size[2];
+  if (count != (int64_t) nx * ny * nz) return fail (FDTD_INVALID_ARGUMENT, "count %lld, grid has %lld cells", (long long) count, (long long) nx * ny * nz);
+  /* the very functions the half-step kernels evaluate (kernels3d_common.cuh), run on the host */
+  StepParams<double> p;
+  memset (&p, 0, sizeof (p));
+  for (int a = 0; a < 3; ++a) { p.L[a] = (int) cfg->tfsf_size[a]; p.R[a] = (int) (cfg->size[a] - cfg->tfsf_size[a]); }
+  const bool is_e = field <= FDTD_EZ;
+  const int a = field % 3, b = (a + 1) % 3, c = (a + 2) % 3;
+  for (int i = 0; i < nx; ++i)
+    for (int j = 0; j < ny; ++j)
+      for (int k = 0; k < nz; ++k)
+      {
+        const int f = is_e ? k3d::tfsf_e_faces (p, a, i, j, k) : k3d::tfsf_h_faces (p, a, i, j, k);
+        /* relative bits (low / high face normal to b, then to c) -> LayoutDirection bits (2 * axis + high) */
+        int m = 0;
+        if (f & 1) m |= 1 << (2 * b);
+        if (f & 2) m |= 1 << (2 * b + 1);
+        if (f & 4) m |= 1 << (2 * c);
+        if (f & 8) m |= 1 << (2 * c + 1);
+        out[((size_t) i * ny + j) * nz + k] = (uint8_t) m;
+      }
   return FDTD_OK;
 }
 
@@ -1122,14 +1231,14 @@ int fdtd_execute_steps (int *status, const fdtd_config *cfg, fdtd_host_arrays *a
 {
   if (status) *status = FDTD_ERROR;
   if (!arr) return fail (FDTD_INVALID_ARGUMENT, "NULL arrays");
+  if (cfg && cfg->nranks > 1)
+    return fail (FDTD_INVALID_ARGUMENT, "fdtd_execute_steps is the single-GPU one-shot call: it has no communicator for %d ranks "
+                 "(use fdtd_create + fdtd_comm_init + fdtd_run per rank)", cfg->nranks);
   fdtd_handle h = NULL;
   int rc = fdtd_create (cfg, &h);
   if (rc) return rc;
   const int64_t nzf = cfg->dims == 3 ? cfg->size[2] : 1;
   const int64_t nzm = cfg->dims == 3 ? cfg->size[2] + 1 : 1;
-  const int64_t kz0 = h->kz0, nzl = h->nzl;
-  /* host arrays hold the whole grid; each rank moves its own slab */
-  (void) kz0; (void) nzl;
   do
   {
     for (int a = 0; a < cfg->dims && !rc; ++a)

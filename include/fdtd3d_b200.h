@@ -158,11 +158,18 @@ int fdtd_init_eps_sphere (fdtd_handle h, double cx, double cy, double cz, double
 /* Runs nsteps leapfrog steps: Scheme3D::performNSteps (Source/Scheme/Scheme3D.cpp:1966-2069) or
  * SchemeTMz::performNSteps (Source/Scheme/SchemeTMz.cpp:1311-1563).  This is what
  * cudaExecute3DSteps' `while (t < totalStep)` loop does (Source/Cuda/CudaInterface.cu:490-814),
- * here with PML, TFSF and the reference's point source.  fdtd_run blocks until the steps are done;
- * fdtd_run_async only enqueues them on the solver's stream and fdtd_sync waits. */
+ * here with PML, TFSF and the reference's point source.  fdtd_run blocks until the steps are done.
+ * fdtd_run_async only enqueues them on the solver's stream and returns; several calls may be queued back to back
+ * (chunks of steps with stream-ordered work of the caller's between them), fdtd_sync waits for all of them and
+ * fdtd_busy tells without waiting whether queued steps are still running.  fdtd_run_async waits only where it has
+ * to: when more source samples are queued than its pinned table holds (65536 complex-double steps between two
+ * synchronisations), when a run is longer than any before (the device table grows), and -- like any CUDA launch --
+ * when the driver's launch queue is full.  Every other entry point that touches the handle's arrays synchronises
+ * first. */
 int fdtd_run (fdtd_handle h, int64_t nsteps);
 int fdtd_run_async (fdtd_handle h, int64_t nsteps);
 int fdtd_sync (fdtd_handle h);
+int fdtd_busy (fdtd_handle h, int *busy);
 
 /* Turns the total field inside the TF/SF box into the scattered field, in place, for all six E/H components:
  * the post-processing the reference applies before it saves results with --save-res
@@ -172,7 +179,7 @@ int fdtd_sync (fdtd_handle h);
 int fdtd_subtract_incident (fdtd_handle h);
 
 /* Device time of the last completed fdtd_run / fdtd_run_async+fdtd_sync, from CUDA events on the
- * solver's stream (milliseconds). */
+ * solver's stream (milliseconds); when several runs were queued, of the one queued last. */
 int fdtd_last_run_ms (fdtd_handle h, float *ms);
 
 /* Per-kernel timing for the roofline report: when enabled, the two half-step kernels of every step of a
@@ -201,6 +208,16 @@ int fdtd_get_core_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
  * creating a handle; host only, no GPU needed (planning, tests).  No reference counterpart. */
 int fdtd_plan_core_box (const fdtd_config *cfg, const void *const sigma[3], int64_t lo[3], int64_t hi[3]);
 
+/*
+ * TF/SF face membership of every cell of component `field` (FDTD_EX .. FDTD_HZ) for cfg's grid and tfsf_size: the
+ * integer boxes the half-step kernels use in place of YeeGridLayout::doNeedTFSFUpdate{Ex..Hz}Border
+ * (Source/Layout/YeeGridLayout.cpp:327-809, floating-point predicates).  out[(i*Ny + j)*Nz + k] gets bit d set when the
+ * reference's predicate holds for LayoutDirection d (LEFT 0, RIGHT 1, DOWN 2, UP 3, BACK 4, FRONT 5;
+ * Source/Layout/GridLayout.h:9-16).  Host only, no GPU needed: this is what pins the index bookkeeping of the TF/SF
+ * correction bit-exactly against the reference (tests/test_tfsf_faces_cpu.py).
+ */
+int fdtd_tfsf_face_masks (const fdtd_config *cfg, int field, uint8_t *out, int64_t count);
+
 /* sum over this rank's cells of |cur|^2 of a field, accumulated in double (diagnostic used by the
  * parity tests at sizes where a full download is impractical; the known-answer vectors of
  * SURVEY.md §8c are quoted in this form). */
@@ -225,7 +242,9 @@ int fdtd_field_sumsq (fdtd_handle h, int field, double *out);
  *     streams, or different host threads) race and return garbage: order them on one stream or with events.
  *     Nothing in the array needs clearing between calls: each call rewrites every slot it later reads;
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress) and loads
- *     the kernels; make that first call outside, and before, any stream capture.
+ *     the kernels; make that first call outside, and before, any stream capture.  The address is remembered for
+ *     the life of the process and belongs to the device's primary context of that moment: do not call this entry
+ *     point again on a device after cudaDeviceReset (the array has moved and the remembered address is stale).
  * errbuf (may be NULL) receives the message of a failure; the return value is an fdtd_status.
  */
 #define FDTD_SUMSQ_NOALLOC_MAX_COUNT 268435456LL

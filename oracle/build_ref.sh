@@ -10,7 +10,7 @@
 #   shim 4  real-valued TMz: per-step probe SchemeTMz.cpp:1429-1508 uses .real() -> cut
 #   shim 6  class members made public in a header copy so the driver can read the grids
 #
-# Usage: oracle/build_ref.sh [variant ...]; variants: 3d_d 3d_dc 3d_f tmz_d tmz_dc tmz_f settings  (default: all)
+# Usage: oracle/build_ref.sh [variant ...]; variants: 3d_d 3d_dc 3d_f tmz_d tmz_dc tmz_f settings faces  (default: all)
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${FDTD3D_REFERENCE:-/root/reference}"
@@ -84,7 +84,13 @@ build_settings_probe () {
   g++ $CXXFLAGS -DDOUBLE_VALUES= -DGRID_3D= $INC "$HERE/ref_settings_probe.cpp" "$S/Settings/Settings.cpp" "$S/Helpers/Assert.cpp" -o "$OUT/ref_settings"
 }
 
-VARIANTS="${*:-3d_d 3d_dc 3d_f tmz_d tmz_dc tmz_f settings}"
+build_faces_probe () {
+  echo "[build_ref] faces"
+  g++ $CXXFLAGS -DDOUBLE_VALUES= -DGRID_3D= $INC "$HERE/ref_faces_probe.cpp" "$S/Layout/YeeGridLayout.cpp" "$S/Coordinate/GridCoordinate.cpp" \
+      "$S/Helpers/Assert.cpp" "$S/Settings/Settings.cpp" -o "$OUT/ref_faces"
+}
+
+VARIANTS="${*:-3d_d 3d_dc 3d_f tmz_d tmz_dc tmz_f settings faces}"
 for v in $VARIANTS; do
   case "$v" in
     3d_d)   build_variant 3d_d   3D DOUBLE_VALUES 0 ;;
@@ -94,6 +100,7 @@ for v in $VARIANTS; do
     tmz_dc) build_variant tmz_dc 2D DOUBLE_VALUES 1 ;;
     tmz_f)  build_variant tmz_f  2D FLOAT_VALUES  0 ;;
     settings) build_settings_probe ;;
+    faces) build_faces_probe ;;
     *) echo "unknown variant $v" >&2; exit 2 ;;
   esac
 done

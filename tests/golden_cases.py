@@ -15,7 +15,15 @@ VARIANT = {  # variant -> (dims, value_type, complex)
 
 
 def case_names():
-    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+    # *.c1.npz are the condensed BASELINE configs[0] fixtures (make_c1_golden.py), loaded by load_c1
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")) if not p.endswith((".c1.npz", ".faces.npz")))
+
+
+def load_c1(name):
+    """(meta, arrays) of a condensed 80^3 x 100 steps fixture: 'c1_d' (real double) or 'c1_dc' (complex double)."""
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".c1.npz"))
+    meta = ast.literal_eval(str(z["meta"]))
+    return meta, {k: z[k] for k in z.files if k != "meta"}
 
 
 def load(name):

@@ -71,6 +71,21 @@ def main():
                     failures += 1
                     print("rank %d mode %d case %s field %s: max |d| = %g (family scale %g)"
                           % (rank, exact_mode, size, name, np.abs(got - want).max(), scale[name[0]]), flush=True)
+            # a whole-grid host buffer that the ranks fill side by side: a rank's download of [0, nz) must write its own
+            # planes only (the others keep the sentinel), and an upload from such a buffer must not touch the halos
+            for name in ("Ez", "Eps"):
+                shape = s.field_shape(name)
+                dt = O.real_dtype(cfg) if name == "Eps" else O.field_dtype(cfg)
+                whole = np.full(int(np.prod(shape)), -7.25, dtype=dt)
+                F._check(F.lib().fdtd_download(s._h, F.FIELD_IDS[name], whole.ctypes.data, F.ORDER_REFERENCE, 0, shape[2]))
+                w3 = whole.reshape(shape)
+                own = nzl + (1 if name == "Eps" else 0)   # material slabs carry one more plane
+                mine = np.ascontiguousarray(w3[:, :, z0:z0 + own]).reshape(-1)
+                if not (np.array_equal(mine, s.download(name, z0=z0, nz=own))
+                        and (w3[:, :, :z0] == dt(-7.25)).all() and (w3[:, :, z0 + own:] == dt(-7.25)).all()):
+                    failures += 1
+                    print("rank %d mode %d case %s: whole-grid download of %s wrote outside the slab or differs"
+                          % (rank, exact_mode, size, name), flush=True)
             if use_tfsf and exact_mode == 1:
                 for name in ("EInc", "HInc"):
                     if vt == 8 and not np.array_equal(s.download(name), ref[name]):

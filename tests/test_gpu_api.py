@@ -37,6 +37,42 @@ def test_async_run_then_implicit_sync_on_download():
         assert s.last_run_ms == 0 and s.time_step == 11
 
 
+def test_run_async_queues_runs_without_waiting():
+    """Three fdtd_run_async calls in a row: the host is back while the first is still running (fdtd_busy), each has its
+    own event pair, and the result is the one run of the same number of steps."""
+    import time
+    kw = dict(size=(256, 256, 192), pml=10, tfsf=20, use_pml=True, use_tfsf=True, exact_mode=0)
+    cfg = O.make_config(**kw)
+    inputs = O.reference_setup(cfg)
+    chunks = (60, 60, 60)
+    with F.Solver(cfg) as s:
+        for a in range(3):
+            s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+        s.upload("Eps", inputs["Eps"])
+        s.run(5)                      # warm-up: module load, first-launch set-up
+        t0 = time.perf_counter()
+        for n in chunks:
+            s.run_async(n)
+        host_s = time.perf_counter() - t0
+        busy_after_queueing = s.busy
+        s.sync()
+        total_s = time.perf_counter() - t0
+        last_ms = s.last_run_ms
+        assert not s.busy
+        a = {k: s.download(k) for k in ("Ez", "Hy", "Dz")}
+    assert busy_after_queueing, "the queued runs had already finished when fdtd_run_async returned"
+    assert host_s < 0.5 * total_s, (host_s, total_s)
+    assert 0 < last_ms * 1e-3 < 0.6 * total_s      # the time of the run queued last, not of all three
+    with F.Solver(cfg) as s:
+        for a_ in range(3):
+            s.set_sigma(a_, inputs["Sigma" + "XYZ"[a_]])
+        s.upload("Eps", inputs["Eps"])
+        s.run(5)
+        s.run(sum(chunks))
+        for k in a:
+            assert np.array_equal(s.download(k), a[k]), k
+
+
 def test_time_step_start_is_performNSteps_start_step():
     """cfg.time_step_start = the reference's startStep: the source waveform continues from t, not from 0."""
     cfg = O.make_config(size=(20, 18, 16), pml=3, tfsf=5, use_pml=True, use_tfsf=False, exact_mode=1)
