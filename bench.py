@@ -134,7 +134,7 @@ def run_reference_arm(args):
     if os.path.exists(exe):
         # the reference has no warm-up notion and runs all steps in one call: W + K steps, whole time counted
         total = steps + warmup
-        # keep the run within a few minutes: ~1.2 s per step at 64^3 on one core
+        # keep the run within a few minutes: ~0.5 s per step at 64^3 on one core
         total = min(total, 120)
         with tempfile.TemporaryDirectory() as tmp:
             out = subprocess.run([exe, str(n), str(n), str(n), str(PML), str(TFSF), str(total), "1", "1", repr(DX), repr(WAVELENGTH),
@@ -145,15 +145,27 @@ def run_reference_arm(args):
               "sample": "%d^3 sub-grid of the workload (same flags: double, PML, TF/SF, sphere), %d steps, unmodified reference "
                         "solver from oracle/_ref, single thread (the reference has no OpenMP; MPI absent)" % (n, total)}
         ms = secs / total * 1e3
-        steps_run = total
+        timed = total
     else:
-        cb = cpu_oracle_baseline("c3", n=128, steps=max(2, min(steps, 20)))
+        n = 128
+        cb = cpu_oracle_baseline("c3", n=n, steps=max(2, min(steps, 20)))
         value = cb["value"]
-        ms = 128 ** 3 / (value * 1e6) * 1e3
-        steps_run = steps
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": steps_run,
-            "warmup": 0, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": workload_config(args.gpus),
+        ms = n ** 3 / (value * 1e6) * 1e3
+        timed = max(2, min(steps, 20))
+    # The line says what ran: a sub-grid sample of the headline workload.  The reference cannot reach 512^3 (about
+    # 250 GB and days), so the per-cell rate of the sample is the only comparison there is.
+    cfg = workload_config(args.gpus)
+    cfg["workload"] = "%d^3 sample of: %s" % (n, cfg["workload"])
+    cfg["full_size"] = cfg["size"]
+    cfg["size"] = [n, n, n]
+    cfg["parallelism"] = "1 host thread"
+    cfg["l2"] = "CPU run"
+    cfg["arithmetic"] = "the reference's own (x86-64 -O2, no FMA contraction)"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warmup, "timed_steps": timed, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": cfg,
+            "note": "the reference runs warm-up and timed steps in one performSteps call: its own 'Total time' over all "
+                    "timed_steps is what value and ms_per_step are computed from",
             "cpu_baseline": cb, "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -184,6 +196,164 @@ def workload_config(n_gpus, name="c3", exact=0):
                                              if w["pml"] else "")}[exact]}
 
 
+# ----------------------------------------------------------------------------- measuring one configuration
+
+def _peak():
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    except Exception:
+        return 6650.0, "fallback 6650 GB/s (of fallback)"
+
+
+def byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=False):
+    """SURVEY.md §8d bytes of one rank's slab per half step: algorithmic (D/B through every cell, a material value per
+    cell, as the reference formulates the step) and needed (what the default mode has to move: no D/B in the sigma-free
+    core, no material array that was set with fdtd_fill)."""
+    dims, nx, ny = w["dims"], w["nx"], w["ny"]
+    fp = w["vt"]
+    fv = fp * (2 if w["cplx"] else 1)
+    ncell = nx * ny * nzl
+    if dims == 3:
+        alg_e = alg_h = ((15 if w["pml"] else 9) * fv + fp) * ncell
+        aux_e = aux_h = 3
+    else:
+        alg_e, alg_h = ((6 if w["pml"] else 4) * fv + fp) * ncell, ((9 if w["pml"] else 5) * fv + fp) * ncell
+        aux_e, aux_h = 1, 2
+    core_cells = 0
+    if box:
+        zlo, zhi = max(box[0][2], z0), min(box[1][2], z0 + nzl - 1)
+        core_cells = (box[1][0] - box[0][0] + 1) * (box[1][1] - box[0][1] + 1) * (max(0, zhi - zlo + 1) if dims == 3 else 1)
+    need_e = alg_e - 2 * aux_e * fv * core_cells - (fp * ncell if eps_uniform else 0)
+    need_h = alg_h - 2 * aux_h * fv * core_cells - (fp * ncell if mu_uniform else 0)
+    return {"alg_e": alg_e, "alg_h": alg_h, "need_e": need_e, "need_h": need_h, "core_cells": core_cells, "cells": ncell}
+
+
+def make_solver(F, name, exact, rank, world, local, dist):
+    w = WORKLOADS[name]
+    dims = w["dims"]
+    nz_total = workload_nz(w, world)
+    cfg = F.make_config(dims=dims, size=(w["nx"], w["ny"], nz_total)[:dims], pml=PML, tfsf=TFSF, use_pml=w["pml"], use_tfsf=w["tfsf"],
+                        value_type=w["vt"], complex_values=w["cplx"], dx=DX, wavelength=WAVELENGTH, exact_mode=exact,
+                        device=local, rank=rank, nranks=world)
+    s = F.Solver(cfg)
+    if world > 1:
+        # the 128-byte NCCL id travels over torch.distributed; the exchange itself is inside the library
+        from fdtd3d_b200 import multi
+        s.comm_init(multi.share_unique_id(dist, rank, "cuda"))
+    if w["pml"]:
+        for a in range(dims):
+            s.set_sigma(a, F.pml_sigma_profile(cfg, a))
+    if w["sphere"]:
+        s.init_eps_sphere()  # Scheme3D.cpp:3437: centre (40.5,40.5,40.5), r = 20, eps = 2
+    return s, cfg, nz_total
+
+
+def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False):
+    """Device-timed throughput of one configuration on the ranks of this job: W untimed steps, then K steps between
+    barriers, CUDA events on the solver's stream, max over ranks.  Returns the numbers of the bench line for it."""
+    rank, world, local, dist, barrier, max_over_ranks = env
+    w = WORKLOADS[name]
+    s, cfg, nz_total = make_solver(F, name, exact, rank, world, local, dist)
+    z0, nzl = F.slab_range(nz_total, rank, world)
+    cells = w["nx"] * w["ny"] * nz_total
+    s.run(warmup)
+    barrier()
+    launches0 = s.launch_count
+    s.set_profiling(True)
+    sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
+    if sampler:
+        sampler.start()
+    barrier()
+    t_wall = time.perf_counter()
+    s.run(steps)
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    clocks = sampler.stop() if sampler else None
+    ms = max_over_ranks(s.last_run_ms)
+    e_ms, h_ms, psteps = s.phase_times()
+    launches = s.launch_count - launches0
+    s.set_profiling(False)
+    peak, peak_source = _peak()
+    box = s.core_box
+    bm = byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=(w["dims"] == 2 and not w["sphere"]))
+    step_s = ms / steps * 1e-3
+    res = {"name": name, "exact_mode": exact, "n_gpus": world, "steps": steps, "warmup": warmup,
+           "value": cells * steps / (ms * 1e-3) / 1e6, "ms_per_step": ms / steps, "gpu_launches": launches,
+           "whole_step_frac": (bm["alg_e"] + bm["alg_h"]) / step_s / 1e9 / peak,
+           "whole_step_frac_of_needed_bytes": (bm["need_e"] + bm["need_h"]) / step_s / 1e9 / peak,
+           "core_cell_fraction": bm["core_cells"] / float(bm["cells"]), "host_wall_s": t_wall, "clocks": clocks,
+           "peak": peak, "peak_source": peak_source, "bytes": bm}
+    if psteps:
+        kn = ("e_phase_3d", "h_phase_3d") if w["dims"] == 3 else ("ez_phase_tmz", "h_phase_tmz")
+        res.update({"e_phase_ms": e_ms / psteps, "h_phase_ms": h_ms / psteps, "kernels": kn,
+                    "e_frac": bm["alg_e"] / (e_ms / psteps * 1e-3) / 1e9 / peak, "h_frac": bm["alg_h"] / (h_ms / psteps * 1e-3) / 1e9 / peak,
+                    "e_frac_of_needed_bytes": bm["need_e"] / (e_ms / psteps * 1e-3) / 1e9 / peak,
+                    "h_frac_of_needed_bytes": bm["need_h"] / (h_ms / psteps * 1e-3) / 1e9 / peak})
+    if keep:
+        return res, s, cfg
+    s.close()
+    return res
+
+
+def brief(res):
+    """The part of a measure() result that goes into roofline.modes / other_configs."""
+    keys = ("name", "exact_mode", "n_gpus", "steps", "warmup", "value", "ms_per_step", "e_phase_ms", "h_phase_ms", "e_frac", "h_frac",
+            "e_frac_of_needed_bytes", "h_frac_of_needed_bytes", "whole_step_frac", "whole_step_frac_of_needed_bytes",
+            "core_cell_fraction", "gpu_launches")
+    out = {k: res[k] for k in keys if k in res}
+    out["unit"] = METRIC
+    out["workload"] = workload_config(res["n_gpus"], res["name"], res["exact_mode"])["workload"]
+    return out
+
+
+def parity_check(F, env):
+    """Before anything is timed: one small case, sharded over the ranks of this job exactly as the timed runs are
+    (z-slabs, NCCL halo planes), against the CPU oracle (checker only) -- exact mode bit for bit, the default fast mode
+    (sigma-free core) within 1e-12.  Every rank checks its own slab; the verdict is reduced over the ranks."""
+    import numpy as np
+    rank, world, local, dist, barrier, max_over_ranks = env
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    from fdtd3d_b200 import multi
+    size, steps = (72, 40, 12 * world + 5), 10
+    out = {"case": "3D %dx%dx%d double, UPML(4)+TF/SF(7), theta 60 phi 30 psi 20, eps sphere, %d steps, %d z-slab(s), vs the CPU oracle"
+                   % (size + (steps, world)), "tol": 1e-12, "ranks": world}
+    worst = 0.0
+    exact_equal = True
+    for mode in (1, 0):
+        cfg1 = O.make_config(size=size, pml=4, tfsf=7, use_pml=True, use_tfsf=True, theta=60, phi=30, psi=20, exact_mode=mode)
+        inputs = O.reference_setup(cfg1)
+        ref = O.run(cfg1, steps, inputs)
+        cfg = O.make_config(size=size, pml=4, tfsf=7, use_pml=True, use_tfsf=True, theta=60, phi=30, psi=20, exact_mode=mode)
+        cfg.rank, cfg.nranks, cfg.device = rank, world, local
+        z0, nzl = F.slab_range(size[2], rank, world)
+        with F.Solver(cfg) as s:
+            if world > 1:
+                s.comm_init(multi.share_unique_id(dist, rank, "cuda"))
+            for a in range(3):
+                s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+            s.upload("Eps", inputs["Eps"])
+            s.run(steps - 3)
+            s.run(3)
+            if mode == 0:
+                out["core_box"] = s.core_box
+            fam = {}
+            for nme in O.field_names(cfg):
+                fam[nme[0]] = max(fam.get(nme[0], 0.0), float(np.abs(ref[nme]).max()))
+            for nme in O.field_names(cfg):
+                got = s.download(nme, z0=z0, nz=nzl)
+                want = multi.slab_of_array(ref[nme], size, z0, nzl)
+                if mode == 1:
+                    exact_equal = exact_equal and bool(np.array_equal(got, want))
+                else:
+                    worst = max(worst, float(np.abs(got - want).max()) / fam[nme[0]])
+    worst = max_over_ranks(worst)
+    bad = max_over_ranks(0.0 if exact_equal else 1.0)
+    out.update({"exact_mode_bit_equal": bad == 0.0, "fast_mode_max_rel_err": worst, "ok": bad == 0.0 and worst <= 1e-12})
+    return out
+
+
 # ----------------------------------------------------------------------------- our arm
 
 def main():
@@ -196,6 +366,8 @@ def main():
                     help="fdtd_config.exact_mode: 0 fast (default), 1 bit-exact kernels, 2 fast with D/B carried through every cell")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the small sharded parity run against the CPU oracle")
+    ap.add_argument("--quick", action="store_true", help="headline line only: no roofline.modes, other_configs, sustained")
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json config (default c3, the headline)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -235,71 +407,37 @@ def main():
     nz_total = workload_nz(w, world)
     if dims == 2 and world > 1:
         raise SystemExit("the 2D TMz workload runs on one GPU")
-    cfg = F.make_config(dims=dims, size=(nx, ny, nz_total)[:dims], pml=PML, tfsf=TFSF, use_pml=w["pml"], use_tfsf=w["tfsf"],
-                        value_type=w["vt"], complex_values=w["cplx"], dx=DX, wavelength=WAVELENGTH, exact_mode=args.exact,
-                        device=local, rank=rank, nranks=world)
-    s = F.Solver(cfg)
-    if world > 1:
-        # the 128-byte NCCL id travels over torch.distributed; the exchange itself is inside the library
-        from fdtd3d_b200 import multi
-        s.comm_init(multi.share_unique_id(dist, rank, "cuda"))
-    if w["pml"]:
-        for a in range(dims):
-            s.set_sigma(a, F.pml_sigma_profile(cfg, a))
-    if w["sphere"]:
-        s.init_eps_sphere()  # Scheme3D.cpp:3437: centre (40.5,40.5,40.5), r = 20, eps = 2
+    env = (rank, world, local, dist, barrier, max_over_ranks)
+    headline = args.workload == "c3" and args.exact == 0 and not args.quick
+
+    # ---- parity of the sharded path against the CPU oracle, before anything is timed
+    parity = None
+    if not args.no_parity:
+        try:
+            parity = parity_check(F, env)
+        except Exception as ex:
+            parity = {"ok": False, "error": repr(ex)}
+
+    # ---- device-resident throughput of the configuration the metric is quoted on
+    res, s, cfg = measure(F, env, args.workload, args.exact, args.steps, args.warmup, sample_clocks=True, keep=True)
+    value, ms, launches, clocks, t_wall = res["value"], res["ms_per_step"] * args.steps, res["gpu_launches"], res["clocks"], res["host_wall_s"]
     cells = nx * ny * nz_total
     z0, nzl = F.slab_range(nz_total, rank, world)
     fp = w["vt"]
     fv = fp * (2 if w["cplx"] else 1)
     rdt = torch.float64 if fp == 8 else torch.float32
     fdt = {(8, False): torch.float64, (4, False): torch.float32, (8, True): torch.complex128, (4, True): torch.complex64}[(fp, w["cplx"])]
-
-    # ---- device-resident throughput
-    s.run(args.warmup)
-    barrier()
-    launches0 = s.launch_count
-    s.set_profiling(True)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    barrier()
-    t_wall = time.perf_counter()
-    s.run(args.steps)
-    barrier()
-    t_wall = time.perf_counter() - t_wall
-    clocks = sampler.stop() if rank == 0 else None
-    ms = max_over_ranks(s.last_run_ms)
-    e_ms, h_ms, psteps = s.phase_times()
-    launches = s.launch_count - launches0
-    s.set_profiling(False)
-    value = cells * args.steps / (ms * 1e-3) / 1e6
+    peak, peak_source = res["peak"], res["peak_source"]
+    bm = res["bytes"]
+    box = s.core_box
 
     # ---- roofline of the dominant kernel (single-rank run: per-kernel CUDA events inside the timed region)
-    # SURVEY.md §8d, per cell per half step: 3D: (9 or 15) FieldValue + 1 FPValue; TMz E: (4 or 6) FV + FP, H: (5 or 9) FV + FP
-    if dims == 3:
-        bytes_e = bytes_h = (15 if w["pml"] else 9) * fv + fp
-        kn = ("e_phase_3d", "h_phase_3d")
-    else:
-        bytes_e, bytes_h = (6 if w["pml"] else 4) * fv + fp, (9 if w["pml"] else 5) * fv + fp
-        kn = ("ez_phase_tmz", "h_phase_tmz")
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    # cells of this rank that the time loop advances without D/B (exact_mode 0, 3D UPML): their D/B values are neither
-    # read nor written, so the bytes actually needed are below the algorithmic figure and frac can exceed 1
-    box = s.core_box
-    core_cells = 0
-    if box:
-        zlo, zhi = max(box[0][2], z0), min(box[1][2], z0 + nzl - 1)
-        core_cells = (box[1][0] - box[0][0] + 1) * (box[1][1] - box[0][1] + 1) * (max(0, zhi - zlo + 1) if dims == 3 else 1)
-    roofline = None
-    if psteps:
-        name, k_ms, bytes_k = (kn[1], h_ms / psteps, bytes_h) if h_ms >= e_ms else (kn[0], e_ms / psteps, bytes_e)
-        achieved = bytes_k * (nx * ny * nzl) / (k_ms * 1e-3) / 1e9
+    if "e_phase_ms" in res:
+        e_dom = res["e_phase_ms"] >= res["h_phase_ms"]
+        name = res["kernels"][0 if e_dom else 1]
+        k_ms = res["e_phase_ms"] if e_dom else res["h_phase_ms"]
+        alg, need = (bm["alg_e"], bm["need_e"]) if e_dom else (bm["alg_h"], bm["need_h"])
+        achieved = alg / (k_ms * 1e-3) / 1e9
         traffic = None
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
@@ -307,29 +445,27 @@ def main():
             # ncu captures exist for c3 (default mode and exact_mode 2) and for c2's default mode
             have = (args.workload == "c3" and args.exact != 1) or (args.workload == "c2" and args.exact == 0)
             traffic = prof.get(key, {}).get("dram_bytes_per_launch") if have else None
+            traffic_tag = prof.get(key, {}).get("tag") if have else None
         except Exception:
-            pass
+            traffic_tag = None
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                    "kernel": name, "kernel_ms": k_ms, "e_phase_ms": e_ms / psteps, "h_phase_ms": h_ms / psteps,
-                    "algorithmic_bytes_per_launch": bytes_k * nx * ny * nzl,
-                    "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
-                    "whole_step_frac": ((bytes_e + bytes_h) * nx * ny * nzl / (ms / args.steps * 1e-3) / 1e9) / peak}
-        # materials set with fdtd_fill are known to be homogeneous and are not loaded: mu always here (never uploaded
-        # before the timed run), eps unless the sphere was initialised; the 3D kernels use this for mu only
-        skip_mat = fp * nx * ny * nzl if ((name == kn[1]) or (dims == 2 and not w["sphere"])) else 0
-        if box or skip_mat:
-            # skipped in the core: D (or B) of each component, read + written (3D: 3 components; TMz: Dz / Bx, By)
-            n_aux = 3 if dims == 3 else (2 if name == kn[1] else 1)
-            needed = bytes_k * nx * ny * nzl - 2 * n_aux * fv * core_cells - skip_mat
-            roofline.update({"core_cell_fraction": core_cells / float(nx * ny * nzl), "needed_bytes_per_launch": needed,
-                             "frac_of_needed_bytes": needed / (k_ms * 1e-3) / 1e9 / peak,
+                    "traffic_source": None if traffic is None else
+                    "constant read from profiles/ncu_summary.json (dram__bytes_read.sum + dram__bytes_write.sum of one "
+                    "`ncu --set full` capture of this kernel, tag %s), NOT measured by this run" % traffic_tag,
+                    "kernel": name, "kernel_ms": k_ms, "e_phase_ms": res["e_phase_ms"], "h_phase_ms": res["h_phase_ms"],
+                    "algorithmic_bytes_per_launch": alg, "peak_source": peak_source, "whole_step_frac": res["whole_step_frac"],
+                    "whole_step_frac_of_needed_bytes": res["whole_step_frac_of_needed_bytes"]}
+        if need != alg:
+            roofline.update({"core_cell_fraction": res["core_cell_fraction"], "needed_bytes_per_launch": need,
+                             "frac_of_needed_bytes": need / (k_ms * 1e-3) / 1e9 / peak,
                              "note": "achieved/frac use SURVEY 8(d)'s algorithmic bytes (D/B through every cell and a material value "
                                      "per cell, as the reference formulates the step); the sigma-free core skips D/B and a material "
                                      "set with fdtd_fill is not loaded, so frac > 1 is bytes not moved, not bandwidth above the peak "
                                      "-- frac_of_needed_bytes is the kernel against its own traffic"})
     else:
-        whole = (bytes_e + bytes_h) * nx * ny * nzl / (ms / args.steps * 1e-3) / 1e9
+        whole = (bm["alg_e"] + bm["alg_h"]) / (res["ms_per_step"] * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": whole, "peak": peak, "unit": "GB/s", "frac": whole / peak, "traffic": None,
+                    "peak_source": peak_source, "whole_step_frac_of_needed_bytes": res["whole_step_frac_of_needed_bytes"],
                     "kernel": "whole step per GPU (multi-rank run: boundary + interior launches overlap with the exchange)"}
 
     # ---- end to end through the C ABI with host buffers (upload + K steps + download in the timed region)
@@ -362,8 +498,37 @@ def main():
                "d2h_bytes_per_step": d2h * world / args.steps, "seconds": t_e2e,
                "what": "per rank: upload eps, mu and %d fields from pinned host memory in reference (z-fastest) order, %d steps, "
                        "download %d fields; host wall clock, max over ranks" % (len(names), args.steps, len(names))}
-        launches_e2e = s.launch_count
     s.close()
+
+    # ---- everything else the round claims, measured by this same run (headline invocation only)
+    modes = other = sustained = None
+    if headline:
+        short = max(5, min(args.steps, 12))
+        # the like-for-like figure (D/B through every cell) and the bit-exact one, same workload, same process
+        modes = {}
+        for mode, label in ((2, "fast_db_everywhere"), (1, "exact_bit_for_bit")):
+            try:
+                modes[label] = brief(measure(F, env, "c3", mode, short, 3))
+            except Exception as ex:
+                modes[label] = {"error": repr(ex)}
+        # the other BASELINE.json configurations this job's GPUs can hold
+        other = {}
+        todo = [("c5", 0)] + ([("c2", 0), ("c2", 2), ("c1", 0)] if world == 1 else [("c4", 0)])
+        for nme, mode in todo:
+            key = nme if mode == 0 else "%s_exact%d" % (nme, mode)
+            try:
+                other[key] = brief(measure(F, env, nme, mode, 100 if nme in ("c2", "c1") else short, 5 if nme in ("c2", "c1") else 3))
+            except Exception as ex:
+                other[key] = {"error": repr(ex)}
+        # BASELINE.json quotes 1000-step runs: the sustained rate of the headline configuration, with its own clock sample
+        try:
+            r1000 = measure(F, env, "c3", 0, 1000, 3, sample_clocks=True)
+            sustained = {"steps": 1000, "value": r1000["value"], "unit": METRIC, "ms_per_step": r1000["ms_per_step"],
+                         "whole_step_frac": r1000["whole_step_frac"], "clocks": r1000["clocks"],
+                         "note": "no per-kernel events in this run's timed region would change it: profiling events are recorded "
+                                 "between launches on the same stream"}
+        except Exception as ex:
+            sustained = {"error": repr(ex)}
 
     # ---- CPU baseline beside it (rank 0, N = 1 only)
     cpu = None
@@ -379,7 +544,13 @@ def main():
                 "dtype": {8: "f64", 4: "f32"}[fp] + ("c" if w["cplx"] else ""), "data": "synthetic",
                 "config": workload_config(world, args.workload, args.exact), "roofline": roofline,
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-                "per_gpu_value": value / world, "host_wall_s": t_wall, "exact_mode": args.exact}
+                "per_gpu_value": value / world, "host_wall_s": t_wall, "exact_mode": args.exact, "parity": parity}
+        if modes is not None:
+            line["roofline"]["modes"] = modes
+        if other is not None:
+            line["other_configs"] = other
+        if sustained is not None:
+            line["sustained"] = sustained
         print(json.dumps(line))
     if dist:
         dist.destroy_process_group()

@@ -71,6 +71,33 @@ def family_rel_errs(out, ref, keys):
     return errs
 
 
+def field_rel_errs(out, ref, keys, floor=1e-9):
+    """{field: max |out-ref| / max(max |ref of that field|, floor * max |ref over the field's family|)}.
+
+    The per-field figure SURVEY.md §8c asks for: every component against its OWN largest magnitude, with an absolute
+    floor so that a component that is zero in exact arithmetic (nothing but rounding noise, ~1e-16 of its family) does
+    not turn noise into a relative error of order one.  family_rel_errs is the bar of the tests; this one is reported
+    beside it and asserted for every component that carries signal (own maximum >= 1e-3 of the family's)."""
+    fam = {}
+    for k in keys:
+        fam[family(k)] = max(fam.get(family(k), 0.0), float(np.abs(ref[k]).max()))
+    errs = {}
+    for k in keys:
+        own = float(np.abs(ref[k]).max())
+        sc = max(own, floor * fam[family(k)])
+        d = float(np.abs(out[k] - ref[k]).max())
+        errs[k] = d / sc if sc > 0 else d
+    return errs
+
+
+def significant(ref, keys, frac=1e-3):
+    """The components whose own maximum is at least `frac` of their family's."""
+    fam = {}
+    for k in keys:
+        fam[family(k)] = max(fam.get(family(k), 0.0), float(np.abs(ref[k]).max()))
+    return [k for k in keys if fam[family(k)] > 0 and float(np.abs(ref[k]).max()) >= frac * fam[family(k)]]
+
+
 def random_inputs(cfg, seed):
     """Random eps/mu in [1,4], sigma profiles from the oracle, random small initial fields."""
     rng = np.random.default_rng(seed)

@@ -19,4 +19,7 @@ def test_reference_arm_prints_one_contract_line():
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["sample"]
     assert d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
-    assert d["config"]["name"] == "c3" and "512x512x512" in d["config"]["workload"]
+    # the line says what ran: a 64^3 sample of the 512^3 headline workload, not the workload itself
+    assert d["config"]["name"] == "c3" and d["config"]["workload"].startswith("64^3 sample of: 3D 512x512x512")
+    assert d["config"]["size"] == [64, 64, 64] and d["config"]["full_size"] == [512, 512, 512]
+    assert d["steps"] == 1 and d["warmup"] == 0 and d["timed_steps"] == 1

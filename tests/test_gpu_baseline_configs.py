@@ -1,0 +1,164 @@
+"""BASELINE.json's configurations as written, in the modes bench.py times (GPU, through the C ABI).
+
+  C1  3D 80^3, PML 10, TF/SF 20, 100 steps, double real and complex -- against the UNMODIFIED reference solver
+      (condensed Tier-1 dump tests/golden/c1_*.c1.npz) and, cell by cell, the Tier-2 oracle that make_c1_golden.py
+      found bit-equal to that dump.
+  C2  2D TMz 4096^2 float, PML, point source at Ez(70, 2048): 200 steps from zero fields as the configuration says,
+      and a few steps from random fields so that every cell of the full-size grid is exercised; all three modes.
+  C5  3D float with a NON-EMPTY sigma-free core (x >= 96: float quarters are 32 cells), 500 steps (C5's count), TF/SF
+      and point source; E/H within 1e-5, D/B reported against both bars.
+  C3 at full size is test_gpu_parity.py::test_full_size_512_cubed_against_oracle (all three modes).
+"""
+import sys
+
+import numpy as np
+import pytest
+
+import fdtd3d_b200 as F
+import golden_cases as G
+import oracle_lib as O
+from gpu_util import family_rel_errs, field_rel_errs, random_inputs, run_gpu, significant
+
+pytestmark = pytest.mark.gpu
+TOL = {8: 1e-12, 4: 1e-5}
+
+sys.path.insert(0, G.GOLDEN_DIR)
+import make_c1_golden as C1  # noqa: E402  (condense() only; nothing of the reference is touched at test time)
+
+
+def _keys(cfg):
+    return O.field_names(cfg) + (["EInc", "HInc"] if cfg.use_tfsf else [])
+
+
+# ----------------------------------------------------------------------------- C1
+
+@pytest.mark.parametrize("name", ["c1_d", "c1_dc"])
+def test_c1_readme_example_against_the_reference(name):
+    meta, gold = G.load_c1(name)
+    cplx = name.endswith("c")
+    kw = dict(size=meta["size"], pml=meta["pml"], tfsf=meta["tfsf"], use_pml=True, use_tfsf=True, value_type=8,
+              complex_values=cplx, dx=meta["dx"], wavelength=meta["wavelength"])
+    cfg = O.make_config(exact_mode=1, **kw)
+    assert cfg.dt == meta["dt"] and cfg.rel_phase_velocity == meta["rel_phase_velocity"]
+    inputs = O.reference_setup(cfg)
+    keys = _keys(cfg)
+
+    # exact mode: every cell of every field bit-equal to the reference (per-plane XOR of the raw bits + full planes)
+    out = run_gpu(cfg, meta["steps"], inputs)
+    small = C1.condense(out)
+    for key, want in gold.items():
+        assert np.array_equal(small[key], want), "exact mode differs from the reference dump in " + key
+
+    # fast modes (0: sigma-free core as bench.py runs it; 2: D/B everywhere): tolerance against the reference's planes
+    # and sums, and cell by cell against the Tier-2 oracle (bit-equal to the reference at this configuration)
+    ref = O.run(cfg, meta["steps"], inputs)
+    assert all(np.array_equal(C1.condense(ref)[k], v) for k, v in gold.items())
+    for mode in (0, 2):
+        got = run_gpu(O.make_config(exact_mode=mode, **kw), meta["steps"], inputs)
+        errs = family_rel_errs(got, ref, keys)
+        assert max(errs.values()) <= TOL[8], (mode, errs)
+        own = field_rel_errs(got, ref, keys)
+        for k in significant(ref, keys):
+            assert own[k] <= TOL[8], (mode, k, own)
+        sm = C1.condense(got)
+        for k in C1.FIELDS:
+            scale = float(np.abs(ref[k[0] + "x"]).max() + np.abs(ref[k[0] + "y"]).max() + np.abs(ref[k[0] + "z"]).max())
+            for i in meta["planes"]:
+                d = float(np.abs(sm["plane_%d_%s" % (i, k)] - gold["plane_%d_%s" % (i, k)]).max())
+                assert d <= TOL[8] * scale, (mode, k, i, d, scale)
+            if gold["sumsq_" + k] > 1e-20 * max(gold["sumsq_" + f] for f in C1.FIELDS if f[0] == k[0]):
+                assert abs(sm["sumsq_" + k] - gold["sumsq_" + k]) <= 1e-10 * gold["sumsq_" + k], (mode, k)
+
+
+# ----------------------------------------------------------------------------- C2
+
+def _c2_cfg(mode, n=4096):
+    return O.make_config(dims=2, size=(n, n), pml=10, tfsf=20, use_pml=True, use_tfsf=False, value_type=4, exact_mode=mode,
+                         source_pos=(70, n // 2, 0))
+
+
+def test_c2_tmz_4096_float_as_written():
+    """200 steps from zero fields, eps = mu = 1 set with fdtd_fill (the reference's TMz set-up): the modes bench.py
+    times.  Exact mode is bit for bit; the fast modes are within 1e-5 on every field (D and B included at this count)."""
+    steps = 200
+    cfg = _c2_cfg(1)
+    inputs = O.reference_setup(cfg)
+    assert (inputs["Eps"] == 1).all() and (inputs["Mu"] == 1).all()
+    ref = O.run(cfg, steps, inputs)
+    assert float(np.abs(ref["Ez"]).max()) > 0.05
+    sig = {k: v for k, v in inputs.items() if k.startswith("Sigma")}
+    keys = _keys(cfg)
+    for mode in (1, 0, 2):
+        out = run_gpu(_c2_cfg(mode), steps, sig, fills={"Eps": 1.0, "Mu": 1.0})
+        if mode == 1:
+            for k in keys:
+                assert np.array_equal(out[k], ref[k]), k
+        else:
+            errs = family_rel_errs(out, ref, keys)
+            print("c2 mode %d: %s" % (mode, {k: "%.2e" % v for k, v in errs.items()}))
+            assert max(errs.values()) <= TOL[4], (mode, errs)
+        if mode == 0:
+            with F.Solver(_c2_cfg(0)) as s:
+                for a in range(2):
+                    s.set_sigma(a, sig["Sigma" + "XY"[a]])
+                assert s.core_box is not None
+
+
+def test_c2_tmz_4096_float_every_cell():
+    """The same grid from random fields and random materials, 8 steps: every one of the 16.8 M cells carries signal."""
+    steps = 8
+    cfg = _c2_cfg(1)
+    inputs, fields = random_inputs(cfg, seed=4096)
+    ref = O.run(cfg, steps, inputs, fields)
+    keys = _keys(cfg)
+    for mode in (1, 0, 2):
+        out = run_gpu(_c2_cfg(mode), steps, inputs, fields)
+        if mode == 1:
+            for k in keys:
+                assert np.array_equal(out[k], ref[k]), k
+        else:
+            errs = family_rel_errs(out, ref, keys)
+            assert max(errs.values()) <= TOL[4], (mode, errs)
+
+
+# ----------------------------------------------------------------------------- C5-like: float, non-empty core, 500 steps
+
+@pytest.mark.parametrize("use_tfsf", [False, True])
+def test_float_3d_with_core_500_steps(use_tfsf):
+    size, steps = (128, 64, 48), 500
+    kw = dict(size=size, pml=6, tfsf=12, use_pml=True, use_tfsf=use_tfsf, theta=65, phi=25, psi=40,
+              source_pos=(size[0] // 2, size[1] // 2, size[2] // 2))
+    cfg = O.make_config(value_type=4, exact_mode=0, **kw)
+    inputs = O.reference_setup(cfg)
+    with F.Solver(cfg) as s:
+        for a in range(3):
+            s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+        box = s.core_box
+    assert box is not None, "the float core must not be empty on this grid"
+    lo, hi = box
+    ncore = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1)
+    assert ncore >= 0.15 * size[0] * size[1] * size[2], box
+    keys = _keys(cfg)
+    ref = O.run(cfg, steps, inputs)
+    assert float(np.abs(ref["Ez"]).max()) > 0.05
+    # exact mode stays bit for bit over C5's step count
+    out_x = run_gpu(O.make_config(value_type=4, exact_mode=1, **kw), steps, inputs)
+    for k in keys:
+        assert np.array_equal(out_x[k], ref[k]), k
+    # double arithmetic as the common yardstick for the running sums D and B
+    cfg_d = O.make_config(value_type=8, exact_mode=0, **kw)
+    truth = {k: v.astype(np.float32) for k, v in O.run(cfg_d, steps, O.reference_setup(cfg_d)).items()}
+    theirs = family_rel_errs(ref, truth, keys)
+    for mode in (0, 2):
+        out = run_gpu(O.make_config(value_type=4, exact_mode=mode, **kw), steps, inputs)
+        errs = family_rel_errs(out, ref, keys)
+        ours = family_rel_errs(out, truth, keys)
+        print("float core, tfsf=%d, mode %d, %d steps: vs float reference %s | vs double: ours %s, float reference %s"
+              % (use_tfsf, mode, steps, {k: "%.1e" % errs[k] for k in keys}, {k: "%.1e" % ours[k] for k in keys if k[0] in "DB"},
+                 {k: "%.1e" % theirs[k] for k in keys if k[0] in "DB"}))
+        for k in keys:
+            if k[0] in "DB":
+                # north-star bar where it is reachable, else: no further from double arithmetic than the float reference is
+                assert errs[k] <= TOL[4] or ours[k] <= 1.25 * theirs[k] + 1e-6, (mode, k, errs[k], ours[k], theirs[k])
+            else:
+                assert errs[k] <= TOL[4], (mode, k, errs)

@@ -37,3 +37,20 @@ def test_oracle_matches_reference_dump(name):
         assert np.array_equal(out[key], data[key]), "%s differs: max |d| = %g" % (key, np.abs(out[key] - data[key]).max())
     # the run is not trivially zero
     assert np.abs(out["Ez"]).max() > 0
+
+
+@pytest.mark.parametrize("name", ["c1_d", "c1_dc"])
+def test_oracle_matches_the_reference_on_baseline_config_c1(name):
+    """BASELINE.json configs[0] as written (80^3, PML 10, TF/SF 20, 100 steps, real and complex double): the oracle
+    against the condensed dump of the unmodified reference (per-plane XOR of the raw bits of all cells, sums, planes)."""
+    import sys
+    sys.path.insert(0, G.GOLDEN_DIR)
+    import make_c1_golden as C1
+    meta, gold = G.load_c1(name)
+    cfg = O.make_config(size=meta["size"], pml=meta["pml"], tfsf=meta["tfsf"], use_pml=True, use_tfsf=True, value_type=8,
+                        complex_values=name.endswith("c"), dx=meta["dx"], wavelength=meta["wavelength"], exact_mode=1)
+    assert cfg.dt == meta["dt"] and cfg.rel_phase_velocity == meta["rel_phase_velocity"]
+    small = C1.condense(O.run(cfg, meta["steps"], O.reference_setup(cfg)))
+    assert sorted(small) == sorted(gold)
+    for key, want in gold.items():
+        assert np.array_equal(small[key], want), key
