@@ -246,6 +246,24 @@ class Solver:
             return None
         return tuple(lo), tuple(hi)
 
+    @property
+    def fused_box(self):
+        """Box advanced with one pass per step (fdtd_get_fused_box), or None."""
+        lo, hi = (C.c_int64 * 3)(), (C.c_int64 * 3)()
+        _check(lib().fdtd_get_fused_box(self._h, lo, hi))
+        if any(lo[a] > hi[a] for a in range(3)):
+            return None
+        return tuple(lo), tuple(hi)
+
+    @property
+    def fused_ms(self):
+        ms = C.c_float()
+        _check(lib().fdtd_fused_time(self._h, C.byref(ms)))
+        return ms.value
+
+    def set_tuning(self, march_planes=0, one_pass_march_planes=0, allow_one_pass=True):
+        _check(lib().fdtd_set_tuning(self._h, march_planes, one_pass_march_planes, int(allow_one_pass)))
+
     def sumsq(self, field):
         fid = FIELD_IDS[field] if isinstance(field, str) else field
         out = C.c_double()

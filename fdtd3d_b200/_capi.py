@@ -76,6 +76,9 @@ PROTOTYPES = {
     "fdtd_run_async": (C.c_int, [C.c_void_p, C.c_int64]),
     "fdtd_sync": (C.c_int, [C.c_void_p]),
     "fdtd_tfsf_face_masks": (C.c_int, [C.POINTER(Config), C.c_int, C.c_void_p, C.c_int64]),
+    "fdtd_get_fused_box": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "fdtd_fused_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "fdtd_set_tuning": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "fdtd_busy": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "fdtd_last_run_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "fdtd_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),

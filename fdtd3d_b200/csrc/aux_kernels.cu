@@ -96,18 +96,6 @@ __global__ void reorder_kernel (CellT *dev, CellT *staged, int ia, int ib, int n
   }
 }
 
-template <typename CellT, bool TO_DEVICE>
-__global__ void repitch_kernel (CellT *dev, CellT *staged, int nx, long long nrows, int pitch)
-{
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nx) return;
-  for (long long r = blockIdx.y; r < nrows; r += gridDim.y)
-  {
-    if (TO_DEVICE) dev[r * pitch + i] = staged[r * nx + i];
-    else staged[r * nx + i] = dev[r * pitch + i];
-  }
-}
-
 template <typename CellT>
 __global__ void fill_kernel (CellT *dev, long long count, CellT value)
 {
@@ -355,16 +343,6 @@ cudaError_t reorder_t (bool to_device, void *dev, void *staged, int ia, int ib, 
   return cudaGetLastError ();
 }
 
-template <typename CellT>
-cudaError_t repitch_t (bool to_device, void *dev, void *staged, int nx, long long nrows, int pitch, cudaStream_t stream)
-{
-  dim3 block (128);
-  dim3 grid ((nx + 127) / 128, (unsigned) (nrows < 16384 ? nrows : 16384));
-  if (to_device) repitch_kernel<CellT, true><<<grid, block, 0, stream>>> ((CellT *) dev, (CellT *) staged, nx, nrows, pitch);
-  else repitch_kernel<CellT, false><<<grid, block, 0, stream>>> ((CellT *) dev, (CellT *) staged, nx, nrows, pitch);
-  return cudaGetLastError ();
-}
-
 } /* namespace */
 
 template <typename T>
@@ -452,18 +430,6 @@ cudaError_t launch_reorder (bool to_device, void *dev, void *staged, int cellByt
     case 4: return reorder_t<uint32_t> (to_device, dev, staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax, stream);
     case 8: return reorder_t<unsigned long long> (to_device, dev, staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax, stream);
     case 16: return reorder_t<int4> (to_device, dev, staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax, stream);
-    default: return cudaErrorInvalidValue;
-  }
-}
-
-cudaError_t launch_repitch (bool to_device, void *dev, void *staged, int cellBytes, int nx, long long nrows, int pitch,
-                            cudaStream_t stream)
-{
-  switch (cellBytes)
-  {
-    case 4: return repitch_t<uint32_t> (to_device, dev, staged, nx, nrows, pitch, stream);
-    case 8: return repitch_t<unsigned long long> (to_device, dev, staged, nx, nrows, pitch, stream);
-    case 16: return repitch_t<int4> (to_device, dev, staged, nx, nrows, pitch, stream);
     default: return cudaErrorInvalidValue;
   }
 }

@@ -45,6 +45,15 @@ struct StepParams
 {
   /* fields: Ex Ey Ez Hx Hy Hz Dx Dy Dz Bx By Bz (scalar pointer; cell stride NC) */
   T *f[12];
+  /* where the updated Ex..Hz go: the same arrays (in place) or, when the one-pass core kernel is in use, the other
+   * buffer of the E / H ping-pong pair (kernels3d_fused.cu); D / B are always updated in place */
+  T *fo[6];
+  /* Sub-boxes a half-step launch covers when it does not cover the whole slab (the shell around the one-pass core):
+   * nreg == 0: planes [kb, ke) of all tile rows, from the launch arguments; else region r covers tile rows
+   * [jt0, jt0 + njt) and planes [kb, ke) in chunks of kc planes, and owns the CTAs [cta0, cta0 of region r + 1) of the
+   * one-dimensional grid. */
+  int nreg;
+  struct Region { int jt0, njt, kb, ke, kc, cta0; } reg[5];
   const T *eps, *mu;
   T mu_const;           /* the value of mu when the whole array holds one value (UNIMU variants of the H kernels) */
   T eps_const;          /* likewise for eps (TMz kernels) */

@@ -1,0 +1,577 @@
+/*
+ * One pass per time step inside the sigma-free core ("temporal blocking" of the two half steps), sm_100a.
+ *
+ * The two half-step kernels (kernels3d_tma.cu) move 18 field values per core cell and step: the E pass reads H and
+ * reads + writes E, the H pass reads E and reads + writes H.  This kernel reads E and H once and writes E' and H' once:
+ * 12 field values (+ eps) per cell and step.  Reference semantics preserved (Scheme3D.cpp:1986-2069): E of step t is
+ * computed from H of step t-1, then H of step t from that E; the per-cell arithmetic is the half-step kernels' own
+ * (kernels3d_common.cuh), only the schedule differs, so the tolerance of fast mode is unchanged.
+ *
+ * How the dependency H'(i,j,k) <- E'(i+1,.,.), E'(.,j+1,.), E'(.,.,k+1) is met without a grid-wide barrier:
+ *   - a CTA owns an (x, y) tile of TXC x TY cells and marches along z; in iteration k it computes E'(k) and then H'(k-1),
+ *     so the z neighbour is simply the plane it has just produced (its own E'(k-1) is carried in registers);
+ *   - the x and y neighbours that belong to the next tile are RECOMPUTED: the CTA has one more lane (33 x 16 bytes) and
+ *     one more thread row than its tile, and those rim threads evaluate E' for the first vector / row of the neighbour
+ *     tiles from the same staged data (boxes one vector wider and one row higher).  E' travels between the threads of
+ *     a CTA through a double-buffered shared-memory tile; only the tile's own cells are stored;
+ *   - a neighbour CTA may run earlier or later, so nobody may overwrite what a rim thread still has to read: E and H
+ *     are ping-pong pairs -- this kernel (and, while it is in use, the half-step kernels of the shell) reads buffer
+ *     `cur` and writes buffer `nxt` (StepParams::f / fo), and the solver swaps them after every step;
+ *   - the planes, rows and cells outside this kernel's box (the absorbing shell in y and z, slab boundary planes of a
+ *     multi-GPU run) are advanced by the half-step kernels on sub-boxes: E shell -> this kernel -> H shell.  Where a
+ *     rim row or the plane above the last one lies outside the box, E' is read from `nxt` (the E shell pass has
+ *     already written it) instead of being recomputed.
+ *
+ * The box spans the whole x range: the few lanes of the first and last x tile that lie in the x absorber take the
+ * UPML path with their D / B values (quarter-row boxes, as in the CORE half-step kernels); everything else is
+ * E' = E + (dt/dx)/(eps eps0) curl H, H' = H + (dt/dx)/(mu mu0) curl E'.  mu must be homogeneous (set with fdtd_fill):
+ * the reference never initialises it to anything but 1; otherwise the solver keeps the two-pass kernels.
+ *
+ * Data movement as in kernels3d_tma.cu: per plane one elected thread issues the TMA box copies of a stage
+ * (cp.async.bulk.tensor.3d, one mbarrier per stage, ring of S stages); results leave with 128-bit stores.
+ */
+#include <cuda.h>
+
+#include <string>
+
+#include "fdtd_device.cuh"
+#include "kernels3d_common.cuh"
+#include "launch.h"
+#include "tma_util.cuh"
+
+namespace fdtd
+{
+
+namespace
+{
+
+using namespace k3d;
+using namespace tma;
+
+#ifndef FDTD_FUSED_TY
+#define FDTD_FUSED_TY 0
+#endif
+#ifndef FDTD_FUSED_STAGES
+#define FDTD_FUSED_STAGES 0
+#endif
+#ifndef FDTD_FUSED_MINB
+#define FDTD_FUSED_MINB 0
+#endif
+
+/* maps: 0 Hz (A) 1 Hy (B) 2 Hx (C) 3..5 Ex Ey Ez 6 eps 7..9 Dx Dy Dz quarter rows 10..12 Bx By Bz quarter rows */
+struct FusedSet
+{
+  CUtensorMap m[13];
+};
+
+template <typename T, int NC>
+struct FTile
+{
+  static constexpr bool F1 = sizeof (T) == 4 && NC == 1;
+  static constexpr int TY = FDTD_FUSED_TY > 0 ? FDTD_FUSED_TY : (F1 ? 8 : 4);
+  static constexpr int LX = 33;                       /* 32 lanes of the tile + the x rim lane */
+  static constexpr int NTHREADS = LX * (TY + 1);
+  static constexpr int CELL = NC * (int) sizeof (T);
+  static constexpr int V = 16 / CELL;
+  static constexpr int TXC = 32 * V;
+  static constexpr int HM = 16 / (int) sizeof (T);
+  static constexpr int QX = 8 * V;
+  static constexpr int RW_A = (TXC + 2 * V) * CELL;   /* Hz, Hy rows: one vector of x halo on either side */
+  static constexpr int RW_C = (TXC + V) * CELL;       /* Hx, E rows: the rim vector on the high side */
+  static constexpr int MW = (TXC + V + 1 + HM - 1) / HM * HM; /* eps values per row */
+  static constexpr int RW_M = MW * (int) sizeof (T);
+  static constexpr int SZ_A = RW_A * (TY + 2);
+  static constexpr int SZ_B = RW_A * (TY + 1);
+  static constexpr int SZ_C = RW_C * (TY + 2);
+  static constexpr int SZ_E = RW_C * (TY + 1);
+  static constexpr int SZ_M = RW_M * (TY + 2);
+  static constexpr int SZ_QD = 128 * (TY + 1);        /* D of a quarter row, rim row included */
+  static constexpr int SZ_QB = 128 * TY;              /* B of a quarter row */
+  static constexpr int E_STRIDE = align128 (SZ_E);
+  static constexpr int OFF_A = 0;
+  static constexpr int OFF_B = OFF_A + align128 (SZ_A);
+  static constexpr int OFF_C = OFF_B + align128 (SZ_B);
+  static constexpr int OFF_E = OFF_C + align128 (SZ_C);
+  static constexpr int OFF_M = OFF_E + 3 * E_STRIDE;
+  static constexpr int OFF_Q = OFF_M + align128 (SZ_M);
+  static constexpr int TX_BASE = SZ_A + SZ_B + SZ_C + 3 * SZ_E + SZ_M;
+  static constexpr int X_BYTES = 3 * E_STRIDE;        /* one E' exchange buffer */
+  static constexpr int STAGES = FDTD_FUSED_STAGES > 0 ? FDTD_FUSED_STAGES : 3;
+  static constexpr int MINB = FDTD_FUSED_MINB > 0 ? FDTD_FUSED_MINB : (F1 ? 1 : 2);
+  __host__ __device__ static constexpr int stage_bytes (int nq) { return OFF_Q + nq * 3 * (SZ_QD + SZ_QB); }
+  __host__ __device__ static constexpr int smem_bytes (int nq) { return STAGES * stage_bytes (nq) + 2 * X_BYTES + 128; }
+};
+
+/* ------------------------------------------------------------------ the kernel */
+
+template <typename T, int NC, bool TFSF>
+__global__ void __launch_bounds__ ((FTile<T, NC>::NTHREADS), (FTile<T, NC>::MINB))
+step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_constant__ FusedSet maps, const FusedBox fb)
+{
+  typedef FTile<T, NC> L;
+  constexpr int V = L::V, W = V * NC, S = L::STAGES, TY = L::TY;
+  typedef Vec<T, W> FVec;
+  typedef Vec<T, V> MVec;
+
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ __align__ (8) unsigned long long full[S];
+  unsigned char *smem = reinterpret_cast<unsigned char *> ((reinterpret_cast<uintptr_t> (smem_raw) + 127) & ~(uintptr_t) 127);
+  const int stage_sz = L::stage_bytes (fb.nq);
+  unsigned char *xbuf = smem + S * stage_sz; /* two E' exchange buffers */
+
+  const int lx = threadIdx.x, ly = threadIdx.y;
+  const bool leader = lx == 0 && ly == 0;
+  const int i0t = blockIdx.x * L::TXC, j0t = fb.fy0 + blockIdx.y * TY;
+  const int k0 = fb.fz0 + blockIdx.z * fb.kc;
+  const int k1 = min (k0 + fb.kc, fb.fz1 + 1);   /* E' and H' of planes [k0, k1); iteration k1 only supplies E'(k1) */
+  if (k0 >= k1) return;
+  const int i0 = i0t + lx * V, j = j0t + ly;
+  const bool ingrid = i0 < p.nx && j < p.ny;
+  const bool own = lx < 32 && ly < TY && ingrid;  /* a cell of this CTA's tile: stored */
+  /* rim row above the last tile row of the box: a shell row, its E' is read from the E shell pass's output */
+  const bool rim_from_nxt = ly == TY && j0t + TY > fb.fy1;
+  /* the plane above the last one of the box likewise */
+  const bool top_from_nxt = k1 > fb.fz1;
+
+  /* quarters (8 lanes) of the tile row that lie in the x absorber: they carry D / B */
+  int qmask = 0;
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+  {
+    const int qa = i0t + q * L::QX, qb = qa + L::QX - 1;
+    if (qa < p.nx && !(qa >= p.core_lo[0] && qb <= p.core_hi[0])) qmask |= 1 << q;
+  }
+  const int myq = lx >> 3;
+  const bool shell = lx < 32 && ((qmask >> myq) & 1);
+  const int qrank = __popc (qmask & ((1 << myq) - 1));
+
+  auto issue = [&] (int slot, int k)
+  {
+    unsigned char *base = smem + slot * stage_sz;
+    unsigned long long *bar = &full[slot];
+    mbar_expect_tx (bar, L::TX_BASE + __popc (qmask) * 3 * (L::SZ_QD + L::SZ_QB));
+    tma_load_3d (base + L::OFF_A, &maps.m[0], bar, (i0t - V) * NC, j0t - 1, k + 1);
+    tma_load_3d (base + L::OFF_B, &maps.m[1], bar, (i0t - V) * NC, j0t, k + 1);
+    tma_load_3d (base + L::OFF_C, &maps.m[2], bar, i0t * NC, j0t - 1, k + 1);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) tma_load_3d (base + L::OFF_E + a * L::E_STRIDE, &maps.m[3 + a], bar, i0t * NC, j0t, k + 1);
+    tma_load_3d (base + L::OFF_M, &maps.m[6], bar, i0t, j0t, k + 2);
+    if (qmask)
+    {
+      int r = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if ((qmask >> q) & 1)
+        {
+#pragma unroll
+          for (int a = 0; a < 3; ++a)
+          {
+            tma_load_3d (base + L::OFF_Q + (a * fb.nq + r) * L::SZ_QD, &maps.m[7 + a], bar, (i0t + q * L::QX) * NC, j0t, k + 1);
+            /* B of plane k - 1: H'(k-1) is computed in iteration k */
+            tma_load_3d (base + L::OFF_Q + 3 * fb.nq * L::SZ_QD + (a * fb.nq + r) * L::SZ_QB, &maps.m[10 + a], bar,
+                         (i0t + q * L::QX) * NC, j0t, k);
+          }
+          ++r;
+        }
+    }
+  };
+
+  if (leader)
+  {
+    for (int s = 0; s < S; ++s) mbar_init (&full[s], 1);
+    asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads ();
+  if (leader)
+  {
+    for (int s = 0; s < S && k0 + s <= k1; ++s) issue (s, k0 + s);
+  }
+
+  long long o = (((long long) (k0 + 1) * p.ny + j) * p.pitch + i0) * NC;
+  const long long pl = p.ps * NC;
+  const long long om = ((long long) (k0 + 1) * (p.ny + 1) + j) * p.pitchM + i0;
+
+  const bool jlo = j >= 1, jhi = j < p.ny - 1;
+  const bool j_face_e = TFSF && tfsf_axis_hit (p, 1, j, true);
+  const bool j_face_h = TFSF && tfsf_axis_hit (p, 1, j, false);
+
+  /* carried from plane to plane: H of the plane below (operands of E', then the own values H' starts from), E' of the
+   * plane below, the material of this plane */
+  FVec hx_km = {}, hy_km = {}, hz_km = {};
+  FVec exm = {}, eym = {}, ezm = {};
+  MVec eps_c = {}, eps_jp = {};
+  T eps_ip = 0;
+  if (ingrid)
+  {
+    hx_km = ldv<T, W> (p.f[3] + o - pl);
+    hy_km = ldv<T, W> (p.f[4] + o - pl);
+    eps_c = ldv<T, V> (p.eps + om);
+    eps_jp = ldv<T, V> (p.eps + om + p.pitchM);
+    eps_ip = __ldg (p.eps + om + V);
+  }
+  const T cb_h = p.dt_dx * rcp_t<T> (p.mu_const * p.mu0); /* homogeneous mu: (m + m) / 2 is m exactly */
+
+  long long step = 0;
+  if (!TFSF) step = p.step;
+
+  const int xo = lx * 16;
+  const int oA_own = L::OFF_A + (ly + 1) * L::RW_A + 16 + xo, oA_jm = L::OFF_A + ly * L::RW_A + 16 + xo;
+  const int oB_own = L::OFF_B + ly * L::RW_A + 16 + xo;
+  const int oC_own = L::OFF_C + (ly + 1) * L::RW_C + xo, oC_jm = L::OFF_C + ly * L::RW_C + xo;
+  const int oE = L::OFF_E + ly * L::RW_C + xo;
+  const int oM = L::OFF_M + ly * L::RW_M + lx * V * (int) sizeof (T);
+  const int oQD = L::OFF_Q + qrank * L::SZ_QD + ly * 128 + (lx & 7) * 16;
+  const int oQB = L::OFF_Q + 3 * fb.nq * L::SZ_QD + qrank * L::SZ_QB + ly * 128 + (lx & 7) * 16;
+  const int oX = ly * L::RW_C + xo;
+
+  for (int k = k0; k <= k1; ++k, o += pl)
+  {
+    const int n = k - k0;
+    const int slot = n % S;
+    const unsigned char *st = smem + slot * stage_sz;
+    mbar_wait (&full[slot], (n / S) & 1);
+
+    const int gk = p.kz0 + k;
+    const bool klo = gk >= 1, khi = gk < p.nzg - 1;
+
+    /* ---------------- E'(k) at this thread's position (tile cell or rim) */
+    const FVec hz = lds<T, W> (st + oA_own), hz_jm = lds<T, W> (st + oA_jm);
+    const FVec hy = lds<T, W> (st + oB_own);
+    const FVec hx = lds<T, W> (st + oC_own), hx_jm = lds<T, W> (st + oC_jm);
+    T hz_im[NC], hy_im[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c)
+    {
+      hz_im[c] = *reinterpret_cast<const T *> (st + oA_own - L::CELL + c * sizeof (T));
+      hy_im[c] = *reinterpret_cast<const T *> (st + oB_own - L::CELL + c * sizeof (T));
+    }
+    FVec ex = lds<T, W> (st + oE + 0 * L::E_STRIDE);
+    FVec ey = lds<T, W> (st + oE + 1 * L::E_STRIDE);
+    FVec ez = lds<T, W> (st + oE + 2 * L::E_STRIDE);
+    const MVec eps_kp = lds<T, V> (st + oM);
+    const MVec eps_jp_next = lds<T, V> (st + oM + L::RW_M);
+    const T eps_ip_next = *reinterpret_cast<const T *> (st + oM + V * sizeof (T));
+
+    if (ingrid && !(rim_from_nxt || (k == k1 && top_from_nxt)))
+    {
+      const bool jk_face = j_face_e || (TFSF && tfsf_axis_hit (p, 2, gk, true));
+      FVec dx, dy, dz;
+      if (shell)
+      {
+        dx = lds<T, W> (st + oQD + (0 * fb.nq) * L::SZ_QD);
+        dy = lds<T, W> (st + oQD + (1 * fb.nq) * L::SZ_QD);
+        dz = lds<T, W> (st + oQD + (2 * fb.nq) * L::SZ_QD);
+      }
+#pragma unroll
+      for (int v = 0; v < V; ++v)
+      {
+        const int i = i0 + v;
+        const bool ilo = i >= 1, ihi = i < p.nx - 1;
+        const bool do_ex = ihi && jlo && klo;
+        const bool do_ey = ilo && jhi && klo;
+        const bool do_ez = ilo && jlo && khi;
+
+        T cex[NC], cey[NC], cez[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+        {
+          const int s = v * NC + c;
+          const T hz_m = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
+          const T hy_m = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
+          cex[c] = hz.v[s] - hz_jm.v[s] - hy.v[s] + hy_km.v[s];
+          cey[c] = hx.v[s] - hx_km.v[s] - hz.v[s] + hz_m;
+          cez[c] = hy.v[s] - hy_m - hx.v[s] + hx_jm.v[s];
+        }
+        if (TFSF && (jk_face || tfsf_axis_hit (p, 0, i, true)))
+        {
+          const int fx = tfsf_e_faces (p, 0, i, j, gk), fy = tfsf_e_faces (p, 1, i, j, gk), fz = tfsf_e_faces (p, 2, i, j, gk);
+          if (fx | fy | fz)
+          {
+#pragma unroll
+            for (int c = 0; c < NC; ++c)
+            {
+              const int s = v * NC + c;
+              const T hz_m = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
+              const T hy_m = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
+              if (fx) cex[c] = tfsf_curl_tab<T, NC, true> (p, 0, fx, c, i, j, k, hz.v[s], hz_jm.v[s], hy.v[s], hy_km.v[s]);
+              if (fy) cey[c] = tfsf_curl_tab<T, NC, true> (p, 1, fy, c, i, j, k, hx.v[s], hx_km.v[s], hz.v[s], hz_m);
+              if (fz) cez[c] = tfsf_curl_tab<T, NC, true> (p, 2, fz, c, i, j, k, hy.v[s], hy_m, hx.v[s], hx_jm.v[s]);
+            }
+          }
+        }
+
+        const T e_c = eps_c.v[v];
+        const T e_xp = v + 1 < V ? eps_c.v[v + 1 < V ? v + 1 : v] : eps_ip;
+        const T mod_x = ((e_c + e_xp) / (T) 2) * p.eps0;
+        const T mod_y = ((e_c + eps_jp.v[v]) / (T) 2) * p.eps0;
+        const T mod_z = ((e_c + eps_kp.v[v]) / (T) 2) * p.eps0;
+
+        if (shell)
+        {
+          /* x absorber lanes: the UPML form, coefficients straight from the tables (few lanes, L1-resident) */
+          T cbx, ccx, cby, ccy, cbz, ccz;
+          sweep3_coefs<T, false> (p.tab[0][KIND_BTW].p[i], p.tab[0][KIND_BTW].m[i], p.tab[2][KIND_AT].invp[gk], mod_x, cbx, ccx);
+          sweep3_coefs<T, false> (p.tab[1][KIND_BTW].p[j], p.tab[1][KIND_BTW].m[j], p.tab[0][KIND_AT].invp[i], mod_y, cby, ccy);
+          sweep3_coefs<T, false> (p.tab[2][KIND_BTW].p[gk], p.tab[2][KIND_BTW].m[gk], p.tab[1][KIND_AT].invp[j], mod_z, cbz, ccz);
+          const T ca_x = p.tab[0][KIND_AT].ca[i], cbd_x = p.tab[0][KIND_AT].cbd[i];
+          const T ca_y = p.tab[1][KIND_AT].ca[j], cbd_y = p.tab[1][KIND_AT].cbd[j];
+          const T ca_z = p.tab[2][KIND_AT].ca[gk], cbd_z = p.tab[2][KIND_AT].cbd[gk];
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_ex) upml_cell<T, false> (dx.v[s], ex.v[s], cex[c], ca_y, cbd_y, ca_z, cbx, ccx);
+            if (do_ey) upml_cell<T, false> (dy.v[s], ey.v[s], cey[c], ca_z, cbd_z, ca_x, cby, ccy);
+            if (do_ez) upml_cell<T, false> (dz.v[s], ez.v[s], cez[c], ca_x, cbd_x, ca_y, cbz, ccz);
+          }
+        }
+        else
+        {
+          const T cbx = plain_coef<T, false> (mod_x, p);
+          const T cby = plain_coef<T, false> (mod_y, p);
+          const T cbz = plain_coef<T, false> (mod_z, p);
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_ex) ex.v[s] = plain_cell<T, NC, false> (ex.v[s], cex[c], cbx);
+            if (do_ey) ey.v[s] = plain_cell<T, NC, false> (ey.v[s], cey[c], cby);
+            if (do_ez) ez.v[s] = plain_cell<T, NC, false> (ez.v[s], cez[c], cbz);
+          }
+        }
+
+        if (!TFSF)
+        {
+          if (gk == p.srcpos[2] && j == p.srcpos[1] && i == p.srcpos[0])
+          {
+            /* the source overwrites Ez but not Dz (Scheme3D.cpp:1995-2024); see e_phase_3d_tma */
+            if (!shell && do_ez && own && k < k1)
+            {
+#pragma unroll
+              for (int c = 0; c < NC; ++c) p.f[8][o + v * NC + c] = fma_t<T> (p.tab[0][KIND_AT].cbd[i], cez[c], p.f[8][o + v * NC + c]);
+            }
+#pragma unroll
+            for (int c = 0; c < NC; ++c) ez.v[v * NC + c] = p.src[step * NC + c];
+          }
+        }
+      }
+      if (own && k < k1)
+      {
+        stv<T, W> (p.fo[0] + o, ex); stv<T, W> (p.fo[1] + o, ey); stv<T, W> (p.fo[2] + o, ez);
+        if (shell)
+        {
+          stv<T, W> (p.f[6] + o, dx); stv<T, W> (p.f[7] + o, dy); stv<T, W> (p.f[8] + o, dz);
+        }
+      }
+    }
+    else if (ingrid)
+    {
+      /* outside the box: E' as the E shell pass wrote it */
+      ex = ldv_rw<T, W> (p.fo[0] + o);
+      ey = ldv_rw<T, W> (p.fo[1] + o);
+      ez = ldv_rw<T, W> (p.fo[2] + o);
+    }
+
+    /* ---------------- H'(k-1) of the tile's own cells: E'(k-1) of the neighbours from the exchange buffer written in
+     * the previous iteration, E'(k-1) of this cell and H(k-1) from registers, E'x, E'y (k) just computed */
+    if (k > k0 && own)
+    {
+      const int m = k - 1, gm = gk - 1;
+      const bool mlo = gm >= 1, mhi = gm < p.nzg - 1;
+      const unsigned char *xb = xbuf + (m & 1) * L::X_BYTES + oX;
+      const FVec ex_jp = lds<T, W> (xb + 0 * L::E_STRIDE + L::RW_C);
+      const FVec ez_jp = lds<T, W> (xb + 2 * L::E_STRIDE + L::RW_C);
+      T ey_ip[NC], ez_ip[NC];
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+      {
+        ey_ip[c] = *reinterpret_cast<const T *> (xb + 1 * L::E_STRIDE + 16 + c * sizeof (T));
+        ez_ip[c] = *reinterpret_cast<const T *> (xb + 2 * L::E_STRIDE + 16 + c * sizeof (T));
+      }
+      const bool mk_face = j_face_h || (TFSF && tfsf_axis_hit (p, 2, gm, false));
+      FVec bx, by, bz;
+      if (shell)
+      {
+        bx = lds<T, W> (st + oQB + (0 * fb.nq) * L::SZ_QB);
+        by = lds<T, W> (st + oQB + (1 * fb.nq) * L::SZ_QB);
+        bz = lds<T, W> (st + oQB + (2 * fb.nq) * L::SZ_QB);
+      }
+      FVec hxn = hx_km, hyn = hy_km, hzn = hz_km;
+#pragma unroll
+      for (int v = 0; v < V; ++v)
+      {
+        const int i = i0 + v;
+        const bool ilo = i >= 1, ihi = i < p.nx - 1;
+        const bool do_hx = ilo && jhi && mhi;
+        const bool do_hy = ihi && jlo && mhi;
+        const bool do_hz = ihi && jhi && mlo;
+        T chx[NC], chy[NC], chz[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+        {
+          const int s = v * NC + c;
+          const T ez_p = v + 1 < V ? ezm.v[v + 1 < V ? s + NC : s] : ez_ip[c];
+          const T ey_p = v + 1 < V ? eym.v[v + 1 < V ? s + NC : s] : ey_ip[c];
+          chx[c] = ey.v[s] - eym.v[s] - ez_jp.v[s] + ezm.v[s];
+          chy[c] = ez_p - ezm.v[s] - ex.v[s] + exm.v[s];
+          chz[c] = ex_jp.v[s] - exm.v[s] - ey_p + eym.v[s];
+        }
+        if (TFSF && (mk_face || tfsf_axis_hit (p, 0, i, false)))
+        {
+          const int fx = tfsf_h_faces (p, 0, i, j, gm), fy = tfsf_h_faces (p, 1, i, j, gm), fz = tfsf_h_faces (p, 2, i, j, gm);
+          if (fx | fy | fz)
+          {
+#pragma unroll
+            for (int c = 0; c < NC; ++c)
+            {
+              const int s = v * NC + c;
+              const T ez_p = v + 1 < V ? ezm.v[v + 1 < V ? s + NC : s] : ez_ip[c];
+              const T ey_p = v + 1 < V ? eym.v[v + 1 < V ? s + NC : s] : ey_ip[c];
+              if (fx) chx[c] = tfsf_curl_tab<T, NC, false> (p, 0, fx, c, i, j, m, ey.v[s], eym.v[s], ez_jp.v[s], ezm.v[s]);
+              if (fy) chy[c] = tfsf_curl_tab<T, NC, false> (p, 1, fy, c, i, j, m, ez_p, ezm.v[s], ex.v[s], exm.v[s]);
+              if (fz) chz[c] = tfsf_curl_tab<T, NC, false> (p, 2, fz, c, i, j, m, ex_jp.v[s], exm.v[s], ey_p, eym.v[s]);
+            }
+          }
+        }
+        if (shell)
+        {
+          const T mod = p.mu_const * p.mu0;
+          T cbx, ccx, cby, ccy, cbz, ccz;
+          sweep3_coefs<T, false> (p.tab[0][KIND_AT].p[i], p.tab[0][KIND_AT].m[i], p.tab[2][KIND_BTW].invp[gm], mod, cbx, ccx);
+          sweep3_coefs<T, false> (p.tab[1][KIND_AT].p[j], p.tab[1][KIND_AT].m[j], p.tab[0][KIND_BTW].invp[i], mod, cby, ccy);
+          sweep3_coefs<T, false> (p.tab[2][KIND_AT].p[gm], p.tab[2][KIND_AT].m[gm], p.tab[1][KIND_BTW].invp[j], mod, cbz, ccz);
+          const T ca_x = p.tab[0][KIND_BTW].ca[i], cbd_x = p.tab[0][KIND_BTW].cbd[i];
+          const T ca_y = p.tab[1][KIND_BTW].ca[j], cbd_y = p.tab[1][KIND_BTW].cbd[j];
+          const T ca_z = p.tab[2][KIND_BTW].ca[gm], cbd_z = p.tab[2][KIND_BTW].cbd[gm];
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_hx) upml_cell<T, false> (bx.v[s], hxn.v[s], chx[c], ca_y, cbd_y, ca_z, cbx, ccx);
+            if (do_hy) upml_cell<T, false> (by.v[s], hyn.v[s], chy[c], ca_z, cbd_z, ca_x, cby, ccy);
+            if (do_hz) upml_cell<T, false> (bz.v[s], hzn.v[s], chz[c], ca_x, cbd_x, ca_y, cbz, ccz);
+          }
+        }
+        else
+        {
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+          {
+            const int s = v * NC + c;
+            if (do_hx) hxn.v[s] = plain_cell<T, NC, false> (hxn.v[s], chx[c], cb_h);
+            if (do_hy) hyn.v[s] = plain_cell<T, NC, false> (hyn.v[s], chy[c], cb_h);
+            if (do_hz) hzn.v[s] = plain_cell<T, NC, false> (hzn.v[s], chz[c], cb_h);
+          }
+        }
+      }
+      stv<T, W> (p.fo[3] + o - pl, hxn); stv<T, W> (p.fo[4] + o - pl, hyn); stv<T, W> (p.fo[5] + o - pl, hzn);
+      if (shell)
+      {
+        stv<T, W> (p.f[9] + o - pl, bx); stv<T, W> (p.f[10] + o - pl, by); stv<T, W> (p.f[11] + o - pl, bz);
+      }
+    }
+
+    /* ---------------- hand E'(k) to the neighbours in the CTA, shift the plane-carried values */
+    if (k < k1)
+    {
+      unsigned char *xw = xbuf + (k & 1) * L::X_BYTES + oX;
+      *reinterpret_cast<FVec *> (xw + 0 * L::E_STRIDE) = ex;
+      *reinterpret_cast<FVec *> (xw + 1 * L::E_STRIDE) = ey;
+      *reinterpret_cast<FVec *> (xw + 2 * L::E_STRIDE) = ez;
+    }
+    exm = ex; eym = ey; ezm = ez;
+    hx_km = hx; hy_km = hy; hz_km = hz;
+    eps_c = eps_kp; eps_jp = eps_jp_next; eps_ip = eps_ip_next;
+
+    /* every thread has read the stage and the older exchange buffer: refill the slot with plane k + S */
+    __syncthreads ();
+    if (leader && k + S <= k1) issue (slot, k + S);
+  }
+}
+
+/* ------------------------------------------------------------------ host side */
+
+template <typename T, int NC>
+bool prepare_fused_t (FusedMaps3D *out, void *const e[3], void *const h[3], void *const d[3], void *const b[3], void *eps,
+                      int pitch, int ny, int planes, int pitchM, int planesM, std::string *err)
+{
+  typedef FTile<T, NC> L;
+  static_assert (sizeof (FusedSet) <= sizeof (out->set), "FusedMaps3D too small");
+  FusedSet *m = reinterpret_cast<FusedSet *> (out->set);
+  const int sb = (int) sizeof (T);
+  const long long xs = (long long) pitch * NC;
+  bool ok = true;
+  ok = ok && encode (&m->m[0], h[2], sb, xs, ny, planes, (L::TXC + 2 * L::V) * NC, L::TY + 2, err);
+  ok = ok && encode (&m->m[1], h[1], sb, xs, ny, planes, (L::TXC + 2 * L::V) * NC, L::TY + 1, err);
+  ok = ok && encode (&m->m[2], h[0], sb, xs, ny, planes, (L::TXC + L::V) * NC, L::TY + 2, err);
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&m->m[3 + a], e[a], sb, xs, ny, planes, (L::TXC + L::V) * NC, L::TY + 1, err);
+  ok = ok && encode (&m->m[6], eps, sb, pitchM, ny + 1, planesM, L::MW, L::TY + 2, err);
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&m->m[7 + a], d[a], sb, xs, ny, planes, L::QX * NC, L::TY + 1, err);
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&m->m[10 + a], b[a], sb, xs, ny, planes, L::QX * NC, L::TY, err);
+  out->valid = ok;
+  return ok;
+}
+
+template <typename T, int NC, bool TFSF>
+cudaError_t launch_fused_t (const StepParams<T> &p, const FusedSet &maps, const FusedBox &fb, cudaStream_t stream)
+{
+  typedef FTile<T, NC> L;
+  const int smem = L::smem_bytes (fb.nq);
+  static int attr_dev[64] = {};
+  int dev = 0;
+  cudaError_t de = cudaGetDevice (&dev);
+  if (de != cudaSuccess) return de;
+  if (attr_dev[dev & 63] < smem)
+  {
+    cudaError_t e = cudaFuncSetAttribute (step_core_3d_fused<T, NC, TFSF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_dev[dev & 63] = smem;
+  }
+  const int rows = fb.fy1 - fb.fy0 + 1, planes = fb.fz1 - fb.fz0 + 1;
+  if (rows <= 0 || planes <= 0) return cudaSuccess;
+  dim3 block (L::LX, L::TY + 1);
+  dim3 grid ((p.nx + L::TXC - 1) / L::TXC, rows / L::TY, (planes + fb.kc - 1) / fb.kc);
+  step_core_3d_fused<T, NC, TFSF><<<grid, block, smem, stream>>> (p, maps, fb);
+  return cudaGetLastError ();
+}
+
+} /* namespace */
+
+void fused_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *ctas_per_sm, int *smem_per_quarter,
+                          int *smem_base)
+{
+#define GEOM(T, NC) do { typedef FTile<T, NC> L; if (tile_cells_x) *tile_cells_x = L::TXC; if (tile_rows) *tile_rows = L::TY; \
+    if (ctas_per_sm) *ctas_per_sm = L::MINB; if (smem_per_quarter) *smem_per_quarter = L::smem_bytes (1) - L::smem_bytes (0); \
+    if (smem_base) *smem_base = L::smem_bytes (0); } while (0)
+  if (value_type == 4 && nc == 1) GEOM (float, 1);
+  else if (value_type == 4) GEOM (float, 2);
+  else if (nc == 1) GEOM (double, 1);
+  else GEOM (double, 2);
+#undef GEOM
+}
+
+bool fused_prepare_3d (FusedMaps3D *out, int value_type, int nc, void *const e[3], void *const h[3], void *const d[3],
+                       void *const b[3], void *eps, int pitch, int ny, int planes, int pitchM, int planesM, std::string *err)
+{
+  out->valid = false;
+  if (value_type == 4)
+    return nc == 2 ? prepare_fused_t<float, 2> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err)
+                   : prepare_fused_t<float, 1> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err);
+  return nc == 2 ? prepare_fused_t<double, 2> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err)
+                 : prepare_fused_t<double, 1> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err);
+}
+
+template <typename T>
+cudaError_t launch_step_core_fused (const StepParams<T> &p, const FusedMaps3D &maps, const FusedBox &fb, bool cplx, bool tfsf,
+                                    cudaStream_t stream)
+{
+  const FusedSet &set = *reinterpret_cast<const FusedSet *> (maps.set);
+  if (cplx)
+    return tfsf ? launch_fused_t<T, 2, true> (p, set, fb, stream) : launch_fused_t<T, 2, false> (p, set, fb, stream);
+  return tfsf ? launch_fused_t<T, 1, true> (p, set, fb, stream) : launch_fused_t<T, 1, false> (p, set, fb, stream);
+}
+
+template cudaError_t launch_step_core_fused<float> (const StepParams<float> &, const FusedMaps3D &, const FusedBox &, bool, bool, cudaStream_t);
+template cudaError_t launch_step_core_fused<double> (const StepParams<double> &, const FusedMaps3D &, const FusedBox &, bool, bool, cudaStream_t);
+
+} /* namespace fdtd */

@@ -41,6 +41,7 @@
 #include "fdtd_device.cuh"
 #include "kernels3d_common.cuh"
 #include "launch.h"
+#include "tma_util.cuh"
 
 namespace fdtd
 {
@@ -49,6 +50,7 @@ namespace
 {
 
 using namespace k3d;
+using namespace tma;
 
 /* tuning knobs: rows per CTA tile (0 = by value type, see Tile), ring depth (0 = as many as fit in 200 KB, at
  * most 4), CTAs per SM the register allocator must allow */
@@ -78,7 +80,6 @@ struct TmaSet
   CUtensorMap m[N_MAPS];
 };
 
-__host__ __device__ constexpr int align128 (int x) { return (x + 127) & ~127; }
 
 /*
  * Rows per CTA tile = warps per CTA, and with it the occupancy recipe.  Two configurations per value type:
@@ -144,49 +145,6 @@ struct Tile
   static constexpr int SMEM = STAGES * STAGE + 128;
 };
 
-/* ------------------------------------------------------------------ PTX wrappers */
-
-__device__ __forceinline__ unsigned smem_u32 (const void *p) { return (unsigned) __cvta_generic_to_shared (p); }
-
-__device__ __forceinline__ void mbar_init (unsigned long long *bar, int count)
-{
-  asm volatile ("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32 (bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx (unsigned long long *bar, unsigned bytes)
-{
-  asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32 (bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait (unsigned long long *bar, unsigned parity)
-{
-  unsigned ok;
-  asm volatile ("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                : "=r"(ok) : "r"(smem_u32 (bar)), "r"(parity) : "memory");
-  return ok != 0;
-}
-/* bounded wait: a mis-programmed pipeline traps (reported as a CUDA error) instead of hanging the GPU */
-__device__ __forceinline__ void mbar_wait (unsigned long long *bar, unsigned parity)
-{
-  unsigned tries = 0;
-  while (!mbar_try_wait (bar, parity))
-  {
-    if (++tries > (1u << 26)) __trap ();
-  }
-}
-__device__ __forceinline__ void tma_load_3d (void *dst, const CUtensorMap *map, unsigned long long *bar, int x, int y, int z)
-{
-  asm volatile ("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-                ::"r"(smem_u32 (dst)), "l"(map), "r"(smem_u32 (bar)), "r"(x), "r"(y), "r"(z) : "memory");
-}
-
-template <typename T, int W>
-__device__ __forceinline__ Vec<T, W> lds (const unsigned char *p)
-{
-  typedef typename RawVec<sizeof (T) * W>::type R;
-  Vec<T, W> r;
-  *reinterpret_cast<R *> (&r) = *reinterpret_cast<const R *> (p);
-  return r;
-}
-
 /*
  * CORE variants: which quarters (8 lanes) of a tile row need their D / B values.  `full`: every quarter that holds
  * grid cells (planes outside the z core, tiles outside the y core); `core`: in planes of the z core, the quarters
@@ -209,6 +167,37 @@ __device__ __forceinline__ void quarter_masks (const StepParams<T> &p, int i0t, 
   }
 }
 
+/*
+ * Which tile and which planes this CTA works on: the whole slab in a 3-D grid (x tiles, tile rows, plane chunks), or
+ * one of the sub-boxes of p.reg in a flat grid (StepParams::reg).  Returns false if the CTA has nothing to do.
+ */
+template <typename L, typename T>
+__device__ __forceinline__ bool cta_work (const StepParams<T> &p, int kb, int ke, int &i0t, int &j0t, int &k0, int &k1)
+{
+  if (p.nreg == 0)
+  {
+    i0t = blockIdx.x * L::TXC;
+    j0t = blockIdx.y * L::TY;
+    k0 = kb + blockIdx.z * p.kchunk;
+    k1 = min (k0 + p.kchunk, ke);
+    return k0 < k1;
+  }
+  int r = 0;
+#pragma unroll
+  for (int q = 1; q < 5; ++q)
+    if (q < p.nreg && (int) blockIdx.x >= p.reg[q].cta0) r = q;
+  const int ntx = (p.nx + L::TXC - 1) / L::TXC;
+  int c = blockIdx.x - p.reg[r].cta0;
+  const int bx = c % ntx;
+  c /= ntx;
+  const int by = c % p.reg[r].njt, bz = c / p.reg[r].njt;
+  i0t = bx * L::TXC;
+  j0t = (p.reg[r].jt0 + by) * L::TY;
+  k0 = p.reg[r].kb + bz * p.reg[r].kc;
+  k1 = min (k0 + p.reg[r].kc, p.reg[r].ke);
+  return k0 < k1;
+}
+
 /* ------------------------------------------------------------------ E half step */
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE>
@@ -227,12 +216,10 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
   const int tx = threadIdx.x, ty = threadIdx.y;
   const bool leader = tx == 0 && ty == 0;
-  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * L::TY;
+  int i0t, j0t, k0, k1;
+  if (!cta_work<L> (p, kb, ke, i0t, j0t, k0, k1)) return; /* uniform over the CTA */
   const int i0 = i0t + tx * V, j = j0t + ty;
   const bool active = i0 < p.nx && j < p.ny;
-  const int k0 = kb + blockIdx.z * p.kchunk;
-  const int k1 = min (k0 + p.kchunk, ke);
-  if (k0 >= k1) return; /* uniform over the CTA */
 
   /* CORE: quarters of the tile row whose D values are needed -- all that hold cells in planes outside the z core
    * or in tiles outside the y core, else only those that stick out of the x core */
@@ -285,7 +272,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   const long long pl = p.ps * NC;
   const long long om = ((long long) (k0 + 1) * (p.ny + 1) + j) * p.pitchM + i0;
 
-  T *Ex = p.f[0], *Ey = p.f[1], *Ez = p.f[2];
+  T *Ex = p.fo[0], *Ey = p.fo[1], *Ez = p.fo[2]; /* stores only: the operands come from the stage */
   T *Dx = p.f[6], *Dy = p.f[7], *Dz = p.f[8];
 
   const bool jlo = j >= 1, jhi = j < p.ny - 1;
@@ -515,12 +502,10 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
 
   const int tx = threadIdx.x, ty = threadIdx.y;
   const bool leader = tx == 0 && ty == 0;
-  const int i0t = blockIdx.x * L::TXC, j0t = blockIdx.y * L::TY;
+  int i0t, j0t, k0, k1;
+  if (!cta_work<L> (p, kb, ke, i0t, j0t, k0, k1)) return; /* uniform over the CTA */
   const int i0 = i0t + tx * V, j = j0t + ty;
   const bool active = i0 < p.nx && j < p.ny;
-  const int k0 = kb + blockIdx.z * p.kchunk;
-  const int k1 = min (k0 + p.kchunk, ke);
-  if (k0 >= k1) return;
 
   int qmask_full = 0, qmask_core = 0; /* see e_phase_3d_tma */
   if (CORE) quarter_masks<L> (p, i0t, j0t, qmask_full, qmask_core);
@@ -573,7 +558,7 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   const long long pl = p.ps * NC;
   const long long om = ((long long) (k0 + 1) * (p.ny + 1) + j) * p.pitchM + i0;
 
-  T *Hx = p.f[3], *Hy = p.f[4], *Hz = p.f[5];
+  T *Hx = p.fo[3], *Hy = p.fo[4], *Hz = p.fo[5]; /* stores only */
   T *Bx = p.f[9], *By = p.f[10], *Bz = p.f[11];
 
   const bool jlo = j >= 1, jhi = j < p.ny - 1;
@@ -805,13 +790,27 @@ template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE = false
 cudaError_t launch_t (bool e_phase, bool unimu, const StepParams<T> &p, const TmaSet &maps, int kb, int ke, cudaStream_t stream)
 {
   typedef Tile<T, NC, PML, (CORE || EXACT)> L;
-  if (ke <= kb) return cudaSuccess;
   constexpr int smem = L::SMEM;
   dim3 block (32, L::TY);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (p.ny + L::TY - 1) / L::TY, (ke - kb + p.kchunk - 1) / p.kchunk);
+  StepParams<T> pr = p;
+  if (p.nreg > 0)
+  {
+    /* flat grid over the sub-boxes: region r owns CTAs [cta0 (r), cta0 (r + 1)) */
+    int total = 0;
+    for (int r = 0; r < p.nreg; ++r)
+    {
+      pr.reg[r].cta0 = total;
+      const int planes = p.reg[r].ke - p.reg[r].kb;
+      if (planes > 0 && p.reg[r].njt > 0) total += (int) grid.x * p.reg[r].njt * ((planes + p.reg[r].kc - 1) / p.reg[r].kc);
+    }
+    if (total == 0) return cudaSuccess;
+    grid = dim3 (total, 1, 1);
+  }
+  else if (ke <= kb) return cudaSuccess;
   if (!e_phase)
-    return unimu ? launch_h<T, NC, PML, TFSF, EXACT, CORE, true> (p, maps, grid, block, smem, kb, ke, stream)
-                 : launch_h<T, NC, PML, TFSF, EXACT, CORE, false> (p, maps, grid, block, smem, kb, ke, stream);
+    return unimu ? launch_h<T, NC, PML, TFSF, EXACT, CORE, true> (pr, maps, grid, block, smem, kb, ke, stream)
+                 : launch_h<T, NC, PML, TFSF, EXACT, CORE, false> (pr, maps, grid, block, smem, kb, ke, stream);
   /* the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute */
   static bool attr_e_dev[64] = {};
   int dev = 0;
@@ -823,7 +822,7 @@ cudaError_t launch_t (bool e_phase, bool unimu, const StepParams<T> &p, const Tm
     if (e != cudaSuccess) return e;
     attr_e_dev[dev & 63] = true;
   }
-  e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, smem, stream>>> (p, maps, kb, ke);
+  e_phase_3d_tma<T, NC, PML, TFSF, EXACT, CORE><<<grid, block, smem, stream>>> (pr, maps, kb, ke);
   return cudaGetLastError ();
 }
 
@@ -849,47 +848,6 @@ cudaError_t launch_nc (bool e_phase, bool unimu, const StepParams<T> &p, const T
 }
 
 /* ------------------------------------------------------------------ tensor maps (host) */
-
-typedef CUresult (*EncodeTiledFn) (CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn (std::string *err)
-{
-  static EncodeTiledFn fn = NULL;
-  static bool tried = false;
-  if (!tried)
-  {
-    tried = true;
-    void *ptr = NULL;
-    cudaDriverEntryPointQueryResult q;
-    cudaError_t e = cudaGetDriverEntryPoint ("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q);
-    if (e == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (EncodeTiledFn) ptr;
-  }
-  if (!fn && err) *err = "cuTensorMapEncodeTiled is not available from the CUDA driver";
-  return fn;
-}
-
-/* 3-D tensor of `scalar_bytes` scalars: x extent xs scalars (row pitch), ny rows, nplanes planes; box bx x by x 1 */
-bool encode (CUtensorMap *out, void *base, int scalar_bytes, long long xs, long long ny, long long nplanes, int bx, int by,
-             std::string *err)
-{
-  EncodeTiledFn fn = encode_fn (err);
-  if (!fn) return false;
-  cuuint64_t gdim[3] = { (cuuint64_t) xs, (cuuint64_t) ny, (cuuint64_t) nplanes };
-  cuuint64_t gstride[2] = { (cuuint64_t) xs * scalar_bytes, (cuuint64_t) xs * ny * scalar_bytes };
-  cuuint32_t box[3] = { (cuuint32_t) bx, (cuuint32_t) by, 1 };
-  cuuint32_t estr[3] = { 1, 1, 1 };
-  CUresult r = fn (out, scalar_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, gdim,
-                   gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS)
-  {
-    if (err) *err = "cuTensorMapEncodeTiled failed with CUresult " + std::to_string ((int) r);
-    return false;
-  }
-  return true;
-}
 
 template <typename T, int NC, bool ALT>
 bool prepare_tt (TmaMaps3D *out, bool pml, void *const f[12], void *eps, void *mu, int pitch, int ny, int planes, int pitchM,

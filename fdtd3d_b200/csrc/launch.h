@@ -1,5 +1,5 @@
 /*
- * Host-callable launch wrappers of the kernel translation units (kernels3d.cu, kernels2d.cu, aux_kernels.cu).
+ * Host-callable launch wrappers of the kernel translation units (kernels3d_tma.cu, kernels3d_fused.cu, kernels2d.cu, aux_kernels.cu).
  * Every wrapper launches exactly one kernel on `stream` and returns cudaGetLastError().
  */
 #ifndef FDTD_LAUNCH_H
@@ -11,11 +11,6 @@
 
 namespace fdtd
 {
-
-/* 3D half steps over local planes [kb, ke) (kernels3d.cu) */
-template <typename T>
-cudaError_t launch_phase_3d (bool e_phase, const StepParams<T> &p, bool cplx, bool pml, bool tfsf, bool exact,
-                             int kb, int ke, cudaStream_t stream);
 
 /* TMA-staged 3D half steps (kernels3d_tma.cu).  TmaMaps3D holds the CUtensorMap descriptors (13 per phase,
  * 128 bytes each) of one solver's arrays; tma_prepare_3d encodes them once the arrays are allocated.
@@ -36,6 +31,30 @@ bool tma_prepare_3d (TmaMaps3D *out, int value_type, int nc, bool pml, bool alt,
 template <typename T>
 cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const TmaMaps3D &maps, bool cplx, bool pml, bool tfsf,
                                  bool exact, bool core, bool uniform_mu, int kb, int ke, cudaStream_t stream);
+
+/*
+ * One-pass core kernel (kernels3d_fused.cu): E and H of one whole time step inside a box of the slab, reading the
+ * `cur` buffers (p.f) and writing the `nxt` buffers (p.fo) of the E / H ping-pong pairs.  FusedBox: rows [fy0, fy1]
+ * (a whole number of the kernel's tile rows, inside the y core), local planes [fz0, fz1] (inside the z core), kc planes
+ * marched per CTA, nq = the largest number of quarter rows of one x tile that lie in the x absorber (sizes the D / B
+ * part of a stage).  The box always spans the whole x range.  FusedMaps3D: the 13 tensor maps for one buffer parity.
+ */
+struct FusedBox
+{
+  int fy0, fy1, fz0, fz1, kc, nq;
+};
+struct FusedMaps3D
+{
+  alignas (64) unsigned char set[13 * 128];
+  bool valid;
+};
+void fused_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *ctas_per_sm, int *smem_per_quarter,
+                          int *smem_base);
+bool fused_prepare_3d (FusedMaps3D *out, int value_type, int nc, void *const e[3], void *const h[3], void *const d[3],
+                       void *const b[3], void *eps, int pitch, int ny, int planes, int pitchM, int planesM, std::string *err);
+template <typename T>
+cudaError_t launch_step_core_fused (const StepParams<T> &p, const FusedMaps3D &maps, const FusedBox &fb, bool cplx, bool tfsf,
+                                    cudaStream_t stream);
 
 /* D (B) -= / += eps eps0 E (mu mu0 H) over the core box, for the six components (aux_kernels.cu): `fold` before
  * running the CORE variants, unfold before anything else reads or replaces D / B / E / H / eps / mu */
@@ -72,10 +91,6 @@ cudaError_t launch_scattered (const StepParams<T> &p, bool cplx, int comp, cudaS
  */
 cudaError_t launch_reorder (bool to_device, void *dev, void *staged, int cellBytes, int ia, int ib, int ny, int nzb,
                             int pitch, long long ps, int kofs, int kmin, int kmax, cudaStream_t stream);
-
-/* native-order (x fastest, unpadded) <-> device layout, rows [0, nrows) of nx cells */
-cudaError_t launch_repitch (bool to_device, void *dev, void *staged, int cellBytes, int nx, long long nrows, int pitch,
-                            cudaStream_t stream);
 
 /* fill `count` cells of `cellBytes` (4, 8 or 16) with a 16-byte pattern */
 cudaError_t launch_fill (void *dev, long long count, int cellBytes, const void *pattern16, cudaStream_t stream);

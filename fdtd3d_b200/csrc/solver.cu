@@ -101,6 +101,22 @@ struct fdtd_solver
   bool comm_failed;   /* a send / recv of the halo exchange failed: the handle refuses further multi-rank runs */
 
   TmaMaps3D tma;        /* tensor maps of the TMA-staged 3D kernels */
+
+  /* One pass per step inside the core (kernels3d_fused.cu): E and H become ping-pong pairs.  fA is the allocation
+   * fdtd_create made, fB the second one; f[0..5] always point at the buffers that hold the current fields (parity 0:
+   * fA), so everything outside the time loop is unaware of the pair. */
+  void *fA[6], *fB[6];
+  int parity;
+  bool fused_ok;        /* geometry allows it and the second buffers exist */
+  bool fused_run;       /* the run being queued uses it (fused_ok and mu homogeneous) */
+  FusedBox fbox;
+  int shell_ty;         /* rows per tile of the half-step kernels that advance the shell */
+  FusedMaps3D fmaps[2]; /* per parity: reads the current buffers */
+  TmaMaps3D tma_pp[2];  /* per parity, half-step kernels of the shell: E phase reads cur, H phase reads E of nxt */
+  int fused_kc;         /* planes marched per CTA of the fused kernel; 0 = default rule */
+  int kchunk_forced;    /* fdtd_set_tuning: planes marched per CTA of the half-step kernels; 0 = default rule */
+  bool fused_forbidden; /* fdtd_set_tuning: keep the two-pass kernels (A/B measurements) */
+  float prof_f_ms;
   bool use_tma;
   int kchunk;
 
@@ -136,6 +152,8 @@ static StepParams<T> make_params (const fdtd_solver *s)
   memset (&p, 0, sizeof (p));
   const fdtd_config &c = s->cfg;
   for (int i = 0; i < 12; ++i) p.f[i] = (T *) s->f[i];
+  for (int i = 0; i < 6; ++i) p.fo[i] = (T *) s->f[i]; /* in place unless the time loop says otherwise */
+  p.nreg = 0;
   p.eps = (const T *) s->eps;
   p.mu = (const T *) s->mu;
   p.mu_const = (T) s->mu_value;
@@ -308,7 +326,7 @@ static int upload_source (fdtd_solver *s, long long n)
 
 /* H phase -> E phase: top owned plane of Hx, Hy goes to the upper neighbour's low halo;
  * E phase -> H phase: bottom owned plane of Ex, Ey goes to the lower neighbour's high halo. */
-static int exchange (fdtd_solver *s, bool h_fields)
+static int exchange (fdtd_solver *s, bool h_fields, void *const *fld)
 {
   const char *why = NULL;
   const NcclApi *nccl = nccl_api (&why);
@@ -324,7 +342,7 @@ static int exchange (fdtd_solver *s, bool h_fields)
   {
     for (int f = FDTD_HX; f <= FDTD_HY; ++f)
     {
-      char *base = (char *) s->f[f];
+      char *base = (char *) fld[f];
       if (r + 1 < n) IN_GROUP (nccl->Send (base + (size_t) s->nzl * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
       if (r > 0) IN_GROUP (nccl->Recv (base, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
     }
@@ -333,7 +351,7 @@ static int exchange (fdtd_solver *s, bool h_fields)
   {
     for (int f = FDTD_EX; f <= FDTD_EY; ++f)
     {
-      char *base = (char *) s->f[f];
+      char *base = (char *) fld[f];
       if (r > 0) IN_GROUP (nccl->Send (base + plane_bytes, plane_bytes, NCCL_INT8, r - 1, s->comm, s->s_comm));
       if (r + 1 < n) IN_GROUP (nccl->Recv (base + (size_t) (s->nzl + 1) * plane_bytes, plane_bytes, NCCL_INT8, r + 1, s->comm, s->s_comm));
     }
@@ -400,11 +418,16 @@ static void update_core (fdtd_solver *s)
  * EXACT variants use other tiles than the plain fast ones (kernels3d_tma.cu, TileRows), and whether the core is on
  * depends on the sigma profiles, so this runs at creation and again when fdtd_set_sigma changes the answer.
  */
+static int configure_fused (fdtd_solver *s);
+static int normalize_parity (fdtd_solver *s);
+
 static int configure_3d (fdtd_solver *s, bool first)
 {
   if (s->cfg.dims != 3) return FDTD_OK;
   const bool alt = s->cfg.exact_mode == 1 || s->core_on;
-  if (!first && alt == s->tma_alt) return FDTD_OK;
+  int rc0 = normalize_parity (s); /* the maps below describe the first allocation */
+  if (rc0) return rc0;
+  if (!first && alt == s->tma_alt) return configure_fused (s); /* the core box may have moved all the same */
   s->tma_alt = alt;
   int txc = 32 * (16 / s->cell), tyr = 8, per_sm = 1; /* cells per CTA tile row, rows per CTA tile, resident CTAs per SM */
   if (s->use_tma) tma_tile_geometry (s->fp, s->nc, alt, &txc, &tyr, NULL, &per_sm);
@@ -418,12 +441,7 @@ static int configure_3d (fdtd_solver *s, bool first)
   int kc = (int) kc_ll;
   if (kc > 64) kc = 64;
   if (kc < 4) kc = 4;
-  s->kchunk = kc;
-  if (const char *kc_env = getenv ("FDTD3D_B200_KCHUNK")) /* tuning aid: planes marched per CTA */
-  {
-    const int v = atoi (kc_env);
-    if (v > 0) s->kchunk = v;
-  }
+  s->kchunk = s->kchunk_forced > 0 ? s->kchunk_forced : kc;
   if (s->use_tma)
   {
     std::string err;
@@ -431,6 +449,114 @@ static int configure_3d (fdtd_solver *s, bool first)
                          s->pitchM, s->nzm + 2, &err))
       return fail (FDTD_ERROR, "TMA descriptor set-up failed: %s", err.c_str ());
   }
+  return configure_fused (s);
+}
+
+/* ------------------------------------------------------------------ one pass per step in the core */
+
+/* the current fields back into the first allocation (after an odd number of fused steps they live in the second) */
+static int normalize_parity (fdtd_solver *s)
+{
+  if (s->parity == 0) return FDTD_OK;
+  for (int i = 0; i < 6; ++i)
+  {
+    CUDA_TRY (cudaMemcpyAsync (s->fA[i], s->fB[i], (size_t) s->field_cells * s->cell, cudaMemcpyDeviceToDevice, s->s_compute));
+    s->f[i] = s->fA[i];
+  }
+  s->parity = 0;
+  return FDTD_OK;
+}
+
+/*
+ * Decides whether the one-pass kernel can run on this configuration and sets up its box, buffers and tensor maps
+ * (3D, fast mode with a sigma-free core).  Requirements beyond a non-empty core: every x tile boundary inside the grid
+ * lies in the x core (the rim lane recomputes E' there with the plain update), the D / B part of a stage fits in
+ * shared memory, and the slab keeps one plane on either side that abuts another rank (its E' / H' travel mid-step).
+ * Not being able to is not an error: the two half-step kernels then advance the whole slab as before.
+ */
+static int configure_fused (fdtd_solver *s)
+{
+  s->fused_ok = false;
+  if (s->cfg.dims != 3 || !s->core_on || !s->use_tma || s->fused_forbidden) return FDTD_OK;
+  int rc = normalize_parity (s);
+  if (rc) return rc;
+  int txc = 0, fty = 0, smem_q = 0, smem_base = 0, sty = 0;
+  fused_tile_geometry (s->fp, s->nc, &txc, &fty, NULL, &smem_q, &smem_base);
+  tma_tile_geometry (s->fp, s->nc, true, NULL, &sty, NULL, NULL);
+  const int V = 16 / s->cell, qx = 8 * V;
+  for (int b = txc; b < s->nx; b += txc)
+    if (b < s->core_lo[0] || b + V - 1 > s->core_hi[0]) return FDTD_OK;
+  FusedBox fb;
+  fb.fy0 = s->core_lo[1];
+  fb.fy1 = s->core_hi[1];
+  if (fb.fy0 % sty || (fb.fy1 + 1) % sty || (fb.fy1 - fb.fy0 + 1) % fty || sty % fty) return FDTD_OK;
+  int zlo = s->core_lo[2] - s->kz0, zhi = s->core_hi[2] - s->kz0;
+  const int zmin = s->cfg.rank > 0 ? 1 : 0, zmax = s->cfg.rank + 1 < s->cfg.nranks ? s->nzl - 2 : s->nzl - 1;
+  if (zlo < zmin) zlo = zmin;
+  if (zhi > zmax) zhi = zmax;
+  if (zhi < zlo) return FDTD_OK;
+  fb.fz0 = zlo;
+  fb.fz1 = zhi;
+  fb.nq = 0;
+  for (int t = 0; t * txc < s->nx; ++t)
+  {
+    int n = 0;
+    for (int q = 0; q < 4; ++q)
+    {
+      const int qa = t * txc + q * qx, qb = qa + qx - 1;
+      if (qa < s->nx && !(qa >= s->core_lo[0] && qb <= s->core_hi[0])) ++n;
+    }
+    if (n > fb.nq) fb.nq = n;
+  }
+  if (smem_base + fb.nq * smem_q > 227 * 1024) return FDTD_OK;
+  /* planes marched per CTA: one redundant plane per march (E' of the plane above the last one), so longer marches than
+   * the half-step kernels'; still several rounds of CTAs per SM */
+  const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((fb.fy1 - fb.fy0 + 1) / fty);
+  int kc = s->fused_kc > 0 ? s->fused_kc : 32;
+  const int planes = fb.fz1 - fb.fz0 + 1;
+  while (kc > 8 && tiles * ((planes + kc - 1) / kc) < 8LL * 148) kc /= 2;
+  if (kc > planes) kc = planes;
+  fb.kc = kc;
+
+  if (!s->fB[0])
+  {
+    for (int i = 0; i < 6; ++i)
+    {
+      cudaError_t e = cudaMalloc (&s->fB[i], (size_t) s->field_cells * s->cell);
+      if (e == cudaSuccess) e = cudaMemsetAsync (s->fB[i], 0, (size_t) s->field_cells * s->cell, s->s_compute);
+      if (e != cudaSuccess)
+      {
+        /* no room for the second buffers: stay with the two-pass kernels */
+        cudaGetLastError ();
+        for (int k = 0; k <= i; ++k) { if (s->fB[k]) cudaFree (s->fB[k]); s->fB[k] = NULL; }
+        return FDTD_OK;
+      }
+    }
+  }
+  std::string err;
+  for (int par = 0; par < 2; ++par)
+  {
+    void **cur = par ? s->fB : s->fA, **nxt = par ? s->fA : s->fB;
+    void *d[3] = { s->f[6], s->f[7], s->f[8] }, *b[3] = { s->f[9], s->f[10], s->f[11] };
+    if (!fused_prepare_3d (&s->fmaps[par], s->fp, s->nc, cur, cur + 3, d, b, s->eps, s->pitch, s->ny, s->nzl + 2, s->pitchM,
+                           s->nzm + 2, &err))
+      return fail (FDTD_ERROR, "TMA descriptor set-up of the one-pass kernel failed: %s", err.c_str ());
+    /* half-step kernels of the shell: the E phase reads H and E of cur; the H phase reads E of nxt and H of cur */
+    void *fe[12], *fh[12];
+    for (int i = 0; i < 12; ++i) fe[i] = fh[i] = s->f[i];
+    for (int i = 0; i < 6; ++i) fe[i] = fh[i] = cur[i];
+    for (int i = 0; i < 3; ++i) fh[i] = nxt[i];
+    TmaMaps3D te, th;
+    if (!tma_prepare_3d (&te, s->fp, s->nc, true, true, fe, s->eps, s->mu, s->pitch, s->ny, s->nzl + 2, s->pitchM, s->nzm + 2, &err)
+        || !tma_prepare_3d (&th, s->fp, s->nc, true, true, fh, s->eps, s->mu, s->pitch, s->ny, s->nzl + 2, s->pitchM, s->nzm + 2, &err))
+      return fail (FDTD_ERROR, "TMA descriptor set-up failed: %s", err.c_str ());
+    memcpy (s->tma_pp[par].e, te.e, sizeof (te.e));
+    memcpy (s->tma_pp[par].h, th.h, sizeof (th.h));
+    s->tma_pp[par].valid = true;
+  }
+  s->fbox = fb;
+  s->shell_ty = sty;
+  s->fused_ok = true;
   return FDTD_OK;
 }
 
@@ -459,8 +585,7 @@ static cudaError_t phase_3d (fdtd_solver *s, bool e_phase, const StepParams<T> &
 {
   const fdtd_config &c = s->cfg;
   const bool cplx = c.complex_values != 0, pml = c.use_pml != 0, tfsf = c.use_tfsf != 0, exact = c.exact_mode == 1;
-  if (s->use_tma) return launch_phase_3d_tma<T> (e_phase, p, s->tma, cplx, pml, tfsf, exact, s->core_on, s->mu_uniform, kb, ke, S);
-  return launch_phase_3d<T> (e_phase, p, cplx, pml, tfsf, exact, kb, ke, S);
+  return launch_phase_3d_tma<T> (e_phase, p, s->tma, cplx, pml, tfsf, exact, s->core_on, s->mu_uniform, kb, ke, S);
 }
 
 template <typename T>
@@ -489,7 +614,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     /* make the low H halo valid for the first E half step */
     CUDA_TRY (cudaEventRecord (s->ev_hb, S));
     CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
-    int rc = exchange (s, true);
+    int rc = exchange (s, true, s->f);
     if (rc) return rc;
     CUDA_TRY (cudaEventRecord (s->ev_hx, C));
   }
@@ -515,7 +640,7 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
       CUDA_TRY (phase_3d<T> (s, true, p, 0, 1, S)); s->launches++;
       CUDA_TRY (cudaEventRecord (s->ev_eb, S));
       CUDA_TRY (cudaStreamWaitEvent (C, s->ev_eb, 0));
-      int rc = exchange (s, false);
+      int rc = exchange (s, false, s->f);
       if (rc) return rc;
       CUDA_TRY (cudaEventRecord (s->ev_ex, C));
       if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, true, p, 1, s->nzl, S)); s->launches++; }
@@ -539,12 +664,149 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
       CUDA_TRY (phase_3d<T> (s, false, p, s->nzl - 1, s->nzl, S)); s->launches++;
       CUDA_TRY (cudaEventRecord (s->ev_hb, S));
       CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
-      int rc = exchange (s, true);
+      int rc = exchange (s, true, s->f);
       if (rc) return rc;
       CUDA_TRY (cudaEventRecord (s->ev_hx, C));
       if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, false, p, 0, s->nzl - 1, S)); s->launches++; }
     }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
+  }
+  if (multi) CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
+  return FDTD_OK;
+}
+
+/*
+ * The sub-boxes of the slab that the one-pass kernel does not cover, as a region table for one half-step launch
+ * (StepParams::reg): the planes below and above its box, and inside its plane range the rows below and above.
+ * `part`: 0 = all of it; 1 = only the plane that has to leave for a neighbour rank first (E phase: local plane 0 when
+ * there is a rank below; H phase: the top plane when there is a rank above); 2 = all but that plane.
+ */
+template <typename T>
+static void shell_regions (const fdtd_solver *s, bool e_phase, int part, StepParams<T> &p)
+{
+  const FusedBox &fb = s->fbox;
+  const int sty = s->shell_ty;
+  const int njt_all = (s->ny + sty - 1) / sty;
+  const bool has_b = e_phase ? s->cfg.rank > 0 : s->cfg.rank + 1 < s->cfg.nranks;
+  const int bplane = e_phase ? 0 : s->nzl - 1;
+  p.nreg = 0;
+  auto add = [&] (int jt0, int njt, int kb, int ke)
+  {
+    if (njt <= 0 || ke <= kb) return;
+    typename StepParams<T>::Region &r = p.reg[p.nreg++];
+    r.jt0 = jt0; r.njt = njt; r.kb = kb; r.ke = ke; r.cta0 = 0;
+    r.kc = ke - kb < 16 ? ke - kb : 16;
+  };
+  if (part == 1)
+  {
+    if (has_b) add (0, njt_all, bplane, bplane + 1);
+    return;
+  }
+  int lo_b = 0, lo_e = fb.fz0, hi_b = fb.fz1 + 1, hi_e = s->nzl;
+  if (part == 2 && has_b)
+  {
+    if (e_phase) lo_b = 1; else hi_e = s->nzl - 1;
+  }
+  add (0, njt_all, lo_b, lo_e);
+  add (0, njt_all, hi_b, hi_e);
+  add (0, fb.fy0 / sty, fb.fz0, fb.fz1 + 1);
+  add ((fb.fy1 + 1) / sty, njt_all - (fb.fy1 + 1) / sty, fb.fz0, fb.fz1 + 1);
+}
+
+/*
+ * nsteps leapfrog steps with the one-pass kernel in the core.  Per step, on the compute stream:
+ *   incident line E and H updates and both sets of TF/SF face tables (they depend on the 1-D line only),
+ *   E half step of the shell (cur -> nxt), one-pass kernel (cur -> nxt, E and H), H half step of the shell,
+ * then the roles of the two buffer sets are swapped.  With several ranks the plane a neighbour waits for is computed
+ * first and travels on the communication stream while the rest runs, as in the two-pass schedule.
+ */
+template <typename T>
+static int enqueue_steps_fused (fdtd_solver *s, long long nsteps)
+{
+  const fdtd_config &c = s->cfg;
+  const bool cplx = c.complex_values != 0, tfsf = c.use_tfsf != 0;
+  const bool multi = c.nranks > 1;
+  cudaStream_t S = s->s_compute, C = s->s_comm;
+  const bool prof = s->profiling && !multi;
+  s->prof_steps = 0;
+  if (prof)
+  {
+    while ((long long) s->prof_ev.size () < 4 * nsteps)
+    {
+      cudaEvent_t e;
+      CUDA_TRY (cudaEventCreate (&e));
+      s->prof_ev.push_back (e);
+    }
+    s->prof_steps = nsteps;
+  }
+  if (multi)
+  {
+    CUDA_TRY (cudaEventRecord (s->ev_hb, S));
+    CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
+    int rc = exchange (s, true, s->f);
+    if (rc) return rc;
+    CUDA_TRY (cudaEventRecord (s->ev_hx, C));
+  }
+  for (long long n = 0; n < nsteps; ++n)
+  {
+    StepParams<T> p = make_params<T> (s); /* s->f are the current buffers */
+    void **nxt = s->parity ? s->fA : s->fB;
+    for (int i = 0; i < 6; ++i) p.fo[i] = (T *) nxt[i];
+    p.step = n;
+    const TmaMaps3D &shell_maps = s->tma_pp[s->parity];
+    if (tfsf)
+    {
+      CUDA_TRY (launch_incident<T> (true, p, cplx, false, S));
+      CUDA_TRY (launch_face_tables<T> (true, p, cplx, S));
+      CUDA_TRY (launch_incident<T> (false, p, cplx, false, S));
+      CUDA_TRY (launch_face_tables<T> (false, p, cplx, S));
+      s->launches += 4;
+    }
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
+
+    /* E half step of the shell */
+    StepParams<T> pe = p;
+    if (multi)
+    {
+      CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
+      shell_regions<T> (s, true, 1, pe);
+      if (pe.nreg) { CUDA_TRY (launch_phase_3d_tma<T> (true, pe, shell_maps, cplx, true, tfsf, false, true, true, 0, 0, S)); s->launches++; }
+      CUDA_TRY (cudaEventRecord (s->ev_eb, S));
+      CUDA_TRY (cudaStreamWaitEvent (C, s->ev_eb, 0));
+      int rc = exchange (s, false, nxt);
+      if (rc) return rc;
+      CUDA_TRY (cudaEventRecord (s->ev_ex, C));
+    }
+    shell_regions<T> (s, true, multi ? 2 : 0, pe);
+    if (pe.nreg) { CUDA_TRY (launch_phase_3d_tma<T> (true, pe, shell_maps, cplx, true, tfsf, false, true, true, 0, 0, S)); s->launches++; }
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
+
+    /* the core: E and H in one pass */
+    CUDA_TRY (launch_step_core_fused<T> (p, s->fmaps[s->parity], s->fbox, cplx, tfsf, S));
+    s->launches++;
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
+
+    /* H half step of the shell: reads E of nxt, H of cur */
+    StepParams<T> ph = p;
+    for (int i = 0; i < 3; ++i) ph.f[i] = (T *) nxt[i];
+    if (multi)
+    {
+      CUDA_TRY (cudaStreamWaitEvent (S, s->ev_ex, 0));
+      shell_regions<T> (s, false, 1, ph);
+      if (ph.nreg) { CUDA_TRY (launch_phase_3d_tma<T> (false, ph, shell_maps, cplx, true, tfsf, false, true, true, 0, 0, S)); s->launches++; }
+      CUDA_TRY (cudaEventRecord (s->ev_hb, S));
+      CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
+      int rc = exchange (s, true, nxt);
+      if (rc) return rc;
+      CUDA_TRY (cudaEventRecord (s->ev_hx, C));
+    }
+    shell_regions<T> (s, false, multi ? 2 : 0, ph);
+    if (ph.nreg) { CUDA_TRY (launch_phase_3d_tma<T> (false, ph, shell_maps, cplx, true, tfsf, false, true, true, 0, 0, S)); s->launches++; }
+    if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
+
+    /* nxt holds the fields of the next step */
+    for (int i = 0; i < 6; ++i) s->f[i] = nxt[i];
+    s->parity ^= 1;
   }
   if (multi) CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
   return FDTD_OK;
@@ -565,8 +827,12 @@ static int run_async (fdtd_solver *s, long long nsteps)
     s->run_ev.push_back (e);
   }
   CUDA_TRY (cudaEventRecord (s->run_ev[2 * s->runs_pending], s->s_compute));
+  /* one pass per step in the core when the geometry allows it and mu is homogeneous (kernels3d_fused.cu) */
+  s->fused_run = s->fused_ok && s->mu_uniform;
+  if (!s->fused_run && (rc = normalize_parity (s))) return rc; /* the two-pass tensor maps describe the first allocation */
   if (s->core_on && !s->folded && (rc = fold_core (s, true))) return rc;
-  rc = s->fp == 4 ? enqueue_steps<float> (s, nsteps) : enqueue_steps<double> (s, nsteps);
+  if (s->fused_run) rc = s->fp == 4 ? enqueue_steps_fused<float> (s, nsteps) : enqueue_steps_fused<double> (s, nsteps);
+  else rc = s->fp == 4 ? enqueue_steps<float> (s, nsteps) : enqueue_steps<double> (s, nsteps);
   if (rc) return rc;
   CUDA_TRY (cudaEventRecord (s->run_ev[2 * s->runs_pending + 1], s->s_compute));
   s->t += nsteps;
@@ -585,14 +851,17 @@ static int sync_run (fdtd_solver *s)
     const int last = s->runs_pending - 1;
     CUDA_TRY (cudaEventElapsedTime (&s->last_ms, s->run_ev[2 * last], s->run_ev[2 * last + 1]));
     s->runs_pending = 0;
-    s->prof_e_ms = s->prof_h_ms = 0;
+    s->prof_e_ms = s->prof_h_ms = s->prof_f_ms = 0;
     for (long long n = 0; n < s->prof_steps; ++n)
     {
-      float a = 0, b = 0;
+      /* two-pass: [0,1] E kernel, [2,3] H kernel; one-pass: [0,1] E shell, [1,2] core kernel, [2,3] H shell */
+      float a = 0, b = 0, f = 0;
       CUDA_TRY (cudaEventElapsedTime (&a, s->prof_ev[4 * n + 0], s->prof_ev[4 * n + 1]));
       CUDA_TRY (cudaEventElapsedTime (&b, s->prof_ev[4 * n + 2], s->prof_ev[4 * n + 3]));
+      if (s->fused_run) CUDA_TRY (cudaEventElapsedTime (&f, s->prof_ev[4 * n + 1], s->prof_ev[4 * n + 2]));
       s->prof_e_ms += a;
       s->prof_h_ms += b;
+      s->prof_f_ms += f;
     }
   }
   return FDTD_OK;
@@ -860,18 +1129,13 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   CREATE_TRY (cudaMalloc ((void **) &s->red_out, sizeof (double)));
 #undef CREATE_TRY
 
+  for (int i = 0; i < 6; ++i) s->fA[i] = s->f[i];
   /* kernel selection; the TF/SF face tables of the TMA kernels */
   s->use_tma = false;
   s->kchunk = 8; /* 2D: rows marched per thread (profiles/r1_kchunk_sweep.log) */
-  if (const char *kc_env = getenv ("FDTD3D_B200_KCHUNK")) /* tuning aid; 3D: see configure_3d */
-  {
-    const int v = atoi (kc_env);
-    if (v > 0) s->kchunk = v;
-  }
   if (is3)
   {
-    const char *sel = getenv ("FDTD3D_B200_KERNELS"); /* "direct": the non-TMA kernels, for A/B measurements */
-    s->use_tma = !(sel && strcmp (sel, "direct") == 0);
+    s->use_tma = true;
     if (s->use_tma && cfg->use_tfsf)
     {
       long long m = (long long) s->nx * s->ny;
@@ -889,10 +1153,8 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
     }
   }
 
-  /* fast mode with UPML on the TMA kernels skips D / B where sigma = 0; exact_mode 2 (or FDTD3D_B200_CORE=0, for
-   * A/B measurements) keeps the reference's formulation everywhere */
-  s->core_allowed = (is3 ? s->use_tma : true) && cfg->use_pml && cfg->exact_mode == 0;
-  if (const char *ce = getenv ("FDTD3D_B200_CORE")) { if (atoi (ce) == 0) s->core_allowed = false; }
+  /* fast mode with UPML skips D / B where sigma = 0; exact_mode 2 keeps the reference's formulation everywhere */
+  s->core_allowed = cfg->use_pml && cfg->exact_mode == 0;
   update_core (s);
   if ((rc = configure_3d (s, true)))
   {
@@ -921,6 +1183,7 @@ int fdtd_destroy (fdtd_handle s)
     const NcclApi *nccl = nccl_api (NULL);
     if (nccl) nccl->CommDestroy (s->comm);
   }
+  for (int f = 0; f < 6; ++f) { if (s->fA[f]) s->f[f] = s->fA[f]; if (s->fB[f]) cudaFree (s->fB[f]); }
   for (int f = 0; f < 12; ++f) if (s->f[f]) cudaFree (s->f[f]);
   void *ptrs[] = { s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->staging, s->red_partials, s->red_out };
   for (void *p : ptrs) if (p) cudaFree (p);
@@ -1156,6 +1419,39 @@ int fdtd_tfsf_face_masks (const fdtd_config *cfg, int field, uint8_t *out, int64
         out[((size_t) i * ny + j) * nz + k] = (uint8_t) m;
       }
   return FDTD_OK;
+}
+
+int fdtd_get_fused_box (fdtd_handle s, int64_t lo[3], int64_t hi[3])
+{
+  if (!s || !lo || !hi) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  const bool on = s->fused_ok && s->mu_uniform;
+  lo[0] = 0; hi[0] = on ? s->nx - 1 : -1;
+  lo[1] = on ? s->fbox.fy0 : 0; hi[1] = on ? s->fbox.fy1 : -1;
+  lo[2] = on ? s->kz0 + s->fbox.fz0 : 0; hi[2] = on ? s->kz0 + s->fbox.fz1 : -1;
+  return FDTD_OK;
+}
+
+int fdtd_fused_time (fdtd_handle s, float *ms)
+{
+  if (!s || !ms) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  int rc = sync_run (s);
+  if (rc) return rc;
+  *ms = s->prof_f_ms;
+  return FDTD_OK;
+}
+
+int fdtd_set_tuning (fdtd_handle s, int march_planes, int one_pass_march_planes, int allow_one_pass)
+{
+  if (!s) return fail (FDTD_INVALID_ARGUMENT, "NULL handle");
+  if (march_planes < 0 || one_pass_march_planes < 0) return fail (FDTD_INVALID_ARGUMENT, "negative march length");
+  CUDA_TRY (cudaSetDevice (s->cfg.device));
+  int rc = sync_run (s);
+  if (rc) return rc;
+  s->kchunk_forced = march_planes;
+  s->fused_kc = one_pass_march_planes;
+  s->fused_forbidden = allow_one_pass == 0;
+  if (s->cfg.dims == 2) { if (march_planes > 0) s->kchunk = march_planes; return FDTD_OK; }
+  return configure_3d (s, true);
 }
 
 int fdtd_get_core_box (fdtd_handle s, int64_t lo[3], int64_t hi[3])

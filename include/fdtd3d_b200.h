@@ -204,6 +204,23 @@ int fdtd_get_time_step (fdtd_handle h, int64_t *t);
  */
 int fdtd_get_core_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
 
+/*
+ * The box of cells (global indices, inclusive; lo > hi when there is none) that the time loop advances with ONE pass
+ * per time step instead of an E and an H half step (exact_mode 0, 3D, use_pml, homogeneous mu): inside it E and H are
+ * read once and written once per step (12 instead of 18 field values per cell), see DESIGN.md.  It spans the whole x
+ * range, the rows of the core box and its planes on this rank minus a plane next to another rank.  No reference
+ * counterpart: a diagnostic (bench.py reports the bytes the step has to move from it).  fdtd_fused_time: summed device
+ * time of that kernel over the last completed run, with fdtd_set_profiling on; fdtd_phase_times then returns the E and
+ * H half steps of the remaining shell.
+ */
+int fdtd_get_fused_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
+int fdtd_fused_time (fdtd_handle h, float *ms);
+
+/* Tuning aid, no reference counterpart: planes (2D: rows) marched per CTA by the half-step kernels and by the one-pass
+ * kernel (0 = the library's rule), and whether the one-pass kernel may be used at all (0 keeps the two half-step
+ * kernels everywhere, for A/B measurements).  Results do not depend on any of it. */
+int fdtd_set_tuning (fdtd_handle h, int march_planes, int one_pass_march_planes, int allow_one_pass);
+
 /* The same box for a configuration and sigma profiles (FPValue arrays of size[a] + 1 values, NULL = all zero) without
  * creating a handle; host only, no GPU needed (planning, tests).  No reference counterpart. */
 int fdtd_plan_core_box (const fdtd_config *cfg, const void *const sigma[3], int64_t lo[3], int64_t hi[3]);

@@ -453,3 +453,84 @@ def test_homogeneous_materials_tmz(vt, cplx, use_tfsf, mode):
             assert np.array_equal(out[key], ref[key]), "%s not bit-exact: rel err %g" % (key, errs[key])
         else:
             assert errs[key] <= TOL[vt], (key, errs)
+
+
+# ----------------------------------------------------------------------------- one pass per step in the core (kernels3d_fused.cu)
+
+FUSED_CASES = [
+    # size, pml, tfsf, use_tfsf, value_type, complex, steps
+    ((100, 24, 20), 3, 6, True, 8, False, 12),    # two x tiles: the rim lane recomputes E' across the tile boundary
+    ((100, 24, 20), 3, 6, False, 8, False, 14),   # point source (its Dz advanced explicitly)
+    ((150, 31, 23), 4, 7, True, 8, False, 9),     # three x tiles, ragged y and z
+    ((70, 28, 18), 3, 6, True, 8, True, 10),      # complex double: 32-cell tiles
+    ((200, 40, 22), 4, 6, False, 4, False, 12),   # float: 128-cell tiles, 8-row fused tiles inside 16-row shell tiles
+    ((200, 40, 22), 4, 6, True, 4, False, 12),
+    ((100, 36, 20), 3, 6, True, 4, True, 10),     # complex float
+    ((48, 36, 28), 5, 9, True, 8, False, 30),     # one x tile (the reference-dump size)
+]
+
+
+@pytest.mark.parametrize("case", FUSED_CASES, ids=lambda c: "%s-t%d-vt%d%s" % ("x".join(map(str, c[0])), c[3], c[4], "c" if c[5] else ""))
+def test_one_pass_core_equals_two_pass_and_oracle(case):
+    """exact_mode 0 with a homogeneous mu advances the core with ONE kernel per step (E and H fused, ping-pong buffers).
+    Same per-cell arithmetic as the two half-step kernels, so the fields are bit-identical to the two-pass run, and both
+    are within the north-star tolerance of the oracle -- also across runs of odd length (buffer parity), D/B reads
+    between runs and an upload that switches the one-pass kernel off (non-homogeneous mu)."""
+    size, pml, tfsf, use_tfsf, vt, cplx, steps = case
+    src = (size[0] // 2, size[1] // 2, size[2] // 2)
+    kw = dict(size=size, pml=pml, tfsf=tfsf, use_pml=True, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx, source_pos=src,
+              theta=60, phi=30, psi=20)
+    cfg = O.make_config(exact_mode=0, **kw)
+    inputs, fields = random_inputs(cfg, seed=77)
+    mu = 1.25
+    inputs_ref = dict(inputs, Mu=np.full_like(inputs["Mu"], mu))
+    keys = _keys(cfg)
+    ref = O.run(cfg, steps, inputs_ref, fields)
+
+    def run(one_pass, chunks):
+        with F.Solver(cfg) as s:
+            s.fill("Mu", mu)
+            for a in range(3):
+                s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+            s.upload("Eps", inputs["Eps"])
+            for name in O.field_names(cfg):
+                s.upload(name, fields[name])
+            if not one_pass:
+                s.set_tuning(allow_one_pass=False)
+            box = s.fused_box
+            mids = []
+            for n in chunks:
+                s.run(n)
+                mids.append(s.download("Ez"))
+            out = {k: s.download(k) for k in keys}
+        return box, out, mids
+
+    chunks = [1, 2, steps - 3]
+    box, out, mids = run(True, chunks)
+    assert box is not None, "the one-pass kernel is meant to be in use on this grid"
+    assert box[0][0] == 0 and box[1][0] == size[0] - 1 and box[0][1] >= pml and box[1][2] <= size[2] - pml - 1
+    box2, two, mids2 = run(False, chunks)
+    assert box2 is None
+    for k in keys:
+        assert np.array_equal(out[k], two[k]), "%s: one-pass and two-pass runs differ, max |d| = %g" % (k, np.abs(out[k] - two[k]).max())
+    for a, b in zip(mids, mids2):
+        assert np.array_equal(a, b)
+    errs = family_rel_errs(out, ref, keys)
+    assert max(errs.values()) <= TOL[vt], errs
+
+    # a non-homogeneous mu switches back to the two-pass kernels mid-way (odd parity at that moment), results unchanged
+    ref2 = O.run(cfg, steps, inputs, fields)
+    with F.Solver(cfg) as s:
+        s.fill("Mu", 1.0)
+        for a in range(3):
+            s.set_sigma(a, inputs["Sigma" + "XYZ"[a]])
+        s.upload("Eps", inputs["Eps"])
+        for name in O.field_names(cfg):
+            s.upload(name, fields[name])
+        assert s.fused_box is not None
+        s.upload("Mu", inputs["Mu"])
+        assert s.fused_box is None
+        s.run(steps)
+        got = {k: s.download(k) for k in keys}
+    errs = family_rel_errs(got, ref2, keys)
+    assert max(errs.values()) <= TOL[vt], errs
