@@ -206,27 +206,51 @@ def _peak():
         return 6650.0, "fallback 6650 GB/s (of fallback)"
 
 
-def byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=False):
+def byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=False, fbox=None):
     """SURVEY.md §8d bytes of one rank's slab per half step: algorithmic (D/B through every cell, a material value per
     cell, as the reference formulates the step) and needed (what the default mode has to move: no D/B in the sigma-free
-    core, no material array that was set with fdtd_fill)."""
+    core, no material array that was set with fdtd_fill).  With the one-pass kernel (fbox = its box) the cells inside
+    the box cost 12 field values + eps per whole step (+ 12 for D/B in the x absorber lanes); `need_f` is that, and
+    need_e / need_h are then the two half steps of the remaining shell."""
     dims, nx, ny = w["dims"], w["nx"], w["ny"]
     fp = w["vt"]
     fv = fp * (2 if w["cplx"] else 1)
     ncell = nx * ny * nzl
     if dims == 3:
-        alg_e = alg_h = ((15 if w["pml"] else 9) * fv + fp) * ncell
+        per_e = per_h = (15 if w["pml"] else 9) * fv + fp
         aux_e = aux_h = 3
     else:
-        alg_e, alg_h = ((6 if w["pml"] else 4) * fv + fp) * ncell, ((9 if w["pml"] else 5) * fv + fp) * ncell
+        per_e, per_h = (6 if w["pml"] else 4) * fv + fp, (9 if w["pml"] else 5) * fv + fp
         aux_e, aux_h = 1, 2
+    alg_e, alg_h = per_e * ncell, per_h * ncell
+
+    def inter(lo, hi, lo2, hi2):
+        return max(0, min(hi, hi2) - max(lo, lo2) + 1)
+
     core_cells = 0
     if box:
-        zlo, zhi = max(box[0][2], z0), min(box[1][2], z0 + nzl - 1)
-        core_cells = (box[1][0] - box[0][0] + 1) * (box[1][1] - box[0][1] + 1) * (max(0, zhi - zlo + 1) if dims == 3 else 1)
-    need_e = alg_e - 2 * aux_e * fv * core_cells - (fp * ncell if eps_uniform else 0)
-    need_h = alg_h - 2 * aux_h * fv * core_cells - (fp * ncell if mu_uniform else 0)
-    return {"alg_e": alg_e, "alg_h": alg_h, "need_e": need_e, "need_h": need_h, "core_cells": core_cells, "cells": ncell}
+        core_cells = (box[1][0] - box[0][0] + 1) * (box[1][1] - box[0][1] + 1) * (inter(box[0][2], box[1][2], z0, z0 + nzl - 1) if dims == 3 else 1)
+    mat_e = 0 if eps_uniform else fp
+    mat_h = 0 if mu_uniform else fp
+    out = {"alg_e": alg_e, "alg_h": alg_h, "core_cells": core_cells, "cells": ncell, "fused_cells": 0, "alg_f": 0, "need_f": 0}
+    if not fbox:
+        out["need_e"] = alg_e - 2 * aux_e * fv * core_cells - (fp - mat_e) * ncell
+        out["need_h"] = alg_h - 2 * aux_h * fv * core_cells - (fp - mat_h) * ncell
+        return out
+    # one-pass box: whole x range, rows and planes of fbox (global indices)
+    rows = fbox[1][1] - fbox[0][1] + 1
+    planes = inter(fbox[0][2], fbox[1][2], z0, z0 + nzl - 1)
+    fcells = nx * rows * planes
+    fcore = (box[1][0] - box[0][0] + 1) * rows * planes       # sigma-free cells inside the box
+    out["fused_cells"] = fcells
+    out["alg_f"] = (per_e + per_h) * fcells
+    out["need_f"] = (12 * fv + mat_e + mat_h) * fcells + 12 * fv * (fcells - fcore)
+    shell = ncell - fcells
+    shell_core = core_cells - fcore                               # sigma-free cells the half-step kernels still advance
+    out["alg_e"], out["alg_h"] = per_e * shell, per_h * shell
+    out["need_e"] = per_e * shell - 2 * aux_e * fv * shell_core - (fp - mat_e) * shell
+    out["need_h"] = per_h * shell - 2 * aux_h * fv * shell_core - (fp - mat_h) * shell
+    return out
 
 
 def make_solver(F, name, exact, rank, world, local, dist):
@@ -276,20 +300,31 @@ def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False)
     s.set_profiling(False)
     peak, peak_source = _peak()
     box = s.core_box
-    bm = byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=(w["dims"] == 2 and not w["sphere"]))
+    fbox = s.fused_box if w["dims"] == 3 else None
+    bm = byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=(w["dims"] == 2 and not w["sphere"]), fbox=fbox)
     step_s = ms / steps * 1e-3
+    alg_step = bm["alg_e"] + bm["alg_h"] + bm["alg_f"]
+    need_step = bm["need_e"] + bm["need_h"] + bm["need_f"]
     res = {"name": name, "exact_mode": exact, "n_gpus": world, "steps": steps, "warmup": warmup,
            "value": cells * steps / (ms * 1e-3) / 1e6, "ms_per_step": ms / steps, "gpu_launches": launches,
-           "whole_step_frac": (bm["alg_e"] + bm["alg_h"]) / step_s / 1e9 / peak,
-           "whole_step_frac_of_needed_bytes": (bm["need_e"] + bm["need_h"]) / step_s / 1e9 / peak,
-           "core_cell_fraction": bm["core_cells"] / float(bm["cells"]), "host_wall_s": t_wall, "clocks": clocks,
-           "peak": peak, "peak_source": peak_source, "bytes": bm}
+           "whole_step_frac": alg_step / step_s / 1e9 / peak,
+           "whole_step_frac_of_needed_bytes": need_step / step_s / 1e9 / peak,
+           "core_cell_fraction": bm["core_cells"] / float(bm["cells"]), "one_pass_cell_fraction": bm["fused_cells"] / float(bm["cells"]),
+           "host_wall_s": t_wall, "clocks": clocks, "peak": peak, "peak_source": peak_source, "bytes": bm}
     if psteps:
         kn = ("e_phase_3d", "h_phase_3d") if w["dims"] == 3 else ("ez_phase_tmz", "h_phase_tmz")
+
+        def frac(nbytes, t_ms):
+            return nbytes / (t_ms * 1e-3) / 1e9 / peak if t_ms > 0 and nbytes > 0 else None
+
         res.update({"e_phase_ms": e_ms / psteps, "h_phase_ms": h_ms / psteps, "kernels": kn,
-                    "e_frac": bm["alg_e"] / (e_ms / psteps * 1e-3) / 1e9 / peak, "h_frac": bm["alg_h"] / (h_ms / psteps * 1e-3) / 1e9 / peak,
-                    "e_frac_of_needed_bytes": bm["need_e"] / (e_ms / psteps * 1e-3) / 1e9 / peak,
-                    "h_frac_of_needed_bytes": bm["need_h"] / (h_ms / psteps * 1e-3) / 1e9 / peak})
+                    "e_frac": frac(bm["alg_e"], e_ms / psteps), "h_frac": frac(bm["alg_h"], h_ms / psteps),
+                    "e_frac_of_needed_bytes": frac(bm["need_e"], e_ms / psteps),
+                    "h_frac_of_needed_bytes": frac(bm["need_h"], h_ms / psteps)})
+        if fbox:
+            f_ms = s.fused_ms / psteps
+            res.update({"one_pass_ms": f_ms, "one_pass_frac": frac(bm["alg_f"], f_ms),
+                        "one_pass_frac_of_needed_bytes": frac(bm["need_f"], f_ms)})
     if keep:
         return res, s, cfg
     s.close()
@@ -299,8 +334,8 @@ def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False)
 def brief(res):
     """The part of a measure() result that goes into roofline.modes / other_configs."""
     keys = ("name", "exact_mode", "n_gpus", "steps", "warmup", "value", "ms_per_step", "e_phase_ms", "h_phase_ms", "e_frac", "h_frac",
-            "e_frac_of_needed_bytes", "h_frac_of_needed_bytes", "whole_step_frac", "whole_step_frac_of_needed_bytes",
-            "core_cell_fraction", "gpu_launches")
+            "e_frac_of_needed_bytes", "h_frac_of_needed_bytes", "one_pass_ms", "one_pass_frac", "one_pass_frac_of_needed_bytes",
+            "whole_step_frac", "whole_step_frac_of_needed_bytes", "core_cell_fraction", "one_pass_cell_fraction", "gpu_launches")
     out = {k: res[k] for k in keys if k in res}
     out["unit"] = METRIC
     out["workload"] = workload_config(res["n_gpus"], res["name"], res["exact_mode"])["workload"]
@@ -437,11 +472,14 @@ def main():
         name = res["kernels"][0 if e_dom else 1]
         k_ms = res["e_phase_ms"] if e_dom else res["h_phase_ms"]
         alg, need = (bm["alg_e"], bm["need_e"]) if e_dom else (bm["alg_h"], bm["need_h"])
+        if res.get("one_pass_ms"):
+            # the one-pass core kernel dominates the step: its algorithmic bytes are both half steps of its cells
+            name, k_ms, alg, need = "step_core_3d_fused", res["one_pass_ms"], bm["alg_f"], bm["need_f"]
         achieved = alg / (k_ms * 1e-3) / 1e9
         traffic = None
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
-            key = name + ("_core" if box else "")
+            key = name if name == "step_core_3d_fused" else name + ("_core" if box else "")
             # ncu captures exist for c3 (default mode and exact_mode 2) and for c2's default mode
             have = (args.workload == "c3" and args.exact != 1) or (args.workload == "c2" and args.exact == 0)
             traffic = prof.get(key, {}).get("dram_bytes_per_launch") if have else None
@@ -455,6 +493,12 @@ def main():
                     "kernel": name, "kernel_ms": k_ms, "e_phase_ms": res["e_phase_ms"], "h_phase_ms": res["h_phase_ms"],
                     "algorithmic_bytes_per_launch": alg, "peak_source": peak_source, "whole_step_frac": res["whole_step_frac"],
                     "whole_step_frac_of_needed_bytes": res["whole_step_frac_of_needed_bytes"]}
+        if res.get("one_pass_ms"):
+            roofline.update({"one_pass_cell_fraction": res["one_pass_cell_fraction"], "one_pass_ms": res["one_pass_ms"],
+                             "shell_e_phase_ms": res["e_phase_ms"], "shell_h_phase_ms": res["h_phase_ms"],
+                             "one_pass_note": "inside its box the step is ONE kernel that reads E, H, eps and writes E, H once: 12 "
+                                              "field values + eps per cell-update instead of the 30 + 2 of the reference's formulation; "
+                                              "e_phase_ms / h_phase_ms are the half-step kernels on the remaining shell"})
         if need != alg:
             roofline.update({"core_cell_fraction": res["core_cell_fraction"], "needed_bytes_per_launch": need,
                              "frac_of_needed_bytes": need / (k_ms * 1e-3) / 1e9 / peak,
@@ -463,7 +507,7 @@ def main():
                                      "set with fdtd_fill is not loaded, so frac > 1 is bytes not moved, not bandwidth above the peak "
                                      "-- frac_of_needed_bytes is the kernel against its own traffic"})
     else:
-        whole = (bm["alg_e"] + bm["alg_h"]) / (res["ms_per_step"] * 1e-3) / 1e9
+        whole = (bm["alg_e"] + bm["alg_h"] + bm["alg_f"]) / (res["ms_per_step"] * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": whole, "peak": peak, "unit": "GB/s", "frac": whole / peak, "traffic": None,
                     "peak_source": peak_source, "whole_step_frac_of_needed_bytes": res["whole_step_frac_of_needed_bytes"],
                     "kernel": "whole step per GPU (multi-rank run: boundary + interior launches overlap with the exchange)"}
