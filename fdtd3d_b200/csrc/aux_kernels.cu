@@ -330,6 +330,23 @@ sumsq_final (const double *partials, int n, double *out)
   if (threadIdx.x == 0) *out = red[0];
 }
 
+/* does a pitched array hold one value everywhere?  out[0] = 1 if some value differs from the first one (else left at
+ * the 0 the caller put there), out[1] = the first value */
+template <typename T>
+__global__ void __launch_bounds__ (SUMSQ_THREADS)
+uniform_check (const T *base, int nscal, long long nrows, long long pitch_scal, double *out)
+{
+  const T v0 = base[0];
+  bool differs = false;
+  for (long long r = blockIdx.x; r < nrows; r += gridDim.x)
+  {
+    const T *rowp = base + r * pitch_scal;
+    for (int s = threadIdx.x; s < nscal; s += SUMSQ_THREADS) differs |= rowp[s] != v0;
+  }
+  if (__syncthreads_or (differs) && threadIdx.x == 0) out[0] = 1.0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) out[1] = (double) v0;
+}
+
 template <typename CellT>
 cudaError_t reorder_t (bool to_device, void *dev, void *staged, int ia, int ib, int ny, int nzb, int pitch, long long ps,
                        int kofs, int kmin, int kmax, cudaStream_t stream)
@@ -473,6 +490,17 @@ cudaError_t launch_sumsq (const T *base, int nscal, long long nrows, long long p
   sumsq_final<<<1, SUMSQ_THREADS, 0, stream>>> (partials, SUMSQ_CTAS, out);
   return cudaGetLastError ();
 }
+template <typename T>
+cudaError_t launch_uniform_check (const T *base, int nscal, long long nrows, long long pitch_scal, double *out2, cudaStream_t stream)
+{
+  cudaError_t e = cudaMemsetAsync (out2, 0, 2 * sizeof (double), stream);
+  if (e != cudaSuccess) return e;
+  uniform_check<T><<<SUMSQ_CTAS, SUMSQ_THREADS, 0, stream>>> (base, nscal, nrows, pitch_scal, out2);
+  return cudaGetLastError ();
+}
+template cudaError_t launch_uniform_check<float> (const float *, int, long long, long long, double *, cudaStream_t);
+template cudaError_t launch_uniform_check<double> (const double *, int, long long, long long, double *, cudaStream_t);
+
 template cudaError_t launch_sumsq<float> (const float *, int, long long, long long, double *, double *, cudaStream_t);
 template cudaError_t launch_sumsq<double> (const double *, int, long long, long long, double *, double *, cudaStream_t);
 

@@ -110,6 +110,10 @@ template <typename T>
 cudaError_t launch_sumsq (const T *base, int nscal, long long nrows, long long pitch_scal, double *partials,
                           double *out, cudaStream_t stream);
 
+/* out2[0] = 1 if the rows of a pitched array do not all hold the value base[0], else 0; out2[1] = base[0] (device doubles) */
+template <typename T>
+cudaError_t launch_uniform_check (const T *base, int nscal, long long nrows, long long pitch_scal, double *out2, cudaStream_t stream);
+
 } /* namespace fdtd */
 
 #endif /* FDTD_LAUNCH_H */

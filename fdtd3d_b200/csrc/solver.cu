@@ -993,6 +993,22 @@ static int transfer (fdtd_solver *s, int field, void *host, int order, long long
   }
   else
     return fail (FDTD_INVALID_ARGUMENT, "unknown order %d", order);
+  if (to_device && (field == FDTD_MU || field == FDTD_EPS))
+  {
+    /* An uploaded material may still be homogeneous (the reference's own mu is 1 everywhere, and in TMz so is eps):
+     * one scan of the owned planes decides whether the kernels may take the value from the parameter block. */
+    const char *base = (const char *) fi.dev + (size_t) fi.ps * fi.cell;
+    const long long nrows = (long long) fi.ny * fi.nzl_planes;
+    if (s->fp == 4) CUDA_TRY (launch_uniform_check<float> ((const float *) base, fi.nx, nrows, fi.pitch, s->red_partials, S));
+    else CUDA_TRY (launch_uniform_check<double> ((const double *) base, fi.nx, nrows, fi.pitch, s->red_partials, S));
+    s->launches++;
+    double res[2] = { 1.0, 0.0 };
+    CUDA_TRY (cudaMemcpyAsync (res, s->red_partials, sizeof (res), cudaMemcpyDeviceToHost, S));
+    CUDA_TRY (cudaStreamSynchronize (S));
+    const bool uni = res[0] == 0.0;
+    if (field == FDTD_MU) { s->mu_uniform = uni; s->mu_value = res[1]; }
+    else { s->eps_uniform = uni; s->eps_value = res[1]; }
+  }
   return FDTD_OK;
 }
 

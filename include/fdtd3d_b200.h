@@ -147,8 +147,10 @@ int fdtd_upload (fdtd_handle h, int field, const void *host, int order, int64_t 
 int fdtd_download (fdtd_handle h, int field, void *host, int order, int64_t z0, int64_t nz);
 
 /* Sets every cell of a field to (re, im).  For FDTD_MU (and, with dims == 2, FDTD_EPS) this also tells the library that
- * the material is homogeneous: until the array is uploaded again the kernels take the value from here instead of
- * reading the array (same results, less memory traffic).  fdtd_create fills eps and mu with 1. */
+ * the material is homogeneous: the kernels then take the value from here instead of reading the array (same results,
+ * less memory traffic), and with a homogeneous mu the 3D fast mode may advance the core with one pass per step
+ * (fdtd_get_fused_box).  fdtd_upload of a material scans what it uploaded, so an uploaded array that holds one value
+ * everywhere (the reference's own mu = 1) is recognised as well.  fdtd_create fills eps and mu with 1. */
 int fdtd_fill (fdtd_handle h, int field, double re, double im);
 
 /* eps := Approximation::approximateSphere (Source/Layout/Approximation.cpp:303-331) evaluated on
