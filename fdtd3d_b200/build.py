@@ -89,7 +89,7 @@ def _build_cli(lib):
         return
     os.makedirs(os.path.dirname(exe), exist_ok=True)
     cmd = ["/usr/bin/g++", "-std=c++14", "-O2", "-ffp-contract=off", "-Wall"] + srcs + \
-          ["-L" + HERE, "-lfdtd3d_b200", "-Wl,-rpath,$ORIGIN/..", "-o", exe]
+          ["-L" + HERE, "-lfdtd3d_b200", "-Wl,-rpath,$ORIGIN/..", "-pthread", "-o", exe]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("building the fdtd3d binary failed:\n" + r.stdout)

@@ -10,6 +10,7 @@
 #define FDTD3D_B200_HOST_SCHEME_H
 
 #include <string>
+#include <vector>
 
 #include "../../include/fdtd3d_b200.h"
 
@@ -35,17 +36,22 @@ class DeviceScheme : public Scheme
 {
 protected:
   YeeGridLayout *yeeLayout;
-  fdtd_config cfg;
-  fdtd_handle handle;
+  fdtd_config cfg;                    /* cfg.rank / nranks / device describe rank 0; rank r runs on device cfg.device + r */
+  std::vector<fdtd_handle> handles;   /* one per GPU: --num-cuda-gpus z-slabs (Source/main.cpp:88-96, Settings.inc:81) */
   long long totalStep;
   double lastRunMs;
+
+  /* runs fn (rank) for every rank on a thread of its own and waits: NCCL set-up and the time loop need all ranks of
+   * the process inside the library at the same time; returns false if any rank failed (message printed) */
+  bool forEachRank (const char *what, int (*fn) (DeviceScheme *, int));
 
   void fail (const char *what) const; /* prints the library's error and exits with EXIT_ERROR */
 
 public:
   DeviceScheme (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
-                int exactMode, int device);
+                int exactMode, int device, int numGpus = 1);
   ~DeviceScheme ();
+  int numRanks () const { return cfg.nranks; }
 
   /* Scheme3D::initScheme (dx, sourceFreq) / SchemeTMz::initScheme: dt, frequency, relative phase velocity */
   void initScheme (double dx, double wavelength);
@@ -73,7 +79,7 @@ class Scheme3D : public DeviceScheme
 {
 public:
   Scheme3D (YeeGridLayout *layout, long long tStep, bool doUsePML, bool doUseTFSF, int valueType, bool complexValues,
-            int exactMode, int device);
+            int exactMode, int device, int numGpus = 1);
 };
 
 class SchemeTMz : public DeviceScheme

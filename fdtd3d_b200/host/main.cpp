@@ -54,8 +54,14 @@ int main (int argc, char **argv)
   const int vt = s.valueType == "f" ? 4 : 8;
   const int exact = (s.exactMode && !s.fastMode) ? 1 : (s.keepAux ? 2 : 0); /* fdtd_config.exact_mode */
   DeviceScheme *scheme;
+  if (s.numCudaGPUs < 1 || (dims == 2 && s.numCudaGPUs != 1))
+  {
+    printf ("ERROR: --num-cuda-gpus must be at least 1, and 1 for --2d (the z-slab decomposition is 3D).\n");
+    return EXIT_ERROR;
+  }
   if (dims == 2) scheme = new SchemeTMz (&yeeLayout, s.numTimeSteps, s.doUsePML, s.doUseTFSF, vt, s.complexValues, exact, (int) s.cudaDevice);
-  else scheme = new Scheme3D (&yeeLayout, s.numTimeSteps, s.doUsePML, s.doUseTFSF, vt, s.complexValues, exact, (int) s.cudaDevice);
+  else scheme = new Scheme3D (&yeeLayout, s.numTimeSteps, s.doUsePML, s.doUseTFSF, vt, s.complexValues, exact, (int) s.cudaDevice,
+                              (int) s.numCudaGPUs);
 
   scheme->initScheme (s.gridStep, s.sourceWaveLength);
   if (!s.loadDatDir.empty ()) scheme->loadDat (s.loadDatDir, s.startStep);
@@ -86,6 +92,7 @@ int main (int argc, char **argv)
   printf ("Number of time steps: 2\n");
   printf ("\n-------- Details --------\n");
   printf ("Parallel grid: %d\n", 0);
+  printf ("GPUs: %d (z-slabs, NCCL halo exchange)\n", scheme->numRanks ());
   const double cells = (double) s.sizeX * s.sizeY * (dims == 3 ? s.sizeZ : 1);
   printf ("Device time: %f ms, %.1f Mcell-updates/s (%s arithmetic)\n", scheme->deviceMilliseconds (),
           scheme->deviceMilliseconds () > 0 ? cells * s.numTimeSteps / (scheme->deviceMilliseconds () * 1e-3) / 1e6 : 0.0,

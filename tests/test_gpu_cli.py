@@ -100,3 +100,31 @@ def test_cli_checkpoint_and_resume(dims, tmp_path):
     for f in names:
         x, y = np.fromfile(str(a / f), dtype=np.uint8), np.fromfile(str(c / f), dtype=np.uint8)
         assert x.size > 0 and np.array_equal(x, y), f
+
+
+@pytest.mark.parametrize("ngpus", [2, 4])
+@pytest.mark.parametrize("flags", [["--exact"], []])
+def test_cli_num_cuda_gpus_is_byte_identical_to_one_gpu(ngpus, flags, tmp_path):
+    """--num-cuda-gpus N (Source/Settings/Settings.inc:81, Source/main.cpp:88-96): N z-slabs in one process, NCCL halo
+    planes, slabs gathered into the reference's whole-grid DAT files -- byte for byte the single-GPU run, in exact mode
+    and in the default fast mode (one-pass core kernel included: the grid is wide enough for it)."""
+    import torch
+    if torch.cuda.device_count() < ngpus:
+        pytest.skip("needs %d GPUs" % ngpus)
+    base = ["--3d", "--sizex", "100", "--sizey", "28", "--sizez", "46", "--pml-sizex", "4", "--same-size-pml", "--tfsf-sizex", "8",
+            "--same-size-tfsf", "--time-steps", "21", "--angle-teta", "60", "--angle-phi", "30", "--angle-psi", "20",
+            "--use-pml", "--use-tfsf"] + flags
+    dumps = {}
+    for n in (1, ngpus):
+        d = tmp_path / ("g%d" % n)
+        d.mkdir()
+        r = subprocess.run([EXE] + base + ["--num-cuda-gpus", str(n), "--dump-dat", str(d)], stdout=subprocess.PIPE,
+                           stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout
+        assert "GPUs: %d" % n in r.stdout
+        dumps[n] = {f: open(str(d / f), "rb").read() for f in sorted(os.listdir(str(d)))}
+    assert sorted(dumps[1]) == sorted(dumps[ngpus]) and len(dumps[1]) == 14
+    for f in dumps[1]:
+        assert dumps[1][f] == dumps[ngpus][f], f
+    ez = np.frombuffer(dumps[1]["current[21]_rank-0_Ez.dat"], dtype=np.float64)
+    assert np.abs(ez).max() > 1e-3
