@@ -14,8 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libfdtd3d_b200.so")
-SOURCES = ["kernels3d_tma.cu", "kernels3d_fused.cu", "kernels2d.cu", "aux_kernels.cu", "solver.cu", "scheme_init.cpp", "noalloc.cu"]
-HEADERS = ["fdtd_device.cuh", "kernels3d_common.cuh", "launch.h", "nccl_dl.h", "tma_util.cuh", os.path.join("..", "..", "include", "fdtd3d_b200.h")]
+SOURCES = ["kernels3d_tma.cu", "kernels3d_fused.cu", "kernels2d.cu", "kernels2d_fused.cu", "aux_kernels.cu", "solver.cu", "scheme_init.cpp", "noalloc.cu"]
+HEADERS = ["fdtd_device.cuh", "kernels3d_common.cuh", "launch.h", "nccl_dl.h", "tma_util.cuh", "kernels2d_common.cuh", os.path.join("..", "..", "include", "fdtd3d_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",

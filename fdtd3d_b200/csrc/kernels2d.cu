@@ -20,6 +20,7 @@
  * folds / unfolds the D/B arrays of exactly those cells (p.core_lo/hi, x aligned to whole vectors).
  */
 #include "fdtd_device.cuh"
+#include "kernels2d_common.cuh"
 #include "launch.h"
 
 namespace fdtd
@@ -28,50 +29,27 @@ namespace fdtd
 namespace
 {
 
+using namespace k2d;
+
 constexpr int TX = 128;
 
-#define IN_RANGE(x, lo, hi) ((x) >= (lo) && (x) <= (hi))
-
-/* inline interpolation of SchemeTMz.cpp:232-248 (H: `- 0.5`) and :645-663 (E: no offset term) */
-template <typename T, int NC>
-__device__ __noinline__ void incident_tmz (const StepParams<T> &p, bool isH, int gi, int gj, T offx, T offy, T *out)
+/* rows [j0, j1) this CTA marches over: a chunk of the whole grid, or of one of the row ranges of p.reg (kb, ke = rows;
+ * cta0 = first blockIdx.y of the range) when the launch covers only the rows around the one-pass kernel's box */
+template <typename T>
+__device__ __forceinline__ bool tmz_rows (const StepParams<T> &p, int &j0, int &j1)
 {
-  T x = ((T) gi + offx) - p.zero_inc[0];
-  T y = ((T) gj + offy) - p.zero_inc[1];
-  double dd = (double) x * p.cphi + (double) y * p.sphi;
-  if (isH) dd = dd - 0.5;
-  T d = (T) dd;
-  unsigned long long n = (unsigned long long) d;
-  T c1 = (T) n;
-  T prop2 = d - c1;
-  T prop1 = (T) 1 - prop2;
-  const T *F = isH ? p.hinc : p.einc;
-#pragma unroll
-  for (int c = 0; c < NC; ++c) out[c] = prop1 * F[n * NC + c] + prop2 * F[(n + 1) * NC + c];
-}
-
-/* v -= s * w  with w a double (cos / sin of the incident angle): `prevHy1 -= -diffX * cos (...)`,
- * SchemeTMz.cpp:275-288 */
-template <typename T, int NC, bool EXACT>
-__device__ __forceinline__ T sub_scaled (T v, T s, double w)
-{
-  if (EXACT && sizeof (T) == 4 && NC == 1) return (T) ((double) v - (double) s * w);
-  if (sizeof (T) == 8) return (T) ((double) v - (double) s * w);
-  return v - s * (T) w;
-}
-
-template <typename T, bool EXACT>
-__device__ __forceinline__ void sweep3_coefs (T pn, T mn, T q, T mod, T &cb, T &cc)
-{
-  if (EXACT) { cb = (pn / mod) / q; cc = pn == mn ? cb : (mn / mod) / q; }
-  else { T r = q * rcp_t<T> (mod); cb = pn * r; cc = mn * r; }
-}
-
-template <typename T, bool EXACT>
-__device__ __forceinline__ T plain_coef (T m, const StepParams<T> &p)
-{
-  if (EXACT) return p.dt / (m * p.dx);
-  return p.dt_dx * rcp_t<T> (m);
+  if (p.nreg == 0)
+  {
+    j0 = blockIdx.y * p.kchunk;
+    j1 = min (j0 + p.kchunk, p.ny);
+    return j0 < j1;
+  }
+  int r = 0;
+  for (int q = 1; q < p.nreg; ++q)
+    if ((int) blockIdx.y >= p.reg[q].cta0) r = q;
+  j0 = p.reg[r].kb + ((int) blockIdx.y - p.reg[r].cta0) * p.kchunk;
+  j1 = min (j0 + p.kchunk, p.reg[r].ke);
+  return j0 < j1;
 }
 
 /* ------------------------------------------------------------------ Ez half step */
@@ -90,15 +68,15 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
 
   const int i0 = (blockIdx.x * TX + threadIdx.x) * V;
   if (i0 >= p.nx) return;
-  const int j0 = blockIdx.y * p.kchunk;
-  const int j1 = min (j0 + p.kchunk, p.ny);
-  if (j0 >= j1) return;
+  int j0, j1;
+  if (!tmz_rows (p, j0, j1)) return;
 
   const long long row = (long long) p.pitch * NC;
   long long o = (p.ps + (long long) j0 * p.pitch + i0) * NC; /* plane 1 */
   long long om = p.psM + (long long) j0 * p.pitchM + i0;
 
-  T *Ez = p.f[2], *Dz = p.f[8];
+  const T *Ez = p.f[2];
+  T *EzOut = p.fo[2], *Dz = p.f[8];
   const T *Hx = p.f[3], *Hy = p.f[4];
 
   MVec ca_x_at, cbd_x_at;
@@ -250,31 +228,13 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
       }
     }
 
-    stv<T, W> (Ez + o, ez);
+    stv<T, W> (EzOut + o, ez);
     if (PML && shell) stv<T, W> (Dz + o, dz);
     hx_jm = hx;
   }
 }
 
 /* ------------------------------------------------------------------ H half step */
-
-/* B update of a TMz H component.  `neg` selects the Hx form (0.0 - 0.0 - Ez1 + Ez2) or the Hy form
- * (Ez1 - Ez2 - 0.0 + 0.0) of Kernels.h:38-42; the double zeros promote the curl of a real float build. */
-template <typename T, int NC, bool EXACT>
-__device__ __forceinline__ T tmz_first (bool plain, bool hx_form, T old, T ez1, T ez2, T ca, T cb)
-{
-  if (EXACT && sizeof (T) == 4 && NC == 1)
-  {
-    /* Hx: ((0.0 - 0.0) - Ez1) + Ez2 is double throughout; Hy: Ez1 - Ez2 is a float subtraction (rounded to float)
-     * before the double zeros promote it */
-    const double curl = hx_form ? (0.0 - 0.0 - (double) ez1 + (double) ez2) : ((double) (ez1 - ez2) - 0.0 + 0.0);
-    const double lhs = plain ? 1.0 * (double) old : (double) (ca * old);
-    return (T) (lhs + (double) cb * curl);
-  }
-  const T curl = hx_form ? ((T) 0 - (T) 0 - ez1 + ez2) : (ez1 - ez2 - (T) 0 + (T) 0);
-  if (EXACT) return (plain ? old : ca * old) + cb * curl;
-  return fma_t<T> (cb, curl, plain ? old : ca * old);
-}
 
 template <typename T, int NC, bool PML, bool TFSF, bool EXACT, bool CORE, bool UNI>
 __global__ void __launch_bounds__ (TX)
@@ -288,16 +248,16 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
 
   const int i0 = (blockIdx.x * TX + threadIdx.x) * V;
   if (i0 >= p.nx) return;
-  const int j0 = blockIdx.y * p.kchunk;
-  const int j1 = min (j0 + p.kchunk, p.ny);
-  if (j0 >= j1) return;
+  int j0, j1;
+  if (!tmz_rows (p, j0, j1)) return;
 
   const long long row = (long long) p.pitch * NC;
   long long o = (p.ps + (long long) j0 * p.pitch + i0) * NC;
   long long om = p.psM + (long long) j0 * p.pitchM + i0;
 
   const T *Ez = p.f[2];
-  T *Hx = p.f[3], *Hy = p.f[4], *Bx = p.f[9], *By = p.f[10];
+  const T *Hx = p.f[3], *Hy = p.f[4];
+  T *HxOut = p.fo[3], *HyOut = p.fo[4], *Bx = p.f[9], *By = p.f[10];
 
   MVec p_x_at, m_x_at, ca_x_btw, q_x_btw;
   T ca_z = 0, cbd_z = 0, q_z = 0;
@@ -434,7 +394,7 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
       }
     }
 
-    stv<T, W> (Hx + o, hx); stv<T, W> (Hy + o, hy);
+    stv<T, W> (HxOut + o, hx); stv<T, W> (HyOut + o, hy);
     if (PML && shell) { stv<T, W> (Bx + o, bx); stv<T, W> (By + o, by); }
     ez = ez_jp;
     mu_c = mu_jp;
@@ -447,15 +407,27 @@ cudaError_t launch_t (bool e_phase, bool uni, const StepParams<T> &p, cudaStream
   constexpr int V = 16 / (NC * (int) sizeof (T));
   dim3 block (TX);
   dim3 grid ((p.nx + TX * V - 1) / (TX * V), (p.ny + p.kchunk - 1) / p.kchunk);
+  StepParams<T> pr = p;
+  if (p.nreg > 0)
+  {
+    int total = 0;
+    for (int r = 0; r < p.nreg; ++r)
+    {
+      pr.reg[r].cta0 = total;
+      if (p.reg[r].ke > p.reg[r].kb) total += (p.reg[r].ke - p.reg[r].kb + p.kchunk - 1) / p.kchunk;
+    }
+    if (total == 0) return cudaSuccess;
+    grid.y = total;
+  }
   if (e_phase)
   {
-    if (uni) ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (p);
-    else ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (p);
+    if (uni) ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (pr);
+    else ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (pr);
   }
   else
   {
-    if (uni) h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (p);
-    else h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (p);
+    if (uni) h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (pr);
+    else h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (pr);
   }
   return cudaGetLastError ();
 }

@@ -56,6 +56,14 @@ template <typename T>
 cudaError_t launch_step_core_fused (const StepParams<T> &p, const FusedMaps3D &maps, const FusedBox &fb, bool cplx, bool tfsf,
                                     cudaStream_t stream);
 
+/* The TMz counterpart (kernels2d_fused.cu): rows [fy0, fy1] of the 2D grid, kc tiles marched per CTA; fz0 / fz1 unused. */
+void fused_tile_geometry_tmz (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *smem_per_quarter, int *smem_base);
+bool fused_prepare_tmz (FusedMaps3D *out, int value_type, int nc, void *ez, void *hx, void *hy, void *dz, void *bx, void *by,
+                        void *eps, int pitch, int ny, int pitchM, std::string *err);
+template <typename T>
+cudaError_t launch_step_core_tmz_fused (const StepParams<T> &p, const FusedMaps3D &maps, const FusedBox &fb, bool cplx, bool tfsf,
+                                        bool uniform_eps, cudaStream_t stream);
+
 /* D (B) -= / += eps eps0 E (mu mu0 H) over the core box, for the six components (aux_kernels.cu): `fold` before
  * running the CORE variants, unfold before anything else reads or replaces D / B / E / H / eps / mu */
 template <typename T>

@@ -379,7 +379,8 @@ static bool compute_core_box (int dims, int fp, int nc, const std::vector<double
   for (int a = 0; a < 3; ++a) { lo_out[a] = 0; hi_out[a] = -1; }
   int txc = 0, ty = 0, qx = 0;
   if (dims == 3) tma_tile_geometry (fp, nc, true, &txc, &ty, &qx, NULL); /* the CORE variants' tiles */
-  else { qx = 16 / (fp * nc); ty = 1; } /* TMz kernels decide per 16-byte vector and per row (kernels2d.cu) */
+  else { qx = 8 * (16 / (fp * nc)); ty = 1; } /* TMz: per row; in x per quarter of a tile row (8 vectors), the unit in
+                                                  which the one-pass kernel stages Dz / Bx / By (kernels2d_fused.cu) */
   int lo3[3], hi3[3];
   for (int a = 0; a < 3; ++a)
   {
@@ -423,7 +424,7 @@ static int normalize_parity (fdtd_solver *s);
 
 static int configure_3d (fdtd_solver *s, bool first)
 {
-  if (s->cfg.dims != 3) return FDTD_OK;
+  if (s->cfg.dims != 3) return configure_fused (s); /* TMz: direct-load half-step kernels, no tensor maps of their own */
   const bool alt = s->cfg.exact_mode == 1 || s->core_on;
   int rc0 = normalize_parity (s); /* the maps below describe the first allocation */
   if (rc0) return rc0;
@@ -460,6 +461,7 @@ static int normalize_parity (fdtd_solver *s)
   if (s->parity == 0) return FDTD_OK;
   for (int i = 0; i < 6; ++i)
   {
+    if (!s->fA[i]) continue; /* TMz has Ez, Hx, Hy only */
     CUDA_TRY (cudaMemcpyAsync (s->fA[i], s->fB[i], (size_t) s->field_cells * s->cell, cudaMemcpyDeviceToDevice, s->s_compute));
     s->f[i] = s->fA[i];
   }
@@ -477,26 +479,41 @@ static int normalize_parity (fdtd_solver *s)
 static int configure_fused (fdtd_solver *s)
 {
   s->fused_ok = false;
-  if (s->cfg.dims != 3 || !s->core_on || !s->use_tma || s->fused_forbidden) return FDTD_OK;
+  const bool tmz = s->cfg.dims == 2;
+  if (!s->core_on || (!tmz && !s->use_tma) || s->fused_forbidden) return FDTD_OK;
   int rc = normalize_parity (s);
   if (rc) return rc;
-  int txc = 0, fty = 0, smem_q = 0, smem_base = 0, sty = 0;
-  fused_tile_geometry (s->fp, s->nc, &txc, &fty, NULL, &smem_q, &smem_base);
-  tma_tile_geometry (s->fp, s->nc, true, NULL, &sty, NULL, NULL);
+  int txc = 0, fty = 0, smem_q = 0, smem_base = 0, sty = 1;
+  if (tmz) fused_tile_geometry_tmz (s->fp, s->nc, &txc, &fty, &smem_q, &smem_base);
+  else
+  {
+    fused_tile_geometry (s->fp, s->nc, &txc, &fty, NULL, &smem_q, &smem_base);
+    tma_tile_geometry (s->fp, s->nc, true, NULL, &sty, NULL, NULL);
+  }
   const int V = 16 / s->cell, qx = 8 * V;
   for (int b = txc; b < s->nx; b += txc)
     if (b < s->core_lo[0] || b + V - 1 > s->core_hi[0]) return FDTD_OK;
   FusedBox fb;
   fb.fy0 = s->core_lo[1];
   fb.fy1 = s->core_hi[1];
-  if (fb.fy0 % sty || (fb.fy1 + 1) % sty || (fb.fy1 - fb.fy0 + 1) % fty || sty % fty) return FDTD_OK;
-  int zlo = s->core_lo[2] - s->kz0, zhi = s->core_hi[2] - s->kz0;
-  const int zmin = s->cfg.rank > 0 ? 1 : 0, zmax = s->cfg.rank + 1 < s->cfg.nranks ? s->nzl - 2 : s->nzl - 1;
-  if (zlo < zmin) zlo = zmin;
-  if (zhi > zmax) zhi = zmax;
-  if (zhi < zlo) return FDTD_OK;
-  fb.fz0 = zlo;
-  fb.fz1 = zhi;
+  if (tmz)
+  {
+    /* the half-step kernels of the shell work row by row: any whole number of tile rows will do */
+    fb.fy1 = fb.fy0 + (fb.fy1 - fb.fy0 + 1) / fty * fty - 1;
+    if (fb.fy1 < fb.fy0) return FDTD_OK;
+    fb.fz0 = fb.fz1 = 0;
+  }
+  else
+  {
+    if (fb.fy0 % sty || (fb.fy1 + 1) % sty || (fb.fy1 - fb.fy0 + 1) % fty || sty % fty) return FDTD_OK;
+    int zlo = s->core_lo[2] - s->kz0, zhi = s->core_hi[2] - s->kz0;
+    const int zmin = s->cfg.rank > 0 ? 1 : 0, zmax = s->cfg.rank + 1 < s->cfg.nranks ? s->nzl - 2 : s->nzl - 1;
+    if (zlo < zmin) zlo = zmin;
+    if (zhi > zmax) zhi = zmax;
+    if (zhi < zlo) return FDTD_OK;
+    fb.fz0 = zlo;
+    fb.fz1 = zhi;
+  }
   fb.nq = 0;
   for (int t = 0; t * txc < s->nx; ++t)
   {
@@ -512,16 +529,27 @@ static int configure_fused (fdtd_solver *s)
   /* planes marched per CTA: one redundant plane per march (E' of the plane above the last one), so longer marches than
    * the half-step kernels'; still several rounds of CTAs per SM */
   const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((fb.fy1 - fb.fy0 + 1) / fty);
-  int kc = s->fused_kc > 0 ? s->fused_kc : 32;
-  const int planes = fb.fz1 - fb.fz0 + 1;
-  while (kc > 8 && tiles * ((planes + kc - 1) / kc) < 8LL * 148) kc /= 2;
-  if (kc > planes) kc = planes;
-  fb.kc = kc;
+  if (tmz)
+  {
+    /* tiles marched per CTA (one below the other) */
+    int kc = s->fused_kc > 0 ? s->fused_kc : 4;
+    while (kc > 1 && tiles / kc < 8LL * 148) kc /= 2;
+    fb.kc = kc;
+  }
+  else
+  {
+    int kc = s->fused_kc > 0 ? s->fused_kc : 32;
+    const int planes = fb.fz1 - fb.fz0 + 1;
+    while (kc > 8 && tiles * ((planes + kc - 1) / kc) < 8LL * 148) kc /= 2;
+    if (kc > planes) kc = planes;
+    fb.kc = kc;
+  }
 
-  if (!s->fB[0])
+  if (!s->fB[2])
   {
     for (int i = 0; i < 6; ++i)
     {
+      if (!s->fA[i]) continue;
       cudaError_t e = cudaMalloc (&s->fB[i], (size_t) s->field_cells * s->cell);
       if (e == cudaSuccess) e = cudaMemsetAsync (s->fB[i], 0, (size_t) s->field_cells * s->cell, s->s_compute);
       if (e != cudaSuccess)
@@ -534,7 +562,14 @@ static int configure_fused (fdtd_solver *s)
     }
   }
   std::string err;
-  for (int par = 0; par < 2; ++par)
+  for (int par = 0; par < 2 && tmz; ++par)
+  {
+    void **cur = par ? s->fB : s->fA;
+    if (!fused_prepare_tmz (&s->fmaps[par], s->fp, s->nc, cur[2], cur[3], cur[4], s->f[8], s->f[9], s->f[10], s->eps, s->pitch,
+                            s->ny, s->pitchM, &err))
+      return fail (FDTD_ERROR, "TMA descriptor set-up of the one-pass TMz kernel failed: %s", err.c_str ());
+  }
+  for (int par = 0; par < 2 && !tmz; ++par)
   {
     void **cur = par ? s->fB : s->fA, **nxt = par ? s->fA : s->fB;
     void *d[3] = { s->f[6], s->f[7], s->f[8] }, *b[3] = { s->f[9], s->f[10], s->f[11] };
@@ -753,6 +788,30 @@ static int enqueue_steps_fused (fdtd_solver *s, long long nsteps)
     void **nxt = s->parity ? s->fA : s->fB;
     for (int i = 0; i < 6; ++i) p.fo[i] = (T *) nxt[i];
     p.step = n;
+    if (c.dims == 2)
+    {
+      /* TMz: Ez half step of the rows outside the box, one-pass kernel, H half step of those rows.  The TF/SF
+       * correction samples the incident line in the kernels: the E updates need HInc of the previous step and the H
+       * updates EInc of this one, so the line's E update runs before and its H update after them. */
+      if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, false, S)); s->launches++; }
+      if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
+      StepParams<T> pe = p;
+      pe.nreg = 2;
+      pe.reg[0].kb = 0; pe.reg[0].ke = s->fbox.fy0;
+      pe.reg[1].kb = s->fbox.fy1 + 1; pe.reg[1].ke = s->ny;
+      CUDA_TRY (launch_phase_tmz<T> (true, pe, cplx, true, tfsf, false, true, s->eps_uniform, S)); s->launches++;
+      if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
+      CUDA_TRY (launch_step_core_tmz_fused<T> (p, s->fmaps[s->parity], s->fbox, cplx, tfsf, s->eps_uniform, S)); s->launches++;
+      if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
+      StepParams<T> ph = pe;
+      ph.f[2] = (T *) nxt[2];
+      CUDA_TRY (launch_phase_tmz<T> (false, ph, cplx, true, tfsf, false, true, true, S)); s->launches++;
+      if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
+      if (tfsf) { CUDA_TRY (launch_incident<T> (false, p, cplx, false, S)); s->launches++; }
+      for (int i = 0; i < 6; ++i) if (nxt[i]) s->f[i] = nxt[i];
+      s->parity ^= 1;
+      continue;
+    }
     const TmaMaps3D &shell_maps = s->tma_pp[s->parity];
     if (tfsf)
     {
@@ -1466,7 +1525,7 @@ int fdtd_set_tuning (fdtd_handle s, int march_planes, int one_pass_march_planes,
   s->kchunk_forced = march_planes;
   s->fused_kc = one_pass_march_planes;
   s->fused_forbidden = allow_one_pass == 0;
-  if (s->cfg.dims == 2) { if (march_planes > 0) s->kchunk = march_planes; return FDTD_OK; }
+  if (s->cfg.dims == 2) s->kchunk = march_planes > 0 ? march_planes : 8;
   return configure_3d (s, true);
 }
 

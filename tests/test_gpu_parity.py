@@ -534,3 +534,65 @@ def test_one_pass_core_equals_two_pass_and_oracle(case):
         got = {k: s.download(k) for k in keys}
     errs = family_rel_errs(got, ref2, keys)
     assert max(errs.values()) <= TOL[vt], errs
+
+
+FUSED_TMZ_CASES = [
+    # size, pml, tfsf, use_tfsf, value_type, complex, steps, uniform eps
+    ((600, 60), 5, 8, False, 8, False, 21, True),     # point source, eps and mu homogeneous (the reference's TMz set-up)
+    ((600, 60), 5, 8, True, 8, False, 20, False),     # TF/SF, varying eps
+    ((1100, 50), 6, 9, False, 4, False, 25, True),    # float: 128-cell tiles
+    ((1100, 50), 6, 9, True, 4, False, 20, False),
+    ((150, 44), 5, 8, True, 8, True, 16, False),      # complex double: 32-cell tiles
+    ((96, 80), 8, 14, False, 8, False, 60, True),     # the reference-dump size
+]
+
+
+@pytest.mark.parametrize("case", FUSED_TMZ_CASES, ids=lambda c: "%s-t%d-vt%d%s%s" % ("x".join(map(str, c[0])), c[3], c[4], "c" if c[5] else "", "-uni" if c[7] else ""))
+def test_one_pass_core_tmz_equals_two_pass_and_oracle(case):
+    """2D TMz: the one-pass kernel (kernels2d_fused.cu) against the two half-step kernels (bit-identical: same per-cell
+    arithmetic) and the oracle, over runs of odd and even length."""
+    size, pml, tfsf, use_tfsf, vt, cplx, steps, uni_eps = case
+    src = (min(70, size[0] // 2), size[1] // 2, 0)
+    kw = dict(dims=2, size=size, pml=pml, tfsf=tfsf, use_pml=True, use_tfsf=use_tfsf, value_type=vt, complex_values=cplx, source_pos=src)
+    cfg = O.make_config(exact_mode=0, **kw)
+    inputs, fields = random_inputs(cfg, seed=78)
+    mu, eps = 1.25, 2.0
+    inputs["Mu"] = np.full_like(inputs["Mu"], mu)
+    if uni_eps:
+        inputs["Eps"] = np.full_like(inputs["Eps"], eps)
+    keys = _keys(cfg)
+    ref = O.run(cfg, steps, inputs, fields)
+
+    def run(one_pass, chunks):
+        with F.Solver(cfg) as s:
+            s.fill("Mu", mu)
+            for a in range(2):
+                s.set_sigma(a, inputs["Sigma" + "XY"[a]])
+            if uni_eps:
+                s.fill("Eps", eps)
+            else:
+                s.upload("Eps", inputs["Eps"])
+            for name in O.field_names(cfg):
+                s.upload(name, fields[name])
+            if not one_pass:
+                s.set_tuning(allow_one_pass=False)
+            box = s.fused_box
+            mids = []
+            for n in chunks:
+                s.run(n)
+                mids.append(s.download("Hy"))
+            out = {k: s.download(k) for k in keys}
+        return box, out, mids
+
+    chunks = [1, 2, steps - 3]
+    box, out, mids = run(True, chunks)
+    assert box is not None, "the one-pass TMz kernel is meant to be in use on this grid"
+    assert box[0][0] == 0 and box[1][0] == size[0] - 1 and box[0][1] >= pml and box[1][1] <= size[1] - pml - 1
+    box2, two, mids2 = run(False, chunks)
+    assert box2 is None
+    for k in keys:
+        assert np.array_equal(out[k], two[k]), "%s: one-pass and two-pass runs differ, max |d| = %g" % (k, np.abs(out[k] - two[k]).max())
+    for a, b in zip(mids, mids2):
+        assert np.array_equal(a, b)
+    errs = family_rel_errs(out, ref, keys)
+    assert max(errs.values()) <= TOL[vt], errs
