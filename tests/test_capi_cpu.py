@@ -163,8 +163,8 @@ def test_core_box_planning_is_host_logic():
     assert box(_cfg(size=(512, 512, 512), pml=10, exact_mode=0, complex_values=True)) == ((16, 12, 10), (495, 499, 501))
     # real float: 32-cell quarters, 16-row tiles
     assert box(_cfg(size=(1024, 1024, 512), pml=10, exact_mode=0, value_type=4)) == ((32, 16, 10), (991, 1007, 501))
-    # 2D TMz float: per 4-cell vector and per row; z is the single plane
-    assert box(_cfg(dims=2, size=(4096, 4096), pml=10, exact_mode=0, value_type=4)) == ((12, 10, 0), (4083, 4085, 0))
+    # 2D TMz float: per row, and in x per quarter of a tile row (8 vectors = 32 cells); z is the single plane
+    assert box(_cfg(dims=2, size=(4096, 4096), pml=10, exact_mode=0, value_type=4)) == ((32, 10, 0), (4063, 4085, 0))
     # exact mode and the D/B-everywhere mode never skip anything; nor does a run without UPML
     assert box(_cfg(size=(64, 64, 64), pml=6, tfsf=9, exact_mode=1)) is None
     assert box(_cfg(size=(64, 64, 64), pml=6, tfsf=9, exact_mode=2)) is None
