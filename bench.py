@@ -239,12 +239,13 @@ def byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=False, fbox=None):
         return out
     # one-pass box: whole x range, rows and planes of fbox (global indices)
     rows = fbox[1][1] - fbox[0][1] + 1
-    planes = inter(fbox[0][2], fbox[1][2], z0, z0 + nzl - 1)
+    planes = inter(fbox[0][2], fbox[1][2], z0, z0 + nzl - 1) if dims == 3 else 1
     fcells = nx * rows * planes
     fcore = (box[1][0] - box[0][0] + 1) * rows * planes       # sigma-free cells inside the box
     out["fused_cells"] = fcells
     out["alg_f"] = (per_e + per_h) * fcells
-    out["need_f"] = (12 * fv + mat_e + mat_h) * fcells + 12 * fv * (fcells - fcore)
+    nf = 12 if dims == 3 else 6    # E and H components read once + written once; as many again for D / B in the x absorber
+    out["need_f"] = (nf * fv + mat_e + mat_h) * fcells + nf * fv * (fcells - fcore)
     shell = ncell - fcells
     shell_core = core_cells - fcore                               # sigma-free cells the half-step kernels still advance
     out["alg_e"], out["alg_h"] = per_e * shell, per_h * shell
@@ -273,12 +274,17 @@ def make_solver(F, name, exact, rank, world, local, dist):
     return s, cfg, nz_total
 
 
+TUNING = None  # (march, one_pass_march, allow_one_pass) from the command line, applied to every solver bench.py creates
+
+
 def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False):
     """Device-timed throughput of one configuration on the ranks of this job: W untimed steps, then K steps between
     barriers, CUDA events on the solver's stream, max over ranks.  Returns the numbers of the bench line for it."""
     rank, world, local, dist, barrier, max_over_ranks = env
     w = WORKLOADS[name]
     s, cfg, nz_total = make_solver(F, name, exact, rank, world, local, dist)
+    if TUNING:
+        s.set_tuning(*TUNING)
     z0, nzl = F.slab_range(nz_total, rank, world)
     cells = w["nx"] * w["ny"] * nz_total
     s.run(warmup)
@@ -300,7 +306,7 @@ def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False)
     s.set_profiling(False)
     peak, peak_source = _peak()
     box = s.core_box
-    fbox = s.fused_box if w["dims"] == 3 else None
+    fbox = s.fused_box
     bm = byte_model(w, nzl, box, z0, mu_uniform=True, eps_uniform=(w["dims"] == 2 and not w["sphere"]), fbox=fbox)
     step_s = ms / steps * 1e-3
     alg_step = bm["alg_e"] + bm["alg_h"] + bm["alg_f"]
@@ -403,6 +409,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the small sharded parity run against the CPU oracle")
     ap.add_argument("--quick", action="store_true", help="headline line only: no roofline.modes, other_configs, sustained")
+    ap.add_argument("--march", type=int, default=0, help="tuning: planes (2D: rows) marched per CTA by the half-step kernels (0 = library rule)")
+    ap.add_argument("--one-pass-march", type=int, default=0, help="tuning: planes (2D: tiles) marched per CTA by the one-pass kernel")
+    ap.add_argument("--no-one-pass", action="store_true", help="keep the two half-step kernels everywhere (A/B measurement)")
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json config (default c3, the headline)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -443,7 +452,10 @@ def main():
     if dims == 2 and world > 1:
         raise SystemExit("the 2D TMz workload runs on one GPU")
     env = (rank, world, local, dist, barrier, max_over_ranks)
-    headline = args.workload == "c3" and args.exact == 0 and not args.quick
+    global TUNING
+    if args.march or args.one_pass_march or args.no_one_pass:
+        TUNING = (args.march, args.one_pass_march, not args.no_one_pass)
+    headline = args.workload == "c3" and args.exact == 0 and not args.quick and not (args.march or args.one_pass_march or args.no_one_pass)
 
     # ---- parity of the sharded path against the CPU oracle, before anything is timed
     parity = None
@@ -474,12 +486,13 @@ def main():
         alg, need = (bm["alg_e"], bm["need_e"]) if e_dom else (bm["alg_h"], bm["need_h"])
         if res.get("one_pass_ms"):
             # the one-pass core kernel dominates the step: its algorithmic bytes are both half steps of its cells
-            name, k_ms, alg, need = "step_core_3d_fused", res["one_pass_ms"], bm["alg_f"], bm["need_f"]
+            name = "step_core_3d_fused" if dims == 3 else "step_core_tmz_fused"
+            k_ms, alg, need = res["one_pass_ms"], bm["alg_f"], bm["need_f"]
         achieved = alg / (k_ms * 1e-3) / 1e9
         traffic = None
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
-            key = name if name == "step_core_3d_fused" else name + ("_core" if box else "")
+            key = name if name.startswith("step_core") else name + ("_core" if box else "")
             # ncu captures exist for c3 (default mode and exact_mode 2) and for c2's default mode
             have = (args.workload == "c3" and args.exact != 1) or (args.workload == "c2" and args.exact == 0)
             traffic = prof.get(key, {}).get("dram_bytes_per_launch") if have else None
@@ -496,8 +509,8 @@ def main():
         if res.get("one_pass_ms"):
             roofline.update({"one_pass_cell_fraction": res["one_pass_cell_fraction"], "one_pass_ms": res["one_pass_ms"],
                              "shell_e_phase_ms": res["e_phase_ms"], "shell_h_phase_ms": res["h_phase_ms"],
-                             "one_pass_note": "inside its box the step is ONE kernel that reads E, H, eps and writes E, H once: 12 "
-                                              "field values + eps per cell-update instead of the 30 + 2 of the reference's formulation; "
+                             "one_pass_note": "inside its box the step is ONE kernel that reads E, H, eps and writes E, H once: 12 (TMz: 6) "
+                                              "field values + eps per cell-update instead of the 30 + 2 (15 + 2) of the reference's formulation; "
                                               "e_phase_ms / h_phase_ms are the half-step kernels on the remaining shell"})
         if need != alg:
             roofline.update({"core_cell_fraction": res["core_cell_fraction"], "needed_bytes_per_launch": need,
