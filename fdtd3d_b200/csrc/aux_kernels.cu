@@ -347,6 +347,29 @@ uniform_check (const T *base, int nscal, long long nrows, long long pitch_scal, 
   if (blockIdx.x == 0 && threadIdx.x == 0) out[1] = (double) v0;
 }
 
+/* D of the absorber quarters inside the one-pass box <-> compact ping-pong array (launch.h, FusedBox): one thread per
+ * 16-byte vector; a quarter row is 128 bytes = 8 vectors */
+__global__ void dq_copy_kernel (int4 *main_d, int4 *dq, bool to_dq, FusedBox fb, int ny, long long pitch_v, long long ps_v)
+{
+  const int rows = fb.fy1 - fb.fy0 + 1;
+  const long long per_plane = (long long) rows * fb.nqt * 8;
+  const long long total = per_plane * (fb.fz1 - fb.fz0 + 1);
+  for (long long t = (long long) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long) gridDim.x * blockDim.x)
+  {
+    const int k = fb.fz0 + (int) (t / per_plane);
+    long long r = t % per_plane;
+    const int j = fb.fy0 + (int) (r / (fb.nqt * 8));
+    const int c = (int) (r % (fb.nqt * 8));
+    const int cq = c >> 3, lane = c & 7;
+    const int gq = cq < fb.nlo ? cq : cq - fb.nlo + fb.hq0;
+    const long long om = ((long long) (k + 1) * ny + j) * pitch_v + (long long) gq * 8 + lane;
+    const long long oq = ((long long) (k + 1) * ny + j) * (fb.nqt * 8LL) + c;
+    if (to_dq) dq[oq] = main_d[om];
+    else main_d[om] = dq[oq];
+  }
+  (void) ps_v;
+}
+
 template <typename CellT>
 cudaError_t reorder_t (bool to_device, void *dev, void *staged, int ia, int ib, int ny, int nzb, int pitch, long long ps,
                        int kofs, int kmin, int kmax, cudaStream_t stream)
@@ -449,6 +472,20 @@ cudaError_t launch_reorder (bool to_device, void *dev, void *staged, int cellByt
     case 16: return reorder_t<int4> (to_device, dev, staged, ia, ib, ny, nzb, pitch, ps, kofs, kmin, kmax, stream);
     default: return cudaErrorInvalidValue;
   }
+}
+
+cudaError_t launch_dq_copy (void *const main_d[3], void *const dq[3], int ncomp, bool to_dq, const FusedBox &fb, int cell_bytes,
+                            int ny, int pitch, long long ps, cudaStream_t stream)
+{
+  if (fb.nqt <= 0) return cudaSuccess;
+  for (int a = 0; a < ncomp; ++a)
+  {
+    dq_copy_kernel<<<592, 256, 0, stream>>> ((int4 *) main_d[a], (int4 *) dq[a], to_dq, fb, ny, (long long) pitch * cell_bytes / 16,
+                                             ps * cell_bytes / 16);
+    cudaError_t e = cudaGetLastError ();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 cudaError_t launch_fill (void *dev, long long count, int cellBytes, const void *pattern16, cudaStream_t stream)

@@ -114,6 +114,13 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
   const int myq = lx >> 3;
   const bool shell = lx < 32 && ((qmask >> myq) & 1);
   const int qrank = __popc (qmask & ((1 << myq) - 1));
+  /* compact quarter index in the Dz ping-pong arrays (launch.h, FusedBox): a rim thread needs the OLD Dz of a cell
+   * the tile below it may already have updated, so Dz of the absorber quarters is a read-cur / write-nxt pair too */
+  auto compact_q = [&] (int q) -> int
+  {
+    const int gq = i0t / L::QX + q;
+    return gq < fb.nlo ? gq : fb.nlo + gq - fb.hq0;
+  };
 
   auto issue = [&] (int slot, int t)
   {
@@ -132,7 +139,7 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
       for (int q = 0; q < 4; ++q)
         if ((qmask >> q) & 1)
         {
-          tma_load_3d (base + L::OFF_Q + r * L::SZ_QD, &maps.m[4], bar, (i0t + q * L::QX) * NC, j0t, 1);
+          tma_load_3d (base + L::OFF_Q + r * L::SZ_QD, &maps.m[4], bar, compact_q (q) * L::QX * NC, j0t, 1);
           tma_load_3d (base + L::OFF_Q + fb.nq * L::SZ_QD + r * L::SZ_QB, &maps.m[5], bar, (i0t + q * L::QX) * NC, j0t, 1);
           tma_load_3d (base + L::OFF_Q + fb.nq * (L::SZ_QD + L::SZ_QB) + r * L::SZ_QB, &maps.m[6], bar, (i0t + q * L::QX) * NC, j0t, 1);
           ++r;
@@ -296,7 +303,11 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
       if (own)
       {
         stv<T, W> (p.fo[2] + o, ez);
-        if (shell) stv<T, W> (p.f[8] + o, dz);
+        if (shell)
+        {
+          const long long od = ((((long long) p.ny + j) * fb.dq_pitch) + compact_q (myq) * L::QX + (lx & 7) * V) * NC; /* plane 1 */
+          stv<T, W> ((T *) fb.dq_out[0] + od, dz);
+        }
       }
     }
     else if (ingrid) ez = ldv_rw<T, W> (p.fo[2] + o);
@@ -397,8 +408,8 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
 /* ------------------------------------------------------------------ host side */
 
 template <typename T, int NC>
-bool prepare_fused2_t (FusedMaps3D *out, void *ez, void *hx, void *hy, void *dz, void *bx, void *by, void *eps, int pitch, int ny,
-                       int pitchM, std::string *err)
+bool prepare_fused2_t (FusedMaps3D *out, void *ez, void *hx, void *hy, void *dz, long long dq_pitch, void *bx, void *by, void *eps,
+                       int pitch, int ny, int pitchM, std::string *err)
 {
   typedef FTile2<T, NC> L;
   static_assert (sizeof (Fused2DSet) <= sizeof (out->set), "FusedMaps3D too small");
@@ -411,7 +422,7 @@ bool prepare_fused2_t (FusedMaps3D *out, void *ez, void *hx, void *hy, void *dz,
   ok = ok && encode (&m->m[1], hx, sb, xs, ny, 3, (L::TXC + L::V) * NC, L::TY + 2, err);
   ok = ok && encode (&m->m[2], ez, sb, xs, ny, 3, (L::TXC + L::V) * NC, L::TY + 1, err);
   ok = ok && encode (&m->m[3], eps, sb, pitchM, ny + 1, 3, L::MW, L::TY + 1, err);
-  ok = ok && encode (&m->m[4], dz, sb, xs, ny, 3, L::QX * NC, L::TY + 1, err);
+  ok = ok && encode (&m->m[4], dz, sb, dq_pitch * NC, ny, 3, L::QX * NC, L::TY + 1, err); /* compact Dz pair member */
   ok = ok && encode (&m->m[5], bx, sb, xs, ny, 3, L::QX * NC, L::TY, err);
   ok = ok && encode (&m->m[6], by, sb, xs, ny, 3, L::QX * NC, L::TY, err);
   out->valid = ok;
@@ -461,15 +472,15 @@ void fused_tile_geometry_tmz (int value_type, int nc, int *tile_cells_x, int *ti
 #undef GEOM
 }
 
-bool fused_prepare_tmz (FusedMaps3D *out, int value_type, int nc, void *ez, void *hx, void *hy, void *dz, void *bx, void *by,
-                        void *eps, int pitch, int ny, int pitchM, std::string *err)
+bool fused_prepare_tmz (FusedMaps3D *out, int value_type, int nc, void *ez, void *hx, void *hy, void *dz, long long dq_pitch,
+                        void *bx, void *by, void *eps, int pitch, int ny, int pitchM, std::string *err)
 {
   out->valid = false;
   if (value_type == 4)
-    return nc == 2 ? prepare_fused2_t<float, 2> (out, ez, hx, hy, dz, bx, by, eps, pitch, ny, pitchM, err)
-                   : prepare_fused2_t<float, 1> (out, ez, hx, hy, dz, bx, by, eps, pitch, ny, pitchM, err);
-  return nc == 2 ? prepare_fused2_t<double, 2> (out, ez, hx, hy, dz, bx, by, eps, pitch, ny, pitchM, err)
-                 : prepare_fused2_t<double, 1> (out, ez, hx, hy, dz, bx, by, eps, pitch, ny, pitchM, err);
+    return nc == 2 ? prepare_fused2_t<float, 2> (out, ez, hx, hy, dz, dq_pitch, bx, by, eps, pitch, ny, pitchM, err)
+                   : prepare_fused2_t<float, 1> (out, ez, hx, hy, dz, dq_pitch, bx, by, eps, pitch, ny, pitchM, err);
+  return nc == 2 ? prepare_fused2_t<double, 2> (out, ez, hx, hy, dz, dq_pitch, bx, by, eps, pitch, ny, pitchM, err)
+                 : prepare_fused2_t<double, 1> (out, ez, hx, hy, dz, dq_pitch, bx, by, eps, pitch, ny, pitchM, err);
 }
 
 template <typename T>

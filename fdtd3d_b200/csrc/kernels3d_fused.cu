@@ -23,7 +23,8 @@
  *     already written it) instead of being recomputed.
  *
  * The box spans the whole x range: the few lanes of the first and last x tile that lie in the x absorber take the
- * UPML path with their D / B values (quarter-row boxes, as in the CORE half-step kernels); everything else is
+ * UPML path with their D / B values (quarter-row boxes, as in the CORE half-step kernels; their D values form a third
+ * ping-pong pair in compact arrays, because a rim thread needs the neighbour cell's old D); everything else is
  * E' = E + (dt/dx)/(eps eps0) curl H, H' = H + (dt/dx)/(mu mu0) curl E'.  mu must be homogeneous (set with fdtd_fill):
  * the reference never initialises it to anything but 1; otherwise the solver keeps the two-pass kernels.
  *
@@ -58,7 +59,7 @@ using namespace tma;
 #define FDTD_FUSED_MINB 0
 #endif
 
-/* maps: 0 Hz (A) 1 Hy (B) 2 Hx (C) 3..5 Ex Ey Ez 6 eps 7..9 Dx Dy Dz quarter rows 10..12 Bx By Bz quarter rows */
+/* maps: 0 Hz (A) 1 Hy (B) 2 Hx (C) 3..5 Ex Ey Ez 6 eps 7..9 Dx Dy Dz quarter rows (compact pair member being read) 10..12 Bx By Bz quarter rows */
 struct FusedSet
 {
   CUtensorMap m[13];
@@ -144,6 +145,12 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   const int myq = lx >> 3;
   const bool shell = lx < 32 && ((qmask >> myq) & 1);
   const int qrank = __popc (qmask & ((1 << myq) - 1));
+  /* compact quarter index of a quarter of this tile in the D ping-pong arrays (launch.h, FusedBox) */
+  auto compact_q = [&] (int q) -> int
+  {
+    const int gq = i0t / L::QX + q;
+    return gq < fb.nlo ? gq : fb.nlo + gq - fb.hq0;
+  };
 
   auto issue = [&] (int slot, int k)
   {
@@ -166,7 +173,7 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
 #pragma unroll
           for (int a = 0; a < 3; ++a)
           {
-            tma_load_3d (base + L::OFF_Q + (a * fb.nq + r) * L::SZ_QD, &maps.m[7 + a], bar, (i0t + q * L::QX) * NC, j0t, k + 1);
+            tma_load_3d (base + L::OFF_Q + (a * fb.nq + r) * L::SZ_QD, &maps.m[7 + a], bar, compact_q (q) * L::QX * NC, j0t, k + 1);
             /* B of plane k - 1: H'(k-1) is computed in iteration k */
             tma_load_3d (base + L::OFF_Q + 3 * fb.nq * L::SZ_QD + (a * fb.nq + r) * L::SZ_QB, &maps.m[10 + a], bar,
                          (i0t + q * L::QX) * NC, j0t, k);
@@ -360,7 +367,9 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
         stv<T, W> (p.fo[0] + o, ex); stv<T, W> (p.fo[1] + o, ey); stv<T, W> (p.fo[2] + o, ez);
         if (shell)
         {
-          stv<T, W> (p.f[6] + o, dx); stv<T, W> (p.f[7] + o, dy); stv<T, W> (p.f[8] + o, dz);
+          /* the other member of the D pair (compact layout) */
+          const long long od = ((((long long) (k + 1) * p.ny + j) * fb.dq_pitch) + compact_q (myq) * L::QX + (lx & 7) * V) * NC;
+          stv<T, W> ((T *) fb.dq_out[0] + od, dx); stv<T, W> ((T *) fb.dq_out[1] + od, dy); stv<T, W> ((T *) fb.dq_out[2] + od, dz);
         }
       }
     }
@@ -492,8 +501,8 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
 /* ------------------------------------------------------------------ host side */
 
 template <typename T, int NC>
-bool prepare_fused_t (FusedMaps3D *out, void *const e[3], void *const h[3], void *const d[3], void *const b[3], void *eps,
-                      int pitch, int ny, int planes, int pitchM, int planesM, std::string *err)
+bool prepare_fused_t (FusedMaps3D *out, void *const e[3], void *const h[3], void *const d[3], long long dq_pitch, void *const b[3],
+                      void *eps, int pitch, int ny, int planes, int pitchM, int planesM, std::string *err)
 {
   typedef FTile<T, NC> L;
   static_assert (sizeof (FusedSet) <= sizeof (out->set), "FusedMaps3D too small");
@@ -506,7 +515,8 @@ bool prepare_fused_t (FusedMaps3D *out, void *const e[3], void *const h[3], void
   ok = ok && encode (&m->m[2], h[0], sb, xs, ny, planes, (L::TXC + L::V) * NC, L::TY + 2, err);
   for (int a = 0; a < 3 && ok; ++a) ok = encode (&m->m[3 + a], e[a], sb, xs, ny, planes, (L::TXC + L::V) * NC, L::TY + 1, err);
   ok = ok && encode (&m->m[6], eps, sb, pitchM, ny + 1, planesM, L::MW, L::TY + 2, err);
-  for (int a = 0; a < 3 && ok; ++a) ok = encode (&m->m[7 + a], d[a], sb, xs, ny, planes, L::QX * NC, L::TY + 1, err);
+  /* d[] are the compact arrays: x extent dq_pitch cells */
+  for (int a = 0; a < 3 && ok; ++a) ok = encode (&m->m[7 + a], d[a], sb, dq_pitch * NC, ny, planes, L::QX * NC, L::TY + 1, err);
   for (int a = 0; a < 3 && ok; ++a) ok = encode (&m->m[10 + a], b[a], sb, xs, ny, planes, L::QX * NC, L::TY, err);
   out->valid = ok;
   return ok;
@@ -551,14 +561,15 @@ void fused_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_r
 }
 
 bool fused_prepare_3d (FusedMaps3D *out, int value_type, int nc, void *const e[3], void *const h[3], void *const d[3],
-                       void *const b[3], void *eps, int pitch, int ny, int planes, int pitchM, int planesM, std::string *err)
+                       long long dq_pitch, void *const b[3], void *eps, int pitch, int ny, int planes, int pitchM, int planesM,
+                       std::string *err)
 {
   out->valid = false;
   if (value_type == 4)
-    return nc == 2 ? prepare_fused_t<float, 2> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err)
-                   : prepare_fused_t<float, 1> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err);
-  return nc == 2 ? prepare_fused_t<double, 2> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err)
-                 : prepare_fused_t<double, 1> (out, e, h, d, b, eps, pitch, ny, planes, pitchM, planesM, err);
+    return nc == 2 ? prepare_fused_t<float, 2> (out, e, h, d, dq_pitch, b, eps, pitch, ny, planes, pitchM, planesM, err)
+                   : prepare_fused_t<float, 1> (out, e, h, d, dq_pitch, b, eps, pitch, ny, planes, pitchM, planesM, err);
+  return nc == 2 ? prepare_fused_t<double, 2> (out, e, h, d, dq_pitch, b, eps, pitch, ny, planes, pitchM, planesM, err)
+                 : prepare_fused_t<double, 1> (out, e, h, d, dq_pitch, b, eps, pitch, ny, planes, pitchM, planesM, err);
 }
 
 template <typename T>

@@ -42,7 +42,19 @@ cudaError_t launch_phase_3d_tma (bool e_phase, const StepParams<T> &p, const Tma
 struct FusedBox
 {
   int fy0, fy1, fz0, fz1, kc, nq;
+  /* D of the absorber quarters.  A rim thread recomputes E' of a neighbour tile's cell from that cell's OLD D, which
+   * the neighbour CTA may already have overwritten in place -- so, like E and H, the D values of the absorber quarters
+   * inside the box live in a ping-pong pair while the kernel is in use: compact arrays that hold only those quarters
+   * (x extent nqt quarter rows; quarter gq of the grid is compact quarter gq if gq < nlo, else nlo + gq - hq0), same
+   * row / plane indexing as the field arrays.  The kernel reads the pair member its tensor maps describe and writes
+   * dq_out; the solver gathers / scatters them from / to the D arrays when the kernel comes into / goes out of use. */
+  int nlo, hq0, nqt;
+  long long dq_pitch;   /* cells per row of a compact array = nqt * cells per quarter */
+  void *dq_out[3];
 };
+/* copies the D values of the absorber quarters of the box between the field arrays and a compact array (to_dq = gather) */
+cudaError_t launch_dq_copy (void *const main_d[3], void *const dq[3], int ncomp, bool to_dq, const FusedBox &fb, int cell_bytes,
+                            int ny, int pitch, long long ps, cudaStream_t stream);
 struct FusedMaps3D
 {
   alignas (64) unsigned char set[13 * 128];
@@ -50,16 +62,18 @@ struct FusedMaps3D
 };
 void fused_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *ctas_per_sm, int *smem_per_quarter,
                           int *smem_base);
+/* e, h: the E / H buffers being read; d: the compact D arrays being read (x extent dq_pitch cells); b: the B arrays */
 bool fused_prepare_3d (FusedMaps3D *out, int value_type, int nc, void *const e[3], void *const h[3], void *const d[3],
-                       void *const b[3], void *eps, int pitch, int ny, int planes, int pitchM, int planesM, std::string *err);
+                       long long dq_pitch, void *const b[3], void *eps, int pitch, int ny, int planes, int pitchM, int planesM,
+                       std::string *err);
 template <typename T>
 cudaError_t launch_step_core_fused (const StepParams<T> &p, const FusedMaps3D &maps, const FusedBox &fb, bool cplx, bool tfsf,
                                     cudaStream_t stream);
 
 /* The TMz counterpart (kernels2d_fused.cu): rows [fy0, fy1] of the 2D grid, kc tiles marched per CTA; fz0 / fz1 unused. */
 void fused_tile_geometry_tmz (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *smem_per_quarter, int *smem_base);
-bool fused_prepare_tmz (FusedMaps3D *out, int value_type, int nc, void *ez, void *hx, void *hy, void *dz, void *bx, void *by,
-                        void *eps, int pitch, int ny, int pitchM, std::string *err);
+bool fused_prepare_tmz (FusedMaps3D *out, int value_type, int nc, void *ez, void *hx, void *hy, void *dz, long long dq_pitch,
+                        void *bx, void *by, void *eps, int pitch, int ny, int pitchM, std::string *err);
 template <typename T>
 cudaError_t launch_step_core_tmz_fused (const StepParams<T> &p, const FusedMaps3D &maps, const FusedBox &fb, bool cplx, bool tfsf,
                                         bool uniform_eps, cudaStream_t stream);

@@ -111,7 +111,14 @@ struct fdtd_solver
   bool fused_run;       /* the run being queued uses it (fused_ok and mu homogeneous) */
   FusedBox fbox;
   int shell_ty;         /* rows per tile of the half-step kernels that advance the shell */
-  FusedMaps3D fmaps[2]; /* per parity: reads the current buffers */
+  FusedMaps3D fmaps[2][2]; /* [E/H parity][D parity]: reads the current buffers */
+  /* D of the absorber quarters inside the box: compact ping-pong pair (launch.h, FusedBox); dq_live: the member dq_par
+   * holds the authoritative values (gathered from the D arrays at the start of a one-pass run, scattered back before
+   * anything else reads or writes D) */
+  void *dq[2][3];
+  size_t dq_bytes;
+  int dq_par;
+  bool dq_live;
   TmaMaps3D tma_pp[2];  /* per parity, half-step kernels of the shell: E phase reads cur, H phase reads E of nxt */
   int fused_kc;         /* planes marched per CTA of the fused kernel; 0 = default rule */
   int kchunk_forced;    /* fdtd_set_tuning: planes marched per CTA of the half-step kernels; 0 = default rule */
@@ -421,6 +428,7 @@ static void update_core (fdtd_solver *s)
  */
 static int configure_fused (fdtd_solver *s);
 static int normalize_parity (fdtd_solver *s);
+static int release_dq (fdtd_solver *s);
 
 static int configure_3d (fdtd_solver *s, bool first)
 {
@@ -478,11 +486,12 @@ static int normalize_parity (fdtd_solver *s)
  */
 static int configure_fused (fdtd_solver *s)
 {
+  int rc = release_dq (s); /* with the box that gathered them */
+  if (rc) return rc;
   s->fused_ok = false;
   const bool tmz = s->cfg.dims == 2;
   if (!s->core_on || (!tmz && !s->use_tma) || s->fused_forbidden) return FDTD_OK;
-  int rc = normalize_parity (s);
-  if (rc) return rc;
+  if ((rc = normalize_parity (s))) return rc;
   int txc = 0, fty = 0, smem_q = 0, smem_base = 0, sty = 1;
   if (tmz) fused_tile_geometry_tmz (s->fp, s->nc, &txc, &fty, &smem_q, &smem_base);
   else
@@ -526,6 +535,12 @@ static int configure_fused (fdtd_solver *s)
     if (n > fb.nq) fb.nq = n;
   }
   if (smem_base + fb.nq * smem_q > 227 * 1024) return FDTD_OK;
+  /* compact D pair of the absorber quarters: quarters below the x core, then those above it */
+  fb.nlo = s->core_lo[0] / qx;
+  fb.hq0 = (s->core_hi[0] + 1) / qx;
+  fb.nqt = fb.nlo + ((s->nx + qx - 1) / qx - fb.hq0);
+  fb.dq_pitch = (long long) (fb.nqt > 0 ? fb.nqt : 1) * qx;
+  for (int a = 0; a < 3; ++a) fb.dq_out[a] = NULL;
   /* planes marched per CTA: one redundant plane per march (E' of the plane above the last one), so longer marches than
    * the half-step kernels'; still several rounds of CTAs per SM */
   const long long tiles = (long long) ((s->nx + txc - 1) / txc) * ((fb.fy1 - fb.fy0 + 1) / fty);
@@ -561,21 +576,39 @@ static int configure_fused (fdtd_solver *s)
       }
     }
   }
-  std::string err;
-  for (int par = 0; par < 2 && tmz; ++par)
   {
-    void **cur = par ? s->fB : s->fA;
-    if (!fused_prepare_tmz (&s->fmaps[par], s->fp, s->nc, cur[2], cur[3], cur[4], s->f[8], s->f[9], s->f[10], s->eps, s->pitch,
-                            s->ny, s->pitchM, &err))
+    const size_t need = (size_t) (s->nzl + 2) * s->ny * fb.dq_pitch * s->cell;
+    if (need != s->dq_bytes)
+    {
+      for (int d = 0; d < 2; ++d)
+        for (int a = 0; a < 3; ++a) { if (s->dq[d][a]) cudaFree (s->dq[d][a]); s->dq[d][a] = NULL; }
+      s->dq_bytes = 0;
+      for (int d = 0; d < 2; ++d)
+        for (int a = 0; a < (tmz ? 1 : 3); ++a)
+        {
+          cudaError_t e = cudaMalloc (&s->dq[d][a], need);
+          if (e == cudaSuccess) e = cudaMemsetAsync (s->dq[d][a], 0, need, s->s_compute);
+          if (e != cudaSuccess) { cudaGetLastError (); return FDTD_OK; } /* stay with the two-pass kernels */
+        }
+      s->dq_bytes = need;
+    }
+  }
+  std::string err;
+  for (int par = 0; par < 4 && tmz; ++par)
+  {
+    void **cur = (par >> 1) ? s->fB : s->fA;
+    if (!fused_prepare_tmz (&s->fmaps[par >> 1][par & 1], s->fp, s->nc, cur[2], cur[3], cur[4], s->dq[par & 1][0], fb.dq_pitch, s->f[9],
+                            s->f[10], s->eps, s->pitch, s->ny, s->pitchM, &err))
       return fail (FDTD_ERROR, "TMA descriptor set-up of the one-pass TMz kernel failed: %s", err.c_str ());
   }
   for (int par = 0; par < 2 && !tmz; ++par)
   {
     void **cur = par ? s->fB : s->fA, **nxt = par ? s->fA : s->fB;
-    void *d[3] = { s->f[6], s->f[7], s->f[8] }, *b[3] = { s->f[9], s->f[10], s->f[11] };
-    if (!fused_prepare_3d (&s->fmaps[par], s->fp, s->nc, cur, cur + 3, d, b, s->eps, s->pitch, s->ny, s->nzl + 2, s->pitchM,
-                           s->nzm + 2, &err))
-      return fail (FDTD_ERROR, "TMA descriptor set-up of the one-pass kernel failed: %s", err.c_str ());
+    void *b[3] = { s->f[9], s->f[10], s->f[11] };
+    for (int dpar = 0; dpar < 2; ++dpar)
+      if (!fused_prepare_3d (&s->fmaps[par][dpar], s->fp, s->nc, cur, cur + 3, s->dq[dpar], fb.dq_pitch, b, s->eps, s->pitch, s->ny,
+                             s->nzl + 2, s->pitchM, s->nzm + 2, &err))
+        return fail (FDTD_ERROR, "TMA descriptor set-up of the one-pass kernel failed: %s", err.c_str ());
     /* half-step kernels of the shell: the E phase reads H and E of cur; the H phase reads E of nxt and H of cur */
     void *fe[12], *fh[12];
     for (int i = 0; i < 12; ++i) fe[i] = fh[i] = s->f[i];
@@ -606,9 +639,24 @@ static int fold_core (fdtd_solver *s, bool fold)
   return FDTD_OK;
 }
 
+/* D of the absorber quarters back from the compact pair into the D arrays (stream-ordered) */
+static int release_dq (fdtd_solver *s)
+{
+  if (!s->dq_live) return FDTD_OK;
+  void *main_d[3] = { s->f[6], s->f[7], s->f[8] };
+  if (s->cfg.dims == 2) main_d[0] = s->f[8];
+  CUDA_TRY (launch_dq_copy (main_d, s->dq[s->dq_par], s->cfg.dims == 2 ? 1 : 3, false, s->fbox, s->cell, s->ny, s->pitch, s->ps, s->s_compute));
+  s->launches += s->cfg.dims == 2 ? 1 : 3;
+  s->dq_live = false;
+  s->dq_par = 0;
+  return FDTD_OK;
+}
+
 /* before anything but the time loop reads or changes D, B, E, H, eps, mu or sigma (stream-ordered, no sync) */
 static int ensure_unfolded (fdtd_solver *s)
 {
+  int rc = release_dq (s);
+  if (rc) return rc;
   if (!s->folded) return FDTD_OK;
   return fold_core (s, false);
 }
@@ -782,10 +830,22 @@ static int enqueue_steps_fused (fdtd_solver *s, long long nsteps)
     if (rc) return rc;
     CUDA_TRY (cudaEventRecord (s->ev_hx, C));
   }
+  if (!s->dq_live)
+  {
+    void *main_d[3] = { s->f[6], s->f[7], s->f[8] };
+    if (c.dims == 2) main_d[0] = s->f[8];
+    s->dq_par = 0;
+    CUDA_TRY (launch_dq_copy (main_d, s->dq[0], c.dims == 2 ? 1 : 3, true, s->fbox, s->cell, s->ny, s->pitch, s->ps, S));
+    s->launches += c.dims == 2 ? 1 : 3;
+    s->dq_live = true;
+  }
   for (long long n = 0; n < nsteps; ++n)
   {
     StepParams<T> p = make_params<T> (s); /* s->f are the current buffers */
     void **nxt = s->parity ? s->fA : s->fB;
+    FusedBox fb = s->fbox;
+    for (int a = 0; a < 3; ++a) fb.dq_out[a] = s->dq[s->dq_par ^ 1][a];
+    const FusedMaps3D &fmap = s->fmaps[s->parity][s->dq_par];
     for (int i = 0; i < 6; ++i) p.fo[i] = (T *) nxt[i];
     p.step = n;
     if (c.dims == 2)
@@ -801,7 +861,7 @@ static int enqueue_steps_fused (fdtd_solver *s, long long nsteps)
       pe.reg[1].kb = s->fbox.fy1 + 1; pe.reg[1].ke = s->ny;
       CUDA_TRY (launch_phase_tmz<T> (true, pe, cplx, true, tfsf, false, true, s->eps_uniform, S)); s->launches++;
       if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
-      CUDA_TRY (launch_step_core_tmz_fused<T> (p, s->fmaps[s->parity], s->fbox, cplx, tfsf, s->eps_uniform, S)); s->launches++;
+      CUDA_TRY (launch_step_core_tmz_fused<T> (p, fmap, fb, cplx, tfsf, s->eps_uniform, S)); s->launches++;
       if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
       StepParams<T> ph = pe;
       ph.f[2] = (T *) nxt[2];
@@ -810,6 +870,7 @@ static int enqueue_steps_fused (fdtd_solver *s, long long nsteps)
       if (tfsf) { CUDA_TRY (launch_incident<T> (false, p, cplx, false, S)); s->launches++; }
       for (int i = 0; i < 6; ++i) if (nxt[i]) s->f[i] = nxt[i];
       s->parity ^= 1;
+      s->dq_par ^= 1;
       continue;
     }
     const TmaMaps3D &shell_maps = s->tma_pp[s->parity];
@@ -841,7 +902,7 @@ static int enqueue_steps_fused (fdtd_solver *s, long long nsteps)
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
 
     /* the core: E and H in one pass */
-    CUDA_TRY (launch_step_core_fused<T> (p, s->fmaps[s->parity], s->fbox, cplx, tfsf, S));
+    CUDA_TRY (launch_step_core_fused<T> (p, fmap, fb, cplx, tfsf, S));
     s->launches++;
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
 
@@ -866,6 +927,7 @@ static int enqueue_steps_fused (fdtd_solver *s, long long nsteps)
     /* nxt holds the fields of the next step */
     for (int i = 0; i < 6; ++i) s->f[i] = nxt[i];
     s->parity ^= 1;
+    s->dq_par ^= 1;
   }
   if (multi) CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
   return FDTD_OK;
@@ -888,7 +950,7 @@ static int run_async (fdtd_solver *s, long long nsteps)
   CUDA_TRY (cudaEventRecord (s->run_ev[2 * s->runs_pending], s->s_compute));
   /* one pass per step in the core when the geometry allows it and mu is homogeneous (kernels3d_fused.cu) */
   s->fused_run = s->fused_ok && s->mu_uniform;
-  if (!s->fused_run && (rc = normalize_parity (s))) return rc; /* the two-pass tensor maps describe the first allocation */
+  if (!s->fused_run && ((rc = release_dq (s)) || (rc = normalize_parity (s)))) return rc; /* the two-pass tensor maps describe the first allocation */
   if (s->core_on && !s->folded && (rc = fold_core (s, true))) return rc;
   if (s->fused_run) rc = s->fp == 4 ? enqueue_steps_fused<float> (s, nsteps) : enqueue_steps_fused<double> (s, nsteps);
   else rc = s->fp == 4 ? enqueue_steps<float> (s, nsteps) : enqueue_steps<double> (s, nsteps);
@@ -1259,6 +1321,7 @@ int fdtd_destroy (fdtd_handle s)
     if (nccl) nccl->CommDestroy (s->comm);
   }
   for (int f = 0; f < 6; ++f) { if (s->fA[f]) s->f[f] = s->fA[f]; if (s->fB[f]) cudaFree (s->fB[f]); }
+  for (int d = 0; d < 2; ++d) for (int a = 0; a < 3; ++a) if (s->dq[d][a]) cudaFree (s->dq[d][a]);
   for (int f = 0; f < 12; ++f) if (s->f[f]) cudaFree (s->f[f]);
   void *ptrs[] = { s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->staging, s->red_partials, s->red_out };
   for (void *p : ptrs) if (p) cudaFree (p);
