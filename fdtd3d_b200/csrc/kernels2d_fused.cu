@@ -7,8 +7,8 @@
  * Hx, Hy of step t from that Ez; per-cell arithmetic = the half-step kernels' (kernels2d_common.cuh).
  *
  * A CTA works on (x, y) tiles of TXC x TY cells, one below the other, staged by TMA (cp.async.bulk.tensor, a ring of
- * stages, one mbarrier each: boxes of Hy with an x halo, Hx with the row below, Ez, eps).  It has one more lane and
- * one more thread row than the tile: every thread computes Ez' at its position, the rim threads for the first vector /
+ * stages, one mbarrier each: boxes of Hy with an x halo, Hx with the row below, Ez, eps).  It covers one more 16-byte vector per row and
+ * one more row than the tile (a warp per row + one warp for the rim column): every thread computes Ez' at its position, the rim threads for the first vector /
  * row of the neighbour tiles; Ez' goes through a double-buffered shared-memory tile, then the tile's own threads
  * compute Hx', Hy' from it.  Ez, Hx, Hy are ping-pong pairs (read `cur`, write `nxt`), because a neighbour CTA may
  * still need the old values this CTA would overwrite.  The rows outside the box (the y absorber) are advanced by the
@@ -52,7 +52,7 @@ struct FTile2
 {
   static constexpr int TY = FDTD_FUSED2D_TY;
   static constexpr int LX = 33;
-  static constexpr int NTHREADS = LX * (TY + 1);
+  static constexpr int NTHREADS = 32 * (TY + 2);          /* a warp per tile row and rim row + one warp for the x rim column */
   static constexpr int CELL = NC * (int) sizeof (T);
   static constexpr int V = 16 / CELL;
   static constexpr int TXC = 32 * V;
@@ -96,8 +96,12 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
   const int stage_sz = L::stage_bytes (fb.nq);
   unsigned char *xbuf = smem + S * stage_sz;
 
-  const int lx = threadIdx.x, ly = threadIdx.y;
-  const bool leader = lx == 0 && ly == 0;
+  /* warps 0 .. TY: lane = x vector of row `warp` (row TY is the y rim); warp TY + 1: the x rim column, lane = row.
+   * Row warps read, write and store whole contiguous rows; the rim warp touches one vector per row. */
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool valid = warp <= TY || lane <= TY;
+  const int lx = warp <= TY ? lane : 32, ly = warp <= TY ? warp : (lane <= TY ? lane : 0);
+  const bool leader = threadIdx.x == 0;
   const int i0t = blockIdx.x * L::TXC;
   const int ntiles = (fb.fy1 - fb.fy0 + 1) / TY;
   const int t0 = blockIdx.y * fb.kc, t1 = min (t0 + fb.kc, ntiles);
@@ -178,7 +182,7 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
     const unsigned char *st = smem + slot * stage_sz;
     const int j0t = fb.fy0 + t * TY;
     const int j = j0t + ly;
-    const bool ingrid = i0 < p.nx && j < p.ny;
+    const bool ingrid = valid && i0 < p.nx && j < p.ny;
     const bool own = lx < 32 && ly < TY && ingrid;
     const bool rim_from_nxt = ly == TY && j0t + TY > fb.fy1; /* a shell row: Ez' as the Ez shell pass wrote it */
     const long long o = (p.ps + (long long) j * p.pitch + i0) * NC;
@@ -313,7 +317,7 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
     else if (ingrid) ez = ldv_rw<T, W> (p.fo[2] + o);
 
     unsigned char *xw = xbuf + (t & 1) * L::X_BYTES;
-    *reinterpret_cast<FVec *> (xw + oX) = ez;
+    if (valid) *reinterpret_cast<FVec *> (xw + oX) = ez;
 
     /* Ez' of the whole tile is visible; every thread has read the stage: refill it with the tile S further down */
     __syncthreads ();
@@ -446,7 +450,7 @@ cudaError_t launch_fused2_t (const StepParams<T> &p, const Fused2DSet &maps, con
   }
   const int ntiles = (fb.fy1 - fb.fy0 + 1) / L::TY;
   if (ntiles <= 0) return cudaSuccess;
-  dim3 block (L::LX, L::TY + 1);
+  dim3 block (L::NTHREADS);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, (ntiles + fb.kc - 1) / fb.kc);
   step_core_tmz_fused<T, NC, TFSF, UNIEPS><<<grid, block, smem, stream>>> (p, maps, fb);
   return cudaGetLastError ();

@@ -10,9 +10,10 @@
  * How the dependency H'(i,j,k) <- E'(i+1,.,.), E'(.,j+1,.), E'(.,.,k+1) is met without a grid-wide barrier:
  *   - a CTA owns an (x, y) tile of TXC x TY cells and marches along z; in iteration k it computes E'(k) and then H'(k-1),
  *     so the z neighbour is simply the plane it has just produced (its own E'(k-1) is carried in registers);
- *   - the x and y neighbours that belong to the next tile are RECOMPUTED: the CTA has one more lane (33 x 16 bytes) and
- *     one more thread row than its tile, and those rim threads evaluate E' for the first vector / row of the neighbour
- *     tiles from the same staged data (boxes one vector wider and one row higher).  E' travels between the threads of
+ *   - the x and y neighbours that belong to the next tile are RECOMPUTED: the CTA covers one more 16-byte vector per row
+ *     and one more row than its tile, and those rim threads evaluate E' for the first vector / row of the neighbour
+ *     tiles from the same staged data (boxes one vector wider and one row higher; thread layout: a warp per row plus
+ *     one warp for the rim column).  E' travels between the threads of
  *     a CTA through a double-buffered shared-memory tile; only the tile's own cells are stored;
  *   - a neighbour CTA may run earlier or later, so nobody may overwrite what a rim thread still has to read: E and H
  *     are ping-pong pairs -- this kernel (and, while it is in use, the half-step kernels of the shell) reads buffer
@@ -71,7 +72,7 @@ struct FTile
   static constexpr bool F1 = sizeof (T) == 4 && NC == 1;
   static constexpr int TY = FDTD_FUSED_TY > 0 ? FDTD_FUSED_TY : (F1 ? 8 : 4);
   static constexpr int LX = 33;                       /* 32 lanes of the tile + the x rim lane */
-  static constexpr int NTHREADS = LX * (TY + 1);
+  static constexpr int NTHREADS = 32 * (TY + 2);          /* a warp per tile row and rim row + one warp for the x rim column */
   static constexpr int CELL = NC * (int) sizeof (T);
   static constexpr int V = 16 / CELL;
   static constexpr int TXC = 32 * V;
@@ -120,14 +121,18 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   const int stage_sz = L::stage_bytes (fb.nq);
   unsigned char *xbuf = smem + S * stage_sz; /* two E' exchange buffers */
 
-  const int lx = threadIdx.x, ly = threadIdx.y;
-  const bool leader = lx == 0 && ly == 0;
+  /* warps 0 .. TY: lane = x vector of row `warp` (row TY is the y rim); warp TY + 1: the x rim column, lane = row.
+   * Row warps read, write and store whole contiguous rows; the rim warp touches one vector per row. */
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool valid = warp <= TY || lane <= TY;
+  const int lx = warp <= TY ? lane : 32, ly = warp <= TY ? warp : (lane <= TY ? lane : 0);
+  const bool leader = threadIdx.x == 0;
   const int i0t = blockIdx.x * L::TXC, j0t = fb.fy0 + blockIdx.y * TY;
   const int k0 = fb.fz0 + blockIdx.z * fb.kc;
   const int k1 = min (k0 + fb.kc, fb.fz1 + 1);   /* E' and H' of planes [k0, k1); iteration k1 only supplies E'(k1) */
   if (k0 >= k1) return;
   const int i0 = i0t + lx * V, j = j0t + ly;
-  const bool ingrid = i0 < p.nx && j < p.ny;
+  const bool ingrid = valid && i0 < p.nx && j < p.ny;
   const bool own = lx < 32 && ly < TY && ingrid;  /* a cell of this CTA's tile: stored */
   /* rim row above the last tile row of the box: a shell row, its E' is read from the E shell pass's output */
   const bool rim_from_nxt = ly == TY && j0t + TY > fb.fy1;
@@ -481,7 +486,7 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
     }
 
     /* ---------------- hand E'(k) to the neighbours in the CTA, shift the plane-carried values */
-    if (k < k1)
+    if (k < k1 && valid)
     {
       unsigned char *xw = xbuf + (k & 1) * L::X_BYTES + oX;
       *reinterpret_cast<FVec *> (xw + 0 * L::E_STRIDE) = ex;
@@ -539,7 +544,7 @@ cudaError_t launch_fused_t (const StepParams<T> &p, const FusedSet &maps, const 
   }
   const int rows = fb.fy1 - fb.fy0 + 1, planes = fb.fz1 - fb.fz0 + 1;
   if (rows <= 0 || planes <= 0) return cudaSuccess;
-  dim3 block (L::LX, L::TY + 1);
+  dim3 block (L::NTHREADS);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, rows / L::TY, (planes + fb.kc - 1) / fb.kc);
   step_core_3d_fused<T, NC, TFSF><<<grid, block, smem, stream>>> (p, maps, fb);
   return cudaGetLastError ();
