@@ -18,7 +18,7 @@ def _ngpus():
         return 0
 
 
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 def test_slabs_match_single_domain(world):
     if _ngpus() < world:
         pytest.skip("needs %d GPUs" % world)
