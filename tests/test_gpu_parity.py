@@ -462,7 +462,7 @@ FUSED_CASES = [
     ((100, 24, 20), 3, 6, True, 8, False, 12),    # two x tiles: the rim lane recomputes E' across the tile boundary
     ((100, 24, 20), 3, 6, False, 8, False, 14),   # point source (its Dz advanced explicitly)
     ((150, 31, 23), 4, 7, True, 8, False, 9),     # three x tiles, ragged y and z
-    ((70, 28, 18), 3, 6, True, 8, True, 10),      # complex double: 32-cell tiles
+    ((80, 28, 18), 3, 6, True, 8, True, 10),      # complex double: 32-cell tiles
     ((200, 40, 22), 4, 6, False, 4, False, 12),   # float: 128-cell tiles, 8-row fused tiles inside 16-row shell tiles
     ((200, 40, 22), 4, 6, True, 4, False, 12),
     ((100, 36, 20), 3, 6, True, 4, True, 10),     # complex float
