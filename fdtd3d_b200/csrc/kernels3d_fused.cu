@@ -71,7 +71,6 @@ struct FTile
 {
   static constexpr bool F1 = sizeof (T) == 4 && NC == 1;
   static constexpr int TY = FDTD_FUSED_TY > 0 ? FDTD_FUSED_TY : (F1 ? 8 : 4);
-  static constexpr int LX = 33;                       /* 32 lanes of the tile + the x rim lane */
   static constexpr int NTHREADS = 32 * (TY + 2);          /* a warp per tile row and rim row + one warp for the x rim column */
   static constexpr int CELL = NC * (int) sizeof (T);
   static constexpr int V = 16 / CELL;
@@ -106,6 +105,46 @@ struct FTile
 
 /* ------------------------------------------------------------------ the kernel */
 
+/* one cell's scalars (re, im), and the three curls of a cell: passed by value so that nothing has its address taken */
+template <typename T, int NC> struct Cell { T v[NC]; };
+template <typename T, int NC> struct Curl3 { T x[NC], y[NC], z[NC]; };
+
+/* Rare path, kept out of the main loop: curls of a cell on a TF/SF face (E update) */
+template <typename T, int NC>
+__device__ __noinline__ Curl3<T, NC> tfsf_fix_e (const StepParams<T> &p, int i, int j, int gk, int k, Cell<T, NC> hz, Cell<T, NC> hz_jm,
+                                                 Cell<T, NC> hy, Cell<T, NC> hy_km, Cell<T, NC> hx, Cell<T, NC> hx_km, Cell<T, NC> hx_jm,
+                                                 Cell<T, NC> hz_m, Cell<T, NC> hy_m, Curl3<T, NC> cu)
+{
+  const int fx = tfsf_e_faces (p, 0, i, j, gk), fy = tfsf_e_faces (p, 1, i, j, gk), fz = tfsf_e_faces (p, 2, i, j, gk);
+  if (!(fx | fy | fz)) return cu;
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
+  {
+    if (fx) cu.x[c] = tfsf_curl_tab<T, NC, true> (p, 0, fx, c, i, j, k, hz.v[c], hz_jm.v[c], hy.v[c], hy_km.v[c]);
+    if (fy) cu.y[c] = tfsf_curl_tab<T, NC, true> (p, 1, fy, c, i, j, k, hx.v[c], hx_km.v[c], hz.v[c], hz_m.v[c]);
+    if (fz) cu.z[c] = tfsf_curl_tab<T, NC, true> (p, 2, fz, c, i, j, k, hy.v[c], hy_m.v[c], hx.v[c], hx_jm.v[c]);
+  }
+  return cu;
+}
+
+/* ... and of the H update (m = local plane, gm = global plane) */
+template <typename T, int NC>
+__device__ __noinline__ Curl3<T, NC> tfsf_fix_h (const StepParams<T> &p, int i, int j, int gm, int m, Cell<T, NC> ey_kp, Cell<T, NC> ey,
+                                                 Cell<T, NC> ez_jp, Cell<T, NC> ez, Cell<T, NC> ez_p, Cell<T, NC> ex_kp, Cell<T, NC> ex,
+                                                 Cell<T, NC> ex_jp, Cell<T, NC> ey_p, Curl3<T, NC> cu)
+{
+  const int fx = tfsf_h_faces (p, 0, i, j, gm), fy = tfsf_h_faces (p, 1, i, j, gm), fz = tfsf_h_faces (p, 2, i, j, gm);
+  if (!(fx | fy | fz)) return cu;
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
+  {
+    if (fx) cu.x[c] = tfsf_curl_tab<T, NC, false> (p, 0, fx, c, i, j, m, ey_kp.v[c], ey.v[c], ez_jp.v[c], ez.v[c]);
+    if (fy) cu.y[c] = tfsf_curl_tab<T, NC, false> (p, 1, fy, c, i, j, m, ez_p.v[c], ez.v[c], ex_kp.v[c], ex.v[c]);
+    if (fz) cu.z[c] = tfsf_curl_tab<T, NC, false> (p, 2, fz, c, i, j, m, ex_jp.v[c], ex.v[c], ey_p.v[c], ey.v[c]);
+  }
+  return cu;
+}
+
 template <typename T, int NC, bool TFSF>
 __global__ void __launch_bounds__ ((FTile<T, NC>::NTHREADS), (FTile<T, NC>::MINB))
 step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_constant__ FusedSet maps, const FusedBox fb)
@@ -115,11 +154,14 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
+  /* all shared-memory accesses index smem_raw with integer offsets, so that they compile to shared-space loads /
+   * stores with 32-bit addresses; `sm0` makes the first stage 128-byte aligned (TMA destination) */
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__ (8) unsigned long long full[S];
-  unsigned char *smem = reinterpret_cast<unsigned char *> ((reinterpret_cast<uintptr_t> (smem_raw) + 127) & ~(uintptr_t) 127);
+  const unsigned sbase = smem_u32 (smem_raw);
+  const int sm0 = (int) ((128u - (sbase & 127u)) & 127u);
   const int stage_sz = L::stage_bytes (fb.nq);
-  unsigned char *xbuf = smem + S * stage_sz; /* two E' exchange buffers */
+  const int xbuf0 = sm0 + S * stage_sz; /* two E' exchange buffers */
 
   /* warps 0 .. TY: lane = x vector of row `warp` (row TY is the y rim); warp TY + 1: the x rim column, lane = row.
    * Row warps read, write and store whole contiguous rows; the rim warp touches one vector per row. */
@@ -138,6 +180,7 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   const bool rim_from_nxt = ly == TY && j0t + TY > fb.fy1;
   /* the plane above the last one of the box likewise */
   const bool top_from_nxt = k1 > fb.fz1;
+  const bool compute_e = ingrid && !rim_from_nxt;
 
   /* quarters (8 lanes) of the tile row that lie in the x absorber: they carry D / B */
   int qmask = 0;
@@ -159,7 +202,7 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
 
   auto issue = [&] (int slot, int k)
   {
-    unsigned char *base = smem + slot * stage_sz;
+    unsigned char *base = smem_raw + sm0 + slot * stage_sz;
     unsigned long long *bar = &full[slot];
     mbar_expect_tx (bar, L::TX_BASE + __popc (qmask) * 3 * (L::SZ_QD + L::SZ_QB));
     tma_load_3d (base + L::OFF_A, &maps.m[0], bar, (i0t - V) * NC, j0t - 1, k + 1);
@@ -203,9 +246,25 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   const long long pl = p.ps * NC;
   const long long om = ((long long) (k0 + 1) * (p.ny + 1) + j) * p.pitchM + i0;
 
+  /* what does not change along the march, once: update ranges (YeeGridLayout.h:131-182) and TF/SF face candidates of
+   * this thread's cells as bit masks over v; rows likewise */
   const bool jlo = j >= 1, jhi = j < p.ny - 1;
+  int ilo_m = 0, ihi_m = 0, ife_m = 0, ifh_m = 0;
+#pragma unroll
+  for (int v = 0; v < V; ++v)
+  {
+    const int i = i0 + v;
+    if (i >= 1) ilo_m |= 1 << v;
+    if (i < p.nx - 1) ihi_m |= 1 << v;
+    if (TFSF && tfsf_axis_hit (p, 0, i, true)) ife_m |= 1 << v;
+    if (TFSF && tfsf_axis_hit (p, 0, i, false)) ifh_m |= 1 << v;
+  }
   const bool j_face_e = TFSF && tfsf_axis_hit (p, 1, j, true);
   const bool j_face_h = TFSF && tfsf_axis_hit (p, 1, j, false);
+  /* E: x needs ihi & jlo & klo, y: ilo & jhi & klo, z: ilo & jlo & khi; H: x: ilo & jhi & khi, y: ihi & jlo & khi, z: ihi & jhi & klo */
+  const int ex_m = jlo ? ihi_m : 0, ey_m = jhi ? ilo_m : 0, ez_m = jlo ? ilo_m : 0;
+  const int hx_m = jhi ? ilo_m : 0, hy_m = jlo ? ihi_m : 0, hz_m = jhi ? ihi_m : 0;
+  const T eps0 = p.eps0, dt_dx = p.dt_dx;
 
   /* carried from plane to plane: H of the plane below (operands of E', then the own values H' starts from), E' of the
    * plane below, the material of this plane */
@@ -221,11 +280,13 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
     eps_jp = ldv<T, V> (p.eps + om + p.pitchM);
     eps_ip = __ldg (p.eps + om + V);
   }
-  const T cb_h = p.dt_dx * rcp_t<T> (p.mu_const * p.mu0); /* homogeneous mu: (m + m) / 2 is m exactly */
+  const T cb_h = dt_dx * rcp_t<T> (p.mu_const * p.mu0); /* homogeneous mu: (m + m) / 2 is m exactly */
 
   long long step = 0;
   if (!TFSF) step = p.step;
+  const bool src_row = !TFSF && j == p.srcpos[1] && p.srcpos[0] >= i0 && p.srcpos[0] < i0 + V;
 
+  /* byte offsets of this thread's operands inside a stage / an exchange buffer */
   const int xo = lx * 16;
   const int oA_own = L::OFF_A + (ly + 1) * L::RW_A + 16 + xo, oA_jm = L::OFF_A + ly * L::RW_A + 16 + xo;
   const int oB_own = L::OFF_B + ly * L::RW_A + 16 + xo;
@@ -236,87 +297,82 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   const int oQB = L::OFF_Q + 3 * fb.nq * L::SZ_QD + qrank * L::SZ_QB + ly * 128 + (lx & 7) * 16;
   const int oX = ly * L::RW_C + xo;
 
+  int slot = 0, st = sm0;       /* ring slot of iteration k and its byte offset */
+  unsigned phase = 0;           /* mbarrier parity of that slot */
+  int xw = xbuf0, xr = xbuf0 + L::X_BYTES; /* exchange buffer written in this iteration / written in the previous one */
+
+#define SMV(W_, off) lds_s<T, W_> (sbase + (unsigned) (off))
+#define SM1(off) (lds_s<T, 1> (sbase + (unsigned) (off)).v[0])
+
   for (int k = k0; k <= k1; ++k, o += pl)
   {
-    const int n = k - k0;
-    const int slot = n % S;
-    const unsigned char *st = smem + slot * stage_sz;
-    mbar_wait (&full[slot], (n / S) & 1);
+    mbar_wait (&full[slot], phase);
 
     const int gk = p.kz0 + k;
     const bool klo = gk >= 1, khi = gk < p.nzg - 1;
 
     /* ---------------- E'(k) at this thread's position (tile cell or rim) */
-    const FVec hz = lds<T, W> (st + oA_own), hz_jm = lds<T, W> (st + oA_jm);
-    const FVec hy = lds<T, W> (st + oB_own);
-    const FVec hx = lds<T, W> (st + oC_own), hx_jm = lds<T, W> (st + oC_jm);
+    const FVec hz = SMV (W, st + oA_own), hz_jm = SMV (W, st + oA_jm);
+    const FVec hy = SMV (W, st + oB_own);
+    const FVec hx = SMV (W, st + oC_own), hx_jm = SMV (W, st + oC_jm);
     T hz_im[NC], hy_im[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c)
     {
-      hz_im[c] = *reinterpret_cast<const T *> (st + oA_own - L::CELL + c * sizeof (T));
-      hy_im[c] = *reinterpret_cast<const T *> (st + oB_own - L::CELL + c * sizeof (T));
+      hz_im[c] = SM1 (st + oA_own - L::CELL + c * (int) sizeof (T));
+      hy_im[c] = SM1 (st + oB_own - L::CELL + c * (int) sizeof (T));
     }
-    FVec ex = lds<T, W> (st + oE + 0 * L::E_STRIDE);
-    FVec ey = lds<T, W> (st + oE + 1 * L::E_STRIDE);
-    FVec ez = lds<T, W> (st + oE + 2 * L::E_STRIDE);
-    const MVec eps_kp = lds<T, V> (st + oM);
-    const MVec eps_jp_next = lds<T, V> (st + oM + L::RW_M);
-    const T eps_ip_next = *reinterpret_cast<const T *> (st + oM + V * sizeof (T));
+    FVec ex = SMV (W, st + oE + 0 * L::E_STRIDE);
+    FVec ey = SMV (W, st + oE + 1 * L::E_STRIDE);
+    FVec ez = SMV (W, st + oE + 2 * L::E_STRIDE);
+    const MVec eps_kp = SMV (V, st + oM);
+    const MVec eps_jp_next = SMV (V, st + oM + L::RW_M);
+    const T eps_ip_next = SM1 (st + oM + V * (int) sizeof (T));
 
-    if (ingrid && !(rim_from_nxt || (k == k1 && top_from_nxt)))
+    if (compute_e && !(k == k1 && top_from_nxt))
     {
-      const bool jk_face = j_face_e || (TFSF && tfsf_axis_hit (p, 2, gk, true));
+      /* cells that may lie on a TF/SF face in this plane (necessary condition; the exact test is in tfsf_fix_e) */
+      const int face_m = !TFSF ? 0 : ((j_face_e || tfsf_axis_hit (p, 2, gk, true)) ? (1 << V) - 1 : ife_m);
+      const int mx = klo ? ex_m : 0, my = klo ? ey_m : 0, mz = khi ? ez_m : 0;
       FVec dx, dy, dz;
       if (shell)
       {
-        dx = lds<T, W> (st + oQD + (0 * fb.nq) * L::SZ_QD);
-        dy = lds<T, W> (st + oQD + (1 * fb.nq) * L::SZ_QD);
-        dz = lds<T, W> (st + oQD + (2 * fb.nq) * L::SZ_QD);
+        dx = SMV (W, st + oQD + (0 * fb.nq) * L::SZ_QD);
+        dy = SMV (W, st + oQD + (1 * fb.nq) * L::SZ_QD);
+        dz = SMV (W, st + oQD + (2 * fb.nq) * L::SZ_QD);
       }
 #pragma unroll
       for (int v = 0; v < V; ++v)
       {
         const int i = i0 + v;
-        const bool ilo = i >= 1, ihi = i < p.nx - 1;
-        const bool do_ex = ihi && jlo && klo;
-        const bool do_ey = ilo && jhi && klo;
-        const bool do_ez = ilo && jlo && khi;
-
         T cex[NC], cey[NC], cez[NC];
+        T hz_m_[NC], hy_m_[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c)
         {
           const int s = v * NC + c;
-          const T hz_m = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
-          const T hy_m = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
+          hz_m_[c] = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
+          hy_m_[c] = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
           cex[c] = hz.v[s] - hz_jm.v[s] - hy.v[s] + hy_km.v[s];
-          cey[c] = hx.v[s] - hx_km.v[s] - hz.v[s] + hz_m;
-          cez[c] = hy.v[s] - hy_m - hx.v[s] + hx_jm.v[s];
+          cey[c] = hx.v[s] - hx_km.v[s] - hz.v[s] + hz_m_[c];
+          cez[c] = hy.v[s] - hy_m_[c] - hx.v[s] + hx_jm.v[s];
         }
-        if (TFSF && (jk_face || tfsf_axis_hit (p, 0, i, true)))
+        if (TFSF && ((face_m >> v) & 1))
         {
-          const int fx = tfsf_e_faces (p, 0, i, j, gk), fy = tfsf_e_faces (p, 1, i, j, gk), fz = tfsf_e_faces (p, 2, i, j, gk);
-          if (fx | fy | fz)
-          {
-#pragma unroll
-            for (int c = 0; c < NC; ++c)
-            {
-              const int s = v * NC + c;
-              const T hz_m = v > 0 ? hz.v[v > 0 ? s - NC : s] : hz_im[c];
-              const T hy_m = v > 0 ? hy.v[v > 0 ? s - NC : s] : hy_im[c];
-              if (fx) cex[c] = tfsf_curl_tab<T, NC, true> (p, 0, fx, c, i, j, k, hz.v[s], hz_jm.v[s], hy.v[s], hy_km.v[s]);
-              if (fy) cey[c] = tfsf_curl_tab<T, NC, true> (p, 1, fy, c, i, j, k, hx.v[s], hx_km.v[s], hz.v[s], hz_m);
-              if (fz) cez[c] = tfsf_curl_tab<T, NC, true> (p, 2, fz, c, i, j, k, hy.v[s], hy_m, hx.v[s], hx_jm.v[s]);
-            }
-          }
+          auto cell = [&] (const FVec &f) { Cell<T, NC> r; for (int c = 0; c < NC; ++c) r.v[c] = f.v[v * NC + c]; return r; };
+          Cell<T, NC> a_, b_;
+          Curl3<T, NC> cu;
+          for (int c = 0; c < NC; ++c) { a_.v[c] = hz_m_[c]; b_.v[c] = hy_m_[c]; cu.x[c] = cex[c]; cu.y[c] = cey[c]; cu.z[c] = cez[c]; }
+          cu = tfsf_fix_e<T, NC> (p, i, j, gk, k, cell (hz), cell (hz_jm), cell (hy), cell (hy_km), cell (hx), cell (hx_km), cell (hx_jm), a_, b_, cu);
+          for (int c = 0; c < NC; ++c) { cex[c] = cu.x[c]; cey[c] = cu.y[c]; cez[c] = cu.z[c]; }
         }
 
         const T e_c = eps_c.v[v];
         const T e_xp = v + 1 < V ? eps_c.v[v + 1 < V ? v + 1 : v] : eps_ip;
-        const T mod_x = ((e_c + e_xp) / (T) 2) * p.eps0;
-        const T mod_y = ((e_c + eps_jp.v[v]) / (T) 2) * p.eps0;
-        const T mod_z = ((e_c + eps_kp.v[v]) / (T) 2) * p.eps0;
+        const T mod_x = ((e_c + e_xp) / (T) 2) * eps0;
+        const T mod_y = ((e_c + eps_jp.v[v]) / (T) 2) * eps0;
+        const T mod_z = ((e_c + eps_kp.v[v]) / (T) 2) * eps0;
+        const bool do_ex = (mx >> v) & 1, do_ey = (my >> v) & 1, do_ez = (mz >> v) & 1;
 
         if (shell)
         {
@@ -339,32 +395,29 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
         }
         else
         {
-          const T cbx = plain_coef<T, false> (mod_x, p);
-          const T cby = plain_coef<T, false> (mod_y, p);
-          const T cbz = plain_coef<T, false> (mod_z, p);
+          /* straight-line code: the update is always evaluated and selected by the cell's range predicate */
+          const T cbx = dt_dx * rcp_t<T> (mod_x), cby = dt_dx * rcp_t<T> (mod_y), cbz = dt_dx * rcp_t<T> (mod_z);
 #pragma unroll
           for (int c = 0; c < NC; ++c)
           {
             const int s = v * NC + c;
-            if (do_ex) ex.v[s] = plain_cell<T, NC, false> (ex.v[s], cex[c], cbx);
-            if (do_ey) ey.v[s] = plain_cell<T, NC, false> (ey.v[s], cey[c], cby);
-            if (do_ez) ez.v[s] = plain_cell<T, NC, false> (ez.v[s], cez[c], cbz);
+            const T nx_ = fma_t<T> (cbx, cex[c], ex.v[s]), ny_ = fma_t<T> (cby, cey[c], ey.v[s]), nz_ = fma_t<T> (cbz, cez[c], ez.v[s]);
+            ex.v[s] = do_ex ? nx_ : ex.v[s];
+            ey.v[s] = do_ey ? ny_ : ey.v[s];
+            ez.v[s] = do_ez ? nz_ : ez.v[s];
           }
         }
 
-        if (!TFSF)
+        if (!TFSF && src_row && gk == p.srcpos[2] && i == p.srcpos[0])
         {
-          if (gk == p.srcpos[2] && j == p.srcpos[1] && i == p.srcpos[0])
+          /* the source overwrites Ez but not Dz (Scheme3D.cpp:1995-2024); see e_phase_3d_tma */
+          if (!shell && do_ez && own && k < k1)
           {
-            /* the source overwrites Ez but not Dz (Scheme3D.cpp:1995-2024); see e_phase_3d_tma */
-            if (!shell && do_ez && own && k < k1)
-            {
 #pragma unroll
-              for (int c = 0; c < NC; ++c) p.f[8][o + v * NC + c] = fma_t<T> (p.tab[0][KIND_AT].cbd[i], cez[c], p.f[8][o + v * NC + c]);
-            }
-#pragma unroll
-            for (int c = 0; c < NC; ++c) ez.v[v * NC + c] = p.src[step * NC + c];
+            for (int c = 0; c < NC; ++c) p.f[8][o + v * NC + c] = fma_t<T> (p.tab[0][KIND_AT].cbd[i], cez[c], p.f[8][o + v * NC + c]);
           }
+#pragma unroll
+          for (int c = 0; c < NC; ++c) ez.v[v * NC + c] = p.src[step * NC + c];
         }
       }
       if (own && k < k1)
@@ -392,60 +445,49 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
     {
       const int m = k - 1, gm = gk - 1;
       const bool mlo = gm >= 1, mhi = gm < p.nzg - 1;
-      const unsigned char *xb = xbuf + (m & 1) * L::X_BYTES + oX;
-      const FVec ex_jp = lds<T, W> (xb + 0 * L::E_STRIDE + L::RW_C);
-      const FVec ez_jp = lds<T, W> (xb + 2 * L::E_STRIDE + L::RW_C);
+      const FVec ex_jp = SMV (W, xr + oX + 0 * L::E_STRIDE + L::RW_C);
+      const FVec ez_jp = SMV (W, xr + oX + 2 * L::E_STRIDE + L::RW_C);
       T ey_ip[NC], ez_ip[NC];
 #pragma unroll
       for (int c = 0; c < NC; ++c)
       {
-        ey_ip[c] = *reinterpret_cast<const T *> (xb + 1 * L::E_STRIDE + 16 + c * sizeof (T));
-        ez_ip[c] = *reinterpret_cast<const T *> (xb + 2 * L::E_STRIDE + 16 + c * sizeof (T));
+        ey_ip[c] = SM1 (xr + oX + 1 * L::E_STRIDE + 16 + c * (int) sizeof (T));
+        ez_ip[c] = SM1 (xr + oX + 2 * L::E_STRIDE + 16 + c * (int) sizeof (T));
       }
-      const bool mk_face = j_face_h || (TFSF && tfsf_axis_hit (p, 2, gm, false));
+      const int face_m = !TFSF ? 0 : ((j_face_h || tfsf_axis_hit (p, 2, gm, false)) ? (1 << V) - 1 : ifh_m);
+      const int mx = mhi ? hx_m : 0, my = mhi ? hy_m : 0, mz = mlo ? hz_m : 0;
       FVec bx, by, bz;
       if (shell)
       {
-        bx = lds<T, W> (st + oQB + (0 * fb.nq) * L::SZ_QB);
-        by = lds<T, W> (st + oQB + (1 * fb.nq) * L::SZ_QB);
-        bz = lds<T, W> (st + oQB + (2 * fb.nq) * L::SZ_QB);
+        bx = SMV (W, st + oQB + (0 * fb.nq) * L::SZ_QB);
+        by = SMV (W, st + oQB + (1 * fb.nq) * L::SZ_QB);
+        bz = SMV (W, st + oQB + (2 * fb.nq) * L::SZ_QB);
       }
       FVec hxn = hx_km, hyn = hy_km, hzn = hz_km;
 #pragma unroll
       for (int v = 0; v < V; ++v)
       {
         const int i = i0 + v;
-        const bool ilo = i >= 1, ihi = i < p.nx - 1;
-        const bool do_hx = ilo && jhi && mhi;
-        const bool do_hy = ihi && jlo && mhi;
-        const bool do_hz = ihi && jhi && mlo;
-        T chx[NC], chy[NC], chz[NC];
+        const bool do_hx = (mx >> v) & 1, do_hy = (my >> v) & 1, do_hz = (mz >> v) & 1;
+        T chx[NC], chy[NC], chz[NC], ez_p[NC], ey_p[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c)
         {
           const int s = v * NC + c;
-          const T ez_p = v + 1 < V ? ezm.v[v + 1 < V ? s + NC : s] : ez_ip[c];
-          const T ey_p = v + 1 < V ? eym.v[v + 1 < V ? s + NC : s] : ey_ip[c];
+          ez_p[c] = v + 1 < V ? ezm.v[v + 1 < V ? s + NC : s] : ez_ip[c];
+          ey_p[c] = v + 1 < V ? eym.v[v + 1 < V ? s + NC : s] : ey_ip[c];
           chx[c] = ey.v[s] - eym.v[s] - ez_jp.v[s] + ezm.v[s];
-          chy[c] = ez_p - ezm.v[s] - ex.v[s] + exm.v[s];
-          chz[c] = ex_jp.v[s] - exm.v[s] - ey_p + eym.v[s];
+          chy[c] = ez_p[c] - ezm.v[s] - ex.v[s] + exm.v[s];
+          chz[c] = ex_jp.v[s] - exm.v[s] - ey_p[c] + eym.v[s];
         }
-        if (TFSF && (mk_face || tfsf_axis_hit (p, 0, i, false)))
+        if (TFSF && ((face_m >> v) & 1))
         {
-          const int fx = tfsf_h_faces (p, 0, i, j, gm), fy = tfsf_h_faces (p, 1, i, j, gm), fz = tfsf_h_faces (p, 2, i, j, gm);
-          if (fx | fy | fz)
-          {
-#pragma unroll
-            for (int c = 0; c < NC; ++c)
-            {
-              const int s = v * NC + c;
-              const T ez_p = v + 1 < V ? ezm.v[v + 1 < V ? s + NC : s] : ez_ip[c];
-              const T ey_p = v + 1 < V ? eym.v[v + 1 < V ? s + NC : s] : ey_ip[c];
-              if (fx) chx[c] = tfsf_curl_tab<T, NC, false> (p, 0, fx, c, i, j, m, ey.v[s], eym.v[s], ez_jp.v[s], ezm.v[s]);
-              if (fy) chy[c] = tfsf_curl_tab<T, NC, false> (p, 1, fy, c, i, j, m, ez_p, ezm.v[s], ex.v[s], exm.v[s]);
-              if (fz) chz[c] = tfsf_curl_tab<T, NC, false> (p, 2, fz, c, i, j, m, ex_jp.v[s], exm.v[s], ey_p, eym.v[s]);
-            }
-          }
+          auto cell = [&] (const FVec &f) { Cell<T, NC> r; for (int c = 0; c < NC; ++c) r.v[c] = f.v[v * NC + c]; return r; };
+          Cell<T, NC> a_, b_;
+          Curl3<T, NC> cu;
+          for (int c = 0; c < NC; ++c) { a_.v[c] = ez_p[c]; b_.v[c] = ey_p[c]; cu.x[c] = chx[c]; cu.y[c] = chy[c]; cu.z[c] = chz[c]; }
+          cu = tfsf_fix_h<T, NC> (p, i, j, gm, m, cell (ey), cell (eym), cell (ez_jp), cell (ezm), a_, cell (ex), cell (exm), cell (ex_jp), b_, cu);
+          for (int c = 0; c < NC; ++c) { chx[c] = cu.x[c]; chy[c] = cu.y[c]; chz[c] = cu.z[c]; }
         }
         if (shell)
         {
@@ -472,9 +514,10 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
           for (int c = 0; c < NC; ++c)
           {
             const int s = v * NC + c;
-            if (do_hx) hxn.v[s] = plain_cell<T, NC, false> (hxn.v[s], chx[c], cb_h);
-            if (do_hy) hyn.v[s] = plain_cell<T, NC, false> (hyn.v[s], chy[c], cb_h);
-            if (do_hz) hzn.v[s] = plain_cell<T, NC, false> (hzn.v[s], chz[c], cb_h);
+            const T nx_ = fma_t<T> (cb_h, chx[c], hxn.v[s]), ny_ = fma_t<T> (cb_h, chy[c], hyn.v[s]), nz_ = fma_t<T> (cb_h, chz[c], hzn.v[s]);
+            hxn.v[s] = do_hx ? nx_ : hxn.v[s];
+            hyn.v[s] = do_hy ? ny_ : hyn.v[s];
+            hzn.v[s] = do_hz ? nz_ : hzn.v[s];
           }
         }
       }
@@ -488,10 +531,9 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
     /* ---------------- hand E'(k) to the neighbours in the CTA, shift the plane-carried values */
     if (k < k1 && valid)
     {
-      unsigned char *xw = xbuf + (k & 1) * L::X_BYTES + oX;
-      *reinterpret_cast<FVec *> (xw + 0 * L::E_STRIDE) = ex;
-      *reinterpret_cast<FVec *> (xw + 1 * L::E_STRIDE) = ey;
-      *reinterpret_cast<FVec *> (xw + 2 * L::E_STRIDE) = ez;
+      sts_s<T, W> (sbase + (unsigned) (xw + oX + 0 * L::E_STRIDE), ex);
+      sts_s<T, W> (sbase + (unsigned) (xw + oX + 1 * L::E_STRIDE), ey);
+      sts_s<T, W> (sbase + (unsigned) (xw + oX + 2 * L::E_STRIDE), ez);
     }
     exm = ex; eym = ey; ezm = ez;
     hx_km = hx; hy_km = hy; hz_km = hz;
@@ -500,7 +542,12 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
     /* every thread has read the stage and the older exchange buffer: refill the slot with plane k + S */
     __syncthreads ();
     if (leader && k + S <= k1) issue (slot, k + S);
+    if (++slot == S) { slot = 0; st = sm0; phase ^= 1u; }
+    else st += stage_sz;
+    { const int t_ = xw; xw = xr; xr = t_; }
   }
+#undef SMV
+#undef SM1
 }
 
 /* ------------------------------------------------------------------ host side */

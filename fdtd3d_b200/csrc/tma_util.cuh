@@ -62,6 +62,31 @@ __device__ __forceinline__ Vec<T, W> lds (const unsigned char *p)
   return r;
 }
 
+/* Shared-space loads / stores by 32-bit shared address (LDS / STS): the generic-pointer form above compiles to generic
+ * LD, which costs 64-bit address arithmetic and the slower generic path.  volatile keeps them in program order with the
+ * mbarrier waits and barriers around them. */
+template <typename T, int W>
+__device__ __forceinline__ Vec<T, W> lds_s (unsigned addr)
+{
+  Vec<T, W> r;
+  constexpr int BYTES = (int) sizeof (T) * W;
+  static_assert (BYTES == 4 || BYTES == 8 || BYTES == 16, "vector of 4, 8 or 16 bytes");
+  unsigned *u = reinterpret_cast<unsigned *> (&r);
+  if (BYTES == 16) asm volatile ("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[BYTES == 16 ? 3 : 0]) : "r"(addr));
+  else if (BYTES == 8) asm volatile ("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(u[0]), "=r"(u[BYTES >= 8 ? 1 : 0]) : "r"(addr));
+  else asm volatile ("ld.shared.b32 %0, [%1];" : "=r"(u[0]) : "r"(addr));
+  return r;
+}
+template <typename T, int W>
+__device__ __forceinline__ void sts_s (unsigned addr, const Vec<T, W> &r)
+{
+  constexpr int BYTES = (int) sizeof (T) * W;
+  const unsigned *u = reinterpret_cast<const unsigned *> (&r);
+  if (BYTES == 16) asm volatile ("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[BYTES == 16 ? 3 : 0]) : "memory");
+  else if (BYTES == 8) asm volatile ("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(u[0]), "r"(u[BYTES >= 8 ? 1 : 0]) : "memory");
+  else asm volatile ("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(u[0]) : "memory");
+}
+
 typedef CUresult (*EncodeTiledFn) (CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
