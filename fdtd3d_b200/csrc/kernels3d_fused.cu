@@ -56,6 +56,9 @@ using namespace tma;
 #ifndef FDTD_FUSED_STAGES
 #define FDTD_FUSED_STAGES 0
 #endif
+#ifndef FDTD_FUSED_UNROLL
+#define FDTD_FUSED_UNROLL 2
+#endif
 #ifndef FDTD_FUSED_MINB
 #define FDTD_FUSED_MINB 0
 #endif
@@ -110,8 +113,10 @@ template <typename T, int NC> struct Cell { T v[NC]; };
 template <typename T, int NC> struct Curl3 { T x[NC], y[NC], z[NC]; };
 
 /* Rare path, kept out of the main loop: curls of a cell on a TF/SF face (E update) */
+/* inlined: as real calls they cost the whole kernel 25 % (ABI register constraints), measured */
+#define FDTD_TFSF_FIX_ATTR __forceinline__
 template <typename T, int NC>
-__device__ __noinline__ Curl3<T, NC> tfsf_fix_e (const StepParams<T> &p, int i, int j, int gk, int k, Cell<T, NC> hz, Cell<T, NC> hz_jm,
+__device__ FDTD_TFSF_FIX_ATTR Curl3<T, NC> tfsf_fix_e (const StepParams<T> &p, int i, int j, int gk, int k, Cell<T, NC> hz, Cell<T, NC> hz_jm,
                                                  Cell<T, NC> hy, Cell<T, NC> hy_km, Cell<T, NC> hx, Cell<T, NC> hx_km, Cell<T, NC> hx_jm,
                                                  Cell<T, NC> hz_m, Cell<T, NC> hy_m, Curl3<T, NC> cu)
 {
@@ -129,7 +134,7 @@ __device__ __noinline__ Curl3<T, NC> tfsf_fix_e (const StepParams<T> &p, int i, 
 
 /* ... and of the H update (m = local plane, gm = global plane) */
 template <typename T, int NC>
-__device__ __noinline__ Curl3<T, NC> tfsf_fix_h (const StepParams<T> &p, int i, int j, int gm, int m, Cell<T, NC> ey_kp, Cell<T, NC> ey,
+__device__ FDTD_TFSF_FIX_ATTR Curl3<T, NC> tfsf_fix_h (const StepParams<T> &p, int i, int j, int gm, int m, Cell<T, NC> ey_kp, Cell<T, NC> ey,
                                                  Cell<T, NC> ez_jp, Cell<T, NC> ez, Cell<T, NC> ez_p, Cell<T, NC> ex_kp, Cell<T, NC> ex,
                                                  Cell<T, NC> ex_jp, Cell<T, NC> ey_p, Curl3<T, NC> cu)
 {
@@ -248,7 +253,6 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
 
   /* what does not change along the march, once: update ranges (YeeGridLayout.h:131-182) and TF/SF face candidates of
    * this thread's cells as bit masks over v; rows likewise */
-  const bool jlo = j >= 1, jhi = j < p.ny - 1;
   int ilo_m = 0, ihi_m = 0, ife_m = 0, ifh_m = 0;
 #pragma unroll
   for (int v = 0; v < V; ++v)
@@ -261,9 +265,9 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   }
   const bool j_face_e = TFSF && tfsf_axis_hit (p, 1, j, true);
   const bool j_face_h = TFSF && tfsf_axis_hit (p, 1, j, false);
-  /* E: x needs ihi & jlo & klo, y: ilo & jhi & klo, z: ilo & jlo & khi; H: x: ilo & jhi & khi, y: ihi & jlo & khi, z: ihi & jhi & klo */
-  const int ex_m = jlo ? ihi_m : 0, ey_m = jhi ? ilo_m : 0, ez_m = jlo ? ilo_m : 0;
-  const int hx_m = jhi ? ilo_m : 0, hy_m = jlo ? ihi_m : 0, hz_m = jhi ? ihi_m : 0;
+  /* the rows and planes the kernel computes lie strictly inside the grid (configure_fused), so of the update ranges
+   * E: x needs ihi & jlo & klo, y: ilo & jhi & klo, z: ilo & jlo & khi; H: x: ilo & jhi & khi, y: ihi & jlo & khi,
+   * z: ihi & jhi & klo only the x parts can be false, and only in the absorber lanes of the first / last x tile */
   const T eps0 = p.eps0, dt_dx = p.dt_dx;
 
   /* carried from plane to plane: H of the plane below (operands of E', then the own values H' starts from), E' of the
@@ -301,16 +305,21 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   unsigned phase = 0;           /* mbarrier parity of that slot */
   int xw = xbuf0, xr = xbuf0 + L::X_BYTES; /* exchange buffer written in this iteration / written in the previous one */
 
+#ifdef FDTD_FUSED_GENERIC_LD
+#define SMV(W_, off) lds<T, W_> (smem_raw + (off))
+#define SM1(off) (*reinterpret_cast<const T *> (smem_raw + (off)))
+#else
 #define SMV(W_, off) lds_s<T, W_> (sbase + (unsigned) (off))
 #define SM1(off) (lds_s<T, 1> (sbase + (unsigned) (off)).v[0])
+#endif
 
+  constexpr int UNROLL_K = FDTD_FUSED_UNROLL; /* 2: the plane-carried values alternate between two register sets instead of being moved */
+#pragma unroll UNROLL_K
   for (int k = k0; k <= k1; ++k, o += pl)
   {
     mbar_wait (&full[slot], phase);
 
     const int gk = p.kz0 + k;
-    const bool klo = gk >= 1, khi = gk < p.nzg - 1;
-
     /* ---------------- E'(k) at this thread's position (tile cell or rim) */
     const FVec hz = SMV (W, st + oA_own), hz_jm = SMV (W, st + oA_jm);
     const FVec hy = SMV (W, st + oB_own);
@@ -333,7 +342,6 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
     {
       /* cells that may lie on a TF/SF face in this plane (necessary condition; the exact test is in tfsf_fix_e) */
       const int face_m = !TFSF ? 0 : ((j_face_e || tfsf_axis_hit (p, 2, gk, true)) ? (1 << V) - 1 : ife_m);
-      const int mx = klo ? ex_m : 0, my = klo ? ey_m : 0, mz = khi ? ez_m : 0;
       FVec dx, dy, dz;
       if (shell)
       {
@@ -369,14 +377,15 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
 
         const T e_c = eps_c.v[v];
         const T e_xp = v + 1 < V ? eps_c.v[v + 1 < V ? v + 1 : v] : eps_ip;
-        const T mod_x = ((e_c + e_xp) / (T) 2) * eps0;
-        const T mod_y = ((e_c + eps_jp.v[v]) / (T) 2) * eps0;
-        const T mod_z = ((e_c + eps_kp.v[v]) / (T) 2) * eps0;
-        const bool do_ex = (mx >> v) & 1, do_ey = (my >> v) & 1, do_ez = (mz >> v) & 1;
 
         if (shell)
         {
-          /* x absorber lanes: the UPML form, coefficients straight from the tables (few lanes, L1-resident) */
+          /* x absorber lanes: the UPML form, coefficients straight from the tables (few lanes, L1-resident); these
+           * lanes include the cells at the x ends of the grid, so they keep the update-range predicates */
+          const T mod_x = ((e_c + e_xp) / (T) 2) * eps0;
+          const T mod_y = ((e_c + eps_jp.v[v]) / (T) 2) * eps0;
+          const T mod_z = ((e_c + eps_kp.v[v]) / (T) 2) * eps0;
+          const bool do_ex = (ihi_m >> v) & 1, do_ey = (ilo_m >> v) & 1, do_ez = do_ey;
           T cbx, ccx, cby, ccy, cbz, ccz;
           sweep3_coefs<T, false> (p.tab[0][KIND_BTW].p[i], p.tab[0][KIND_BTW].m[i], p.tab[2][KIND_AT].invp[gk], mod_x, cbx, ccx);
           sweep3_coefs<T, false> (p.tab[1][KIND_BTW].p[j], p.tab[1][KIND_BTW].m[j], p.tab[0][KIND_AT].invp[i], mod_y, cby, ccy);
@@ -395,23 +404,32 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
         }
         else
         {
-          /* straight-line code: the update is always evaluated and selected by the cell's range predicate */
-          const T cbx = dt_dx * rcp_t<T> (mod_x), cby = dt_dx * rcp_t<T> (mod_y), cbz = dt_dx * rcp_t<T> (mod_z);
+          /* Core lanes.  Every cell computed here lies strictly inside the grid (configure_fused keeps the box off the
+           * grid's faces), so all three components are inside their update ranges: no predicates.  Where the four
+           * material samples of the cell coincide -- everywhere but at material interfaces -- ((e + e) / 2) eps0 is
+           * e eps0 exactly and one reciprocal serves the three components (same bits as three). */
+          T cbx, cby, cbz;
+          if (e_xp == e_c && eps_jp.v[v] == e_c && eps_kp.v[v] == e_c) cbx = cby = cbz = dt_dx * rcp_t<T> (e_c * eps0);
+          else
+          {
+            cbx = dt_dx * rcp_t<T> (((e_c + e_xp) / (T) 2) * eps0);
+            cby = dt_dx * rcp_t<T> (((e_c + eps_jp.v[v]) / (T) 2) * eps0);
+            cbz = dt_dx * rcp_t<T> (((e_c + eps_kp.v[v]) / (T) 2) * eps0);
+          }
 #pragma unroll
           for (int c = 0; c < NC; ++c)
           {
             const int s = v * NC + c;
-            const T nx_ = fma_t<T> (cbx, cex[c], ex.v[s]), ny_ = fma_t<T> (cby, cey[c], ey.v[s]), nz_ = fma_t<T> (cbz, cez[c], ez.v[s]);
-            ex.v[s] = do_ex ? nx_ : ex.v[s];
-            ey.v[s] = do_ey ? ny_ : ey.v[s];
-            ez.v[s] = do_ez ? nz_ : ez.v[s];
+            ex.v[s] = fma_t<T> (cbx, cex[c], ex.v[s]);
+            ey.v[s] = fma_t<T> (cby, cey[c], ey.v[s]);
+            ez.v[s] = fma_t<T> (cbz, cez[c], ez.v[s]);
           }
         }
 
         if (!TFSF && src_row && gk == p.srcpos[2] && i == p.srcpos[0])
         {
           /* the source overwrites Ez but not Dz (Scheme3D.cpp:1995-2024); see e_phase_3d_tma */
-          if (!shell && do_ez && own && k < k1)
+          if (!shell && own && k < k1)
           {
 #pragma unroll
             for (int c = 0; c < NC; ++c) p.f[8][o + v * NC + c] = fma_t<T> (p.tab[0][KIND_AT].cbd[i], cez[c], p.f[8][o + v * NC + c]);
@@ -444,7 +462,6 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
     if (k > k0 && own)
     {
       const int m = k - 1, gm = gk - 1;
-      const bool mlo = gm >= 1, mhi = gm < p.nzg - 1;
       const FVec ex_jp = SMV (W, xr + oX + 0 * L::E_STRIDE + L::RW_C);
       const FVec ez_jp = SMV (W, xr + oX + 2 * L::E_STRIDE + L::RW_C);
       T ey_ip[NC], ez_ip[NC];
@@ -455,7 +472,6 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
         ez_ip[c] = SM1 (xr + oX + 2 * L::E_STRIDE + 16 + c * (int) sizeof (T));
       }
       const int face_m = !TFSF ? 0 : ((j_face_h || tfsf_axis_hit (p, 2, gm, false)) ? (1 << V) - 1 : ifh_m);
-      const int mx = mhi ? hx_m : 0, my = mhi ? hy_m : 0, mz = mlo ? hz_m : 0;
       FVec bx, by, bz;
       if (shell)
       {
@@ -468,7 +484,6 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
       for (int v = 0; v < V; ++v)
       {
         const int i = i0 + v;
-        const bool do_hx = (mx >> v) & 1, do_hy = (my >> v) & 1, do_hz = (mz >> v) & 1;
         T chx[NC], chy[NC], chz[NC], ez_p[NC], ey_p[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c)
@@ -492,6 +507,7 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
         if (shell)
         {
           const T mod = p.mu_const * p.mu0;
+          const bool do_hx = (ilo_m >> v) & 1, do_hy = (ihi_m >> v) & 1, do_hz = do_hy;
           T cbx, ccx, cby, ccy, cbz, ccz;
           sweep3_coefs<T, false> (p.tab[0][KIND_AT].p[i], p.tab[0][KIND_AT].m[i], p.tab[2][KIND_BTW].invp[gm], mod, cbx, ccx);
           sweep3_coefs<T, false> (p.tab[1][KIND_AT].p[j], p.tab[1][KIND_AT].m[j], p.tab[0][KIND_BTW].invp[i], mod, cby, ccy);
@@ -510,14 +526,14 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
         }
         else
         {
+          /* core lanes: inside every update range (see above) */
 #pragma unroll
           for (int c = 0; c < NC; ++c)
           {
             const int s = v * NC + c;
-            const T nx_ = fma_t<T> (cb_h, chx[c], hxn.v[s]), ny_ = fma_t<T> (cb_h, chy[c], hyn.v[s]), nz_ = fma_t<T> (cb_h, chz[c], hzn.v[s]);
-            hxn.v[s] = do_hx ? nx_ : hxn.v[s];
-            hyn.v[s] = do_hy ? ny_ : hyn.v[s];
-            hzn.v[s] = do_hz ? nz_ : hzn.v[s];
+            hxn.v[s] = fma_t<T> (cb_h, chx[c], hxn.v[s]);
+            hyn.v[s] = fma_t<T> (cb_h, chy[c], hyn.v[s]);
+            hzn.v[s] = fma_t<T> (cb_h, chz[c], hzn.v[s]);
           }
         }
       }

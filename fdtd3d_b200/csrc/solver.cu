@@ -514,8 +514,17 @@ static int configure_fused (fdtd_solver *s)
   }
   else
   {
+    /* The kernel's core lanes carry no update-range predicates: every cell it computes must lie strictly inside the
+     * grid.  With an absorber on every face this costs nothing; without one the box gives up the tile row / plane
+     * on the face, and a core that reaches the x faces keeps the two-pass kernels. */
+    if (s->core_lo[0] < 1 || s->core_hi[0] > s->nx - 2) return FDTD_OK;
+    if (fb.fy0 < 1) fb.fy0 += sty;
+    if (fb.fy1 > s->ny - 2) fb.fy1 = (s->ny - 1) / sty * sty - 1;
+    if (fb.fy1 < fb.fy0) return FDTD_OK;
     if (fb.fy0 % sty || (fb.fy1 + 1) % sty || (fb.fy1 - fb.fy0 + 1) % fty || sty % fty) return FDTD_OK;
     int zlo = s->core_lo[2] - s->kz0, zhi = s->core_hi[2] - s->kz0;
+    if (s->kz0 + zlo < 1) zlo = 1 - s->kz0;
+    if (s->kz0 + zhi > s->nzg - 2) zhi = s->nzg - 2 - s->kz0;
     const int zmin = s->cfg.rank > 0 ? 1 : 0, zmax = s->cfg.rank + 1 < s->cfg.nranks ? s->nzl - 2 : s->nzl - 1;
     if (zlo < zmin) zlo = zmin;
     if (zhi > zmax) zhi = zmax;
