@@ -277,14 +277,14 @@ def make_solver(F, name, exact, rank, world, local, dist):
 TUNING = None  # (march, one_pass_march, allow_one_pass) from the command line, applied to every solver bench.py creates
 
 
-def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False):
+def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False, tuning=None):
     """Device-timed throughput of one configuration on the ranks of this job: W untimed steps, then K steps between
     barriers, CUDA events on the solver's stream, max over ranks.  Returns the numbers of the bench line for it."""
     rank, world, local, dist, barrier, max_over_ranks = env
     w = WORKLOADS[name]
     s, cfg, nz_total = make_solver(F, name, exact, rank, world, local, dist)
-    if TUNING:
-        s.set_tuning(*TUNING)
+    if tuning or TUNING:
+        s.set_tuning(*(tuning or TUNING))
     z0, nzl = F.slab_range(nz_total, rank, world)
     cells = w["nx"] * w["ny"] * nz_total
     s.run(warmup)
@@ -411,7 +411,7 @@ def main():
     ap.add_argument("--quick", action="store_true", help="headline line only: no roofline.modes, other_configs, sustained")
     ap.add_argument("--march", type=int, default=0, help="tuning: planes (2D: rows) marched per CTA by the half-step kernels (0 = library rule)")
     ap.add_argument("--one-pass-march", type=int, default=0, help="tuning: planes (2D: tiles) marched per CTA by the one-pass kernel")
-    ap.add_argument("--no-one-pass", action="store_true", help="keep the two half-step kernels everywhere (A/B measurement)")
+    ap.add_argument("--one-pass", action="store_true", help="experimental: one kernel per step in the core (fdtd_set_tuning; slower today, DESIGN 3.1c)")
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="BASELINE.json config (default c3, the headline)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -453,9 +453,9 @@ def main():
         raise SystemExit("the 2D TMz workload runs on one GPU")
     env = (rank, world, local, dist, barrier, max_over_ranks)
     global TUNING
-    if args.march or args.one_pass_march or args.no_one_pass:
-        TUNING = (args.march, args.one_pass_march, not args.no_one_pass)
-    headline = args.workload == "c3" and args.exact == 0 and not args.quick and not (args.march or args.one_pass_march or args.no_one_pass)
+    if args.march or args.one_pass_march or args.one_pass:
+        TUNING = (args.march, args.one_pass_march, args.one_pass)
+    headline = args.workload == "c3" and args.exact == 0 and not args.quick and not (args.march or args.one_pass_march or args.one_pass)
 
     # ---- parity of the sharded path against the CPU oracle, before anything is timed
     parity = None
@@ -558,7 +558,7 @@ def main():
     s.close()
 
     # ---- everything else the round claims, measured by this same run (headline invocation only)
-    modes = other = sustained = None
+    modes = other = sustained = one_pass = None
     if headline:
         short = max(5, min(args.steps, 12))
         # the like-for-like figure (D/B through every cell) and the bit-exact one, same workload, same process
@@ -577,6 +577,13 @@ def main():
                 other[key] = brief(measure(F, env, nme, mode, 100 if nme in ("c2", "c1") else short, 5 if nme in ("c2", "c1") else 3))
             except Exception as ex:
                 other[key] = {"error": repr(ex)}
+        # the experimental one-pass core kernels (off by default), measured beside the shipped two-pass path
+        one_pass = {}
+        for nme in ["c3", "c5"] + (["c2"] if world == 1 else []):
+            try:
+                one_pass[nme] = brief(measure(F, env, nme, 0, 100 if nme == "c2" else short, 3, tuning=(0, 0, True)))
+            except Exception as ex:
+                one_pass[nme] = {"error": repr(ex)}
         # BASELINE.json quotes 1000-step runs: the sustained rate of the headline configuration, with its own clock sample
         try:
             r1000 = measure(F, env, "c3", 0, 1000, 3, sample_clocks=True)
@@ -608,6 +615,10 @@ def main():
             line["other_configs"] = other
         if sustained is not None:
             line["sustained"] = sustained
+        if one_pass is not None:
+            line["one_pass_experiment"] = {"note": "fdtd_set_tuning (allow_one_pass = 1): E and H of the core in ONE kernel per step (12 instead of 18 "
+                                                   "field values per cell, bit-identical results); latency-bound today, hence not the default "
+                                                   "(DESIGN.md 3.1c, profiles/r2_one_pass.md)", "configs": one_pass}
         print(json.dumps(line))
     if dist:
         dist.destroy_process_group()

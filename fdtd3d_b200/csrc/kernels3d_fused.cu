@@ -57,7 +57,7 @@ using namespace tma;
 #define FDTD_FUSED_STAGES 0
 #endif
 #ifndef FDTD_FUSED_UNROLL
-#define FDTD_FUSED_UNROLL 2
+#define FDTD_FUSED_UNROLL 1
 #endif
 #ifndef FDTD_FUSED_MINB
 #define FDTD_FUSED_MINB 0
@@ -73,7 +73,9 @@ template <typename T, int NC>
 struct FTile
 {
   static constexpr bool F1 = sizeof (T) == 4 && NC == 1;
-  static constexpr int TY = FDTD_FUSED_TY > 0 ? FDTD_FUSED_TY : (F1 ? 8 : 4);
+  /* measured on 512^3 double (profiles/r2_one_pass.md): 8 rows x 3 stages x 1 CTA per SM 3.51 ms, 4 rows x 2 CTAs 3.85 ms,
+   * 16 rows (register-capped, spills) 4.67 ms, 4 rows x 3 CTAs (spills) 6.8 ms */
+  static constexpr int TY = FDTD_FUSED_TY > 0 ? FDTD_FUSED_TY : 8;
   static constexpr int NTHREADS = 32 * (TY + 2);          /* a warp per tile row and rim row + one warp for the x rim column */
   static constexpr int CELL = NC * (int) sizeof (T);
   static constexpr int V = 16 / CELL;
@@ -101,7 +103,7 @@ struct FTile
   static constexpr int TX_BASE = SZ_A + SZ_B + SZ_C + 3 * SZ_E + SZ_M;
   static constexpr int X_BYTES = 3 * E_STRIDE;        /* one E' exchange buffer */
   static constexpr int STAGES = FDTD_FUSED_STAGES > 0 ? FDTD_FUSED_STAGES : 3;
-  static constexpr int MINB = FDTD_FUSED_MINB > 0 ? FDTD_FUSED_MINB : (F1 ? 1 : 2);
+  static constexpr int MINB = FDTD_FUSED_MINB > 0 ? FDTD_FUSED_MINB : 1;
   __host__ __device__ static constexpr int stage_bytes (int nq) { return OFF_Q + nq * 3 * (SZ_QD + SZ_QB); }
   __host__ __device__ static constexpr int smem_bytes (int nq) { return STAGES * stage_bytes (nq) + 2 * X_BYTES + 128; }
 };

@@ -122,7 +122,7 @@ struct fdtd_solver
   TmaMaps3D tma_pp[2];  /* per parity, half-step kernels of the shell: E phase reads cur, H phase reads E of nxt */
   int fused_kc;         /* planes marched per CTA of the fused kernel; 0 = default rule */
   int kchunk_forced;    /* fdtd_set_tuning: planes marched per CTA of the half-step kernels; 0 = default rule */
-  bool fused_forbidden; /* fdtd_set_tuning: keep the two-pass kernels (A/B measurements) */
+  bool fused_wanted;    /* fdtd_set_tuning: use the one-pass kernels where the geometry allows (off by default: slower) */
   float prof_f_ms;
   bool use_tma;
   int kchunk;
@@ -490,7 +490,7 @@ static int configure_fused (fdtd_solver *s)
   if (rc) return rc;
   s->fused_ok = false;
   const bool tmz = s->cfg.dims == 2;
-  if (!s->core_on || (!tmz && !s->use_tma) || s->fused_forbidden) return FDTD_OK;
+  if (!s->core_on || (!tmz && !s->use_tma) || !s->fused_wanted) return FDTD_OK;
   if ((rc = normalize_parity (s))) return rc;
   int txc = 0, fty = 0, smem_q = 0, smem_base = 0, sty = 1;
   if (tmz) fused_tile_geometry_tmz (s->fp, s->nc, &txc, &fty, &smem_q, &smem_base);
@@ -518,10 +518,13 @@ static int configure_fused (fdtd_solver *s)
      * grid.  With an absorber on every face this costs nothing; without one the box gives up the tile row / plane
      * on the face, and a core that reaches the x faces keeps the two-pass kernels. */
     if (s->core_lo[0] < 1 || s->core_hi[0] > s->nx - 2) return FDTD_OK;
-    if (fb.fy0 < 1) fb.fy0 += sty;
-    if (fb.fy1 > s->ny - 2) fb.fy1 = (s->ny - 1) / sty * sty - 1;
+    /* rows: whole tile rows of both the one-pass kernel and the half-step kernels that take the rest */
+    const int al = sty % fty == 0 ? sty : (fty % sty == 0 ? fty : sty * fty);
+    fb.fy0 = (fb.fy0 + al - 1) / al * al;
+    if (fb.fy0 < 1) fb.fy0 = al;
+    fb.fy1 = (fb.fy1 + 1) / al * al - 1;
+    if (fb.fy1 > s->ny - 2) fb.fy1 = (s->ny - 1) / al * al - 1;
     if (fb.fy1 < fb.fy0) return FDTD_OK;
-    if (fb.fy0 % sty || (fb.fy1 + 1) % sty || (fb.fy1 - fb.fy0 + 1) % fty || sty % fty) return FDTD_OK;
     int zlo = s->core_lo[2] - s->kz0, zhi = s->core_hi[2] - s->kz0;
     if (s->kz0 + zlo < 1) zlo = 1 - s->kz0;
     if (s->kz0 + zhi > s->nzg - 2) zhi = s->nzg - 2 - s->kz0;
@@ -1596,7 +1599,7 @@ int fdtd_set_tuning (fdtd_handle s, int march_planes, int one_pass_march_planes,
   if (rc) return rc;
   s->kchunk_forced = march_planes;
   s->fused_kc = one_pass_march_planes;
-  s->fused_forbidden = allow_one_pass == 0;
+  s->fused_wanted = allow_one_pass != 0;
   if (s->cfg.dims == 2) s->kchunk = march_planes > 0 ? march_planes : 8;
   return configure_3d (s, true);
 }

@@ -148,8 +148,7 @@ int fdtd_download (fdtd_handle h, int field, void *host, int order, int64_t z0, 
 
 /* Sets every cell of a field to (re, im).  For FDTD_MU (and, with dims == 2, FDTD_EPS) this also tells the library that
  * the material is homogeneous: the kernels then take the value from here instead of reading the array (same results,
- * less memory traffic), and with a homogeneous mu the 3D fast mode may advance the core with one pass per step
- * (fdtd_get_fused_box).  fdtd_upload of a material scans what it uploaded, so an uploaded array that holds one value
+ * less memory traffic).  fdtd_upload of a material scans what it uploaded, so an uploaded array that holds one value
  * everywhere (the reference's own mu = 1) is recognised as well.  fdtd_create fills eps and mu with 1. */
 int fdtd_fill (fdtd_handle h, int field, double re, double im);
 
@@ -207,20 +206,22 @@ int fdtd_get_time_step (fdtd_handle h, int64_t *t);
 int fdtd_get_core_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
 
 /*
- * The box of cells (global indices, inclusive; lo > hi when there is none) that the time loop advances with ONE pass
- * per time step instead of an E and an H half step (exact_mode 0, 3D, use_pml, homogeneous mu): inside it E and H are
- * read once and written once per step (12 instead of 18 field values per cell), see DESIGN.md.  It spans the whole x
- * range, the rows of the core box and its planes on this rank minus a plane next to another rank.  No reference
- * counterpart: a diagnostic (bench.py reports the bytes the step has to move from it).  fdtd_fused_time: summed device
- * time of that kernel over the last completed run, with fdtd_set_profiling on; fdtd_phase_times then returns the E and
- * H half steps of the remaining shell.
+ * One pass per time step in the core (experimental, OFF unless switched on with fdtd_set_tuning): instead of an E and
+ * an H half step, one kernel reads E and H once and writes them once inside a box that spans the whole x range, the
+ * rows of the core box and its planes on this rank (12 instead of 18 field values per cell and step; exact_mode 0,
+ * use_pml, homogeneous mu).  Results are bit-identical to the two half-step kernels.  On B200 it is currently SLOWER
+ * than they are -- the fused instruction stream is latency-bound at the occupancy its registers allow (DESIGN.md 3.1c,
+ * profiles/r2_one_pass.md) -- which is why it is not the default.  fdtd_get_fused_box: the box (global indices,
+ * inclusive; lo > hi when the kernel is not in use); fdtd_fused_time: summed device time of that kernel over the last
+ * completed run, with fdtd_set_profiling on (fdtd_phase_times then returns the E and H half steps of the remaining
+ * shell).  No reference counterpart.
  */
 int fdtd_get_fused_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
 int fdtd_fused_time (fdtd_handle h, float *ms);
 
 /* Tuning aid, no reference counterpart: planes (2D: rows) marched per CTA by the half-step kernels and by the one-pass
- * kernel (0 = the library's rule), and whether the one-pass kernel may be used at all (0 keeps the two half-step
- * kernels everywhere, for A/B measurements).  Results do not depend on any of it. */
+ * kernel (0 = the library's rule), and whether the one-pass kernel is used where the geometry allows (0 = no, the
+ * default; 1 = yes).  Results do not depend on any of it. */
 int fdtd_set_tuning (fdtd_handle h, int march_planes, int one_pass_march_planes, int allow_one_pass);
 
 /* The same box for a configuration and sigma profiles (FPValue arrays of size[a] + 1 values, NULL = all zero) without

@@ -107,7 +107,7 @@ def test_cli_checkpoint_and_resume(dims, tmp_path):
 def test_cli_num_cuda_gpus_is_byte_identical_to_one_gpu(ngpus, flags, tmp_path):
     """--num-cuda-gpus N (Source/Settings/Settings.inc:81, Source/main.cpp:88-96): N z-slabs in one process, NCCL halo
     planes, slabs gathered into the reference's whole-grid DAT files -- byte for byte the single-GPU run, in exact mode
-    and in the default fast mode (one-pass core kernel included: the grid is wide enough for it)."""
+    and in the default fast mode."""
     import torch
     if torch.cuda.device_count() < ngpus:
         pytest.skip("needs %d GPUs" % ngpus)

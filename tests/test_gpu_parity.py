@@ -472,7 +472,8 @@ FUSED_CASES = [
 
 @pytest.mark.parametrize("case", FUSED_CASES, ids=lambda c: "%s-t%d-vt%d%s" % ("x".join(map(str, c[0])), c[3], c[4], "c" if c[5] else ""))
 def test_one_pass_core_equals_two_pass_and_oracle(case):
-    """exact_mode 0 with a homogeneous mu advances the core with ONE kernel per step (E and H fused, ping-pong buffers).
+    """With fdtd_set_tuning (allow_one_pass) exact_mode 0 with a homogeneous mu advances the core with ONE kernel per step
+    (E and H fused, ping-pong buffers).
     Same per-cell arithmetic as the two half-step kernels, so the fields are bit-identical to the two-pass run, and both
     are within the north-star tolerance of the oracle -- also across runs of odd length (buffer parity), D/B reads
     between runs and an upload that switches the one-pass kernel off (non-homogeneous mu)."""
@@ -495,8 +496,7 @@ def test_one_pass_core_equals_two_pass_and_oracle(case):
             s.upload("Eps", inputs["Eps"])
             for name in O.field_names(cfg):
                 s.upload(name, fields[name])
-            if not one_pass:
-                s.set_tuning(allow_one_pass=False)
+            s.set_tuning(allow_one_pass=one_pass)   # off by default
             box = s.fused_box
             mids = []
             for n in chunks:
@@ -527,6 +527,8 @@ def test_one_pass_core_equals_two_pass_and_oracle(case):
         s.upload("Eps", inputs["Eps"])
         for name in O.field_names(cfg):
             s.upload(name, fields[name])
+        assert s.fused_box is None              # off unless asked for
+        s.set_tuning(allow_one_pass=True)
         assert s.fused_box is not None
         s.upload("Mu", inputs["Mu"])
         assert s.fused_box is None
@@ -574,8 +576,7 @@ def test_one_pass_core_tmz_equals_two_pass_and_oracle(case):
                 s.upload("Eps", inputs["Eps"])
             for name in O.field_names(cfg):
                 s.upload(name, fields[name])
-            if not one_pass:
-                s.set_tuning(allow_one_pass=False)
+            s.set_tuning(allow_one_pass=one_pass)   # off by default
             box = s.fused_box
             mids = []
             for n in chunks:

@@ -7,12 +7,12 @@ timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q -k "one_pass" > 
 timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/${P}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${P}_pytest.log
 tail -3 gpurun_out/${P}_pytest.log
 timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/${P}_bench.json 2> gpurun_out/${P}_bench.err; echo "bench rc=$?"
-for v in "--no-one-pass" "--one-pass-march 16" "--one-pass-march 64"; do
+for v in "--one-pass" "--one-pass --one-pass-march 16" "--one-pass --one-pass-march 64"; do
   timeout 300 python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline --no-parity --quick $v 2>/dev/null | tail -1 >> gpurun_out/${P}_variants.jsonl
 done
 for w in c5 c2 c4s; do
   timeout 300 python bench.py --workload $w --steps 20 --warmup 3 --no-e2e --no-cpu-baseline --no-parity --quick 2>/dev/null | tail -1 >> gpurun_out/${P}_variants.jsonl
-  timeout 300 python bench.py --workload $w --steps 20 --warmup 3 --no-e2e --no-cpu-baseline --no-parity --quick --no-one-pass 2>/dev/null | tail -1 >> gpurun_out/${P}_variants.jsonl
+  timeout 300 python bench.py --workload $w --steps 20 --warmup 3 --no-e2e --no-cpu-baseline --no-parity --quick --one-pass 2>/dev/null | tail -1 >> gpurun_out/${P}_variants.jsonl
 done
 P=$P python - <<'PY'
 import json, os

@@ -3,7 +3,7 @@
 # usage: tools/sweep_kchunk.sh <workload> <one-pass: 0|1> k1 k2 ...   (run on the GPU box)
 w=$1; op=$2; shift 2
 for kc in "$@"; do
-  if [ "$op" = 1 ]; then flag="--one-pass-march $kc"; else flag="--march $kc --no-one-pass"; fi
+  if [ "$op" = 1 ]; then flag="--one-pass --one-pass-march $kc"; else flag="--march $kc"; fi
   python bench.py --workload $w --steps 20 --warmup 3 --no-e2e --no-cpu-baseline --no-parity --quick $flag 2>/dev/null | tail -1 | python -c "
 import json,sys
 d=json.loads(sys.stdin.read()); r=d['roofline']
