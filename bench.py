@@ -454,7 +454,7 @@ def main():
     env = (rank, world, local, dist, barrier, max_over_ranks)
     global TUNING
     if args.march or args.one_pass_march or args.one_pass:
-        TUNING = (args.march, args.one_pass_march, args.one_pass)
+        TUNING = (args.march, args.one_pass_march, True if args.one_pass else None)
     headline = args.workload == "c3" and args.exact == 0 and not args.quick and not (args.march or args.one_pass_march or args.one_pass)
 
     # ---- parity of the sharded path against the CPU oracle, before anything is timed

@@ -261,8 +261,9 @@ class Solver:
         _check(lib().fdtd_fused_time(self._h, C.byref(ms)))
         return ms.value
 
-    def set_tuning(self, march_planes=0, one_pass_march_planes=0, allow_one_pass=False):
-        _check(lib().fdtd_set_tuning(self._h, march_planes, one_pass_march_planes, int(allow_one_pass)))
+    def set_tuning(self, march_planes=0, one_pass_march_planes=0, allow_one_pass=None):
+        """allow_one_pass: True / False, or None = the library's default (complex double only)."""
+        _check(lib().fdtd_set_tuning(self._h, march_planes, one_pass_march_planes, -1 if allow_one_pass is None else int(allow_one_pass)))
 
     def sumsq(self, field):
         fid = FIELD_IDS[field] if isinstance(field, str) else field

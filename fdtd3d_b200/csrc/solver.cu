@@ -122,7 +122,8 @@ struct fdtd_solver
   TmaMaps3D tma_pp[2];  /* per parity, half-step kernels of the shell: E phase reads cur, H phase reads E of nxt */
   int fused_kc;         /* planes marched per CTA of the fused kernel; 0 = default rule */
   int kchunk_forced;    /* fdtd_set_tuning: planes marched per CTA of the half-step kernels; 0 = default rule */
-  bool fused_wanted;    /* fdtd_set_tuning: use the one-pass kernels where the geometry allows (off by default: slower) */
+  int fused_policy;     /* fdtd_set_tuning: 0 never, 1 wherever the geometry allows, -1 (default) where it was measured to
+                           pay: complex double */
   float prof_f_ms;
   bool use_tma;
   int kchunk;
@@ -490,7 +491,8 @@ static int configure_fused (fdtd_solver *s)
   if (rc) return rc;
   s->fused_ok = false;
   const bool tmz = s->cfg.dims == 2;
-  if (!s->core_on || (!tmz && !s->use_tma) || !s->fused_wanted) return FDTD_OK;
+  const bool wanted = s->fused_policy > 0 || (s->fused_policy < 0 && !tmz && s->nc == 2 && s->fp == 8);
+  if (!s->core_on || (!tmz && !s->use_tma) || !wanted) return FDTD_OK;
   if ((rc = normalize_parity (s))) return rc;
   int txc = 0, fty = 0, smem_q = 0, smem_base = 0, sty = 1;
   if (tmz) fused_tile_geometry_tmz (s->fp, s->nc, &txc, &fty, &smem_q, &smem_base);
@@ -1228,6 +1230,7 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   s->mat_vals = s->psM * (s->nzm + 2);
   s->ninc = cfg->use_tfsf ? 100LL * (s->nx + s->ny + (cfg->dims == 3 ? s->nzg : 0)) : 0;
   s->t = cfg->time_step_start;
+  s->fused_policy = -1;
   for (int a = 0; a < 3; ++a) s->sigma[a].assign ((size_t) (a < cfg->dims ? cfg->size[a] : 1) + 1, 0.0);
 
 #define CREATE_TRY(expr) \
@@ -1599,7 +1602,7 @@ int fdtd_set_tuning (fdtd_handle s, int march_planes, int one_pass_march_planes,
   if (rc) return rc;
   s->kchunk_forced = march_planes;
   s->fused_kc = one_pass_march_planes;
-  s->fused_wanted = allow_one_pass != 0;
+  s->fused_policy = allow_one_pass;
   if (s->cfg.dims == 2) s->kchunk = march_planes > 0 ? march_planes : 8;
   return configure_3d (s, true);
 }

@@ -206,12 +206,12 @@ int fdtd_get_time_step (fdtd_handle h, int64_t *t);
 int fdtd_get_core_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
 
 /*
- * One pass per time step in the core (experimental, OFF unless switched on with fdtd_set_tuning): instead of an E and
+ * One pass per time step in the core (by default only for complex double, where it was measured to pay): instead of an E and
  * an H half step, one kernel reads E and H once and writes them once inside a box that spans the whole x range, the
  * rows of the core box and its planes on this rank (12 instead of 18 field values per cell and step; exact_mode 0,
- * use_pml, homogeneous mu).  Results are bit-identical to the two half-step kernels.  On B200 it is currently SLOWER
- * than they are -- the fused instruction stream is latency-bound at the occupancy its registers allow (DESIGN.md 3.1c,
- * profiles/r2_one_pass.md) -- which is why it is not the default.  fdtd_get_fused_box: the box (global indices,
+ * use_pml, homogeneous mu).  Results are bit-identical to the two half-step kernels.  On B200 it is 6 % faster than
+ * they are for complex double but slower for real double and float -- the fused instruction stream is latency-bound at
+ * the occupancy its registers allow (profiles/r2_one_pass.md) -- hence the default.  fdtd_get_fused_box: the box (global indices,
  * inclusive; lo > hi when the kernel is not in use); fdtd_fused_time: summed device time of that kernel over the last
  * completed run, with fdtd_set_profiling on (fdtd_phase_times then returns the E and H half steps of the remaining
  * shell).  No reference counterpart.
@@ -220,8 +220,8 @@ int fdtd_get_fused_box (fdtd_handle h, int64_t lo[3], int64_t hi[3]);
 int fdtd_fused_time (fdtd_handle h, float *ms);
 
 /* Tuning aid, no reference counterpart: planes (2D: rows) marched per CTA by the half-step kernels and by the one-pass
- * kernel (0 = the library's rule), and whether the one-pass kernel is used where the geometry allows (0 = no, the
- * default; 1 = yes).  Results do not depend on any of it. */
+ * kernel (0 = the library's rule), and whether the one-pass kernel is used where the geometry allows (0 = never,
+ * 1 = always, -1 = the library's default: complex double only).  Results do not depend on any of it. */
 int fdtd_set_tuning (fdtd_handle h, int march_planes, int one_pass_march_planes, int allow_one_pass);
 
 /* The same box for a configuration and sigma profiles (FPValue arrays of size[a] + 1 values, NULL = all zero) without
