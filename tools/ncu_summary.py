@@ -44,7 +44,7 @@ def main():
     js = json.load(open(js_path)) if os.path.exists(js_path) else {}
     for r in rows[2:]:
         name = r[hdr.index("Kernel Name")]
-        short = re.search(r"([eh]z?_phase_\w+)", name)
+        short = re.search(r"([eh]z?_phase_\w+|step_core_\w+)", name)
         short = short.group(1) if short else name[:40]
         lines += ["## `%s`" % name, "", "| metric | value |", "|---|---|"]
         dram = 0.0
@@ -59,8 +59,10 @@ def main():
         base = short.replace("_tma", "")
         targs = re.search(r"<(.*?)>\(", name)
         targ = [a.strip() for a in targs.group(1).split(",")] if targs else []
-        if len(targ) >= 6 and targ[5] in ("1", "(bool)1", "true"):  # <T, NC, PML, TFSF, EXACT, CORE[, UNIMU]>
+        if "phase" in base and len(targ) >= 6 and targ[5] in ("1", "(bool)1", "true"):  # <T, NC, PML, TFSF, EXACT, CORE[, UNIMU]>
             base += "_core"  # the variants that skip D/B in the sigma-free core
+        if len(sys.argv) > 3:
+            base = sys.argv[3] + base  # e.g. "c4s_": a capture of another workload must not replace the headline's entry
         js[base] = {"dram_bytes_per_launch": dram, "tag": tag, "kernel": name}
     open(os.path.join(ROOT, "profiles", tag + "_ncu_summary.md"), "w").write("\n".join(lines))
     json.dump(js, open(js_path, "w"), indent=1)
