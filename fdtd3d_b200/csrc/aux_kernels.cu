@@ -23,7 +23,7 @@ __global__ void incident_e (const StepParams<T> p)
   if (i >= p.ninc) return;
   if (i == 0)
   {
-    const long long s = p.step;
+    const long long s = current_step (p);
 #pragma unroll
     for (int c = 0; c < NC; ++c) p.einc[c] = p.src[s * NC + c];
     return;

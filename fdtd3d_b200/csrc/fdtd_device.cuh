@@ -63,6 +63,9 @@ struct StepParams
   long long face_stride; /* cells per table */
   const T *src;         /* source samples for the steps of the current run, one cell per step */
   long long step;       /* index into src of the step being computed (set per launch by the time loop) */
+  long long *step_ptr;  /* when not NULL the index is read from here instead (and advanced by the H half-step kernel): every
+                           step's launches then have identical parameters, so one captured step can be replayed as a
+                           CUDA graph (launch-bound grids; solver.cu, run_graph) */
   long long ninc;       /* cells in einc / hinc */
 
   int nx, ny;           /* global x/y size */
@@ -88,6 +91,19 @@ struct StepParams
   T proj_e[3], proj_h[3]; /* proj_h[2] carries the leading minus of getHzFromIncidentH */
   double cphi, sphi;      /* TMz: cos / sin of incidentWaveAngle */
 };
+
+/* the index of the step being computed (StepParams::step / step_ptr) */
+template <typename T>
+__device__ __forceinline__ long long current_step (const StepParams<T> &p)
+{
+  return p.step_ptr ? *reinterpret_cast<const volatile long long *> (p.step_ptr) : p.step;
+}
+/* called by one thread of the H half-step kernel: the next step's kernels start after this kernel has ended */
+template <typename T>
+__device__ __forceinline__ void advance_step (const StepParams<T> &p)
+{
+  if (p.step_ptr) *p.step_ptr += 1;
+}
 
 /* vector of W scalars moved with one 4-, 8- or 16-byte access */
 template <typename T, int W>

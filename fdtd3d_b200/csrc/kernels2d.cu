@@ -91,7 +91,7 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
 
   FVec hx_jm = ldv<T, W> (Hx + o - row);
   long long step = 0;
-  if (!TFSF) step = p.step;
+  if (!TFSF) step = current_step (p);
   const bool x_core = CORE && i0 >= p.core_lo[0] && i0 + V - 1 <= p.core_hi[0];
 
   for (int j = j0; j < j1; ++j, o += row, om += p.pitchM)
@@ -246,6 +246,7 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) advance_step (p); /* nobody reads it in this half step */
   const int i0 = (blockIdx.x * TX + threadIdx.x) * V;
   if (i0 >= p.nx) return;
   int j0, j1;

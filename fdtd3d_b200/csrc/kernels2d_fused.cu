@@ -165,7 +165,7 @@ step_core_tmz_fused (const __grid_constant__ StepParams<T> p, const __grid_const
   const T mod_h = p.mu_const * p.mu0; /* homogeneous mu: (m + m) / 2 is m exactly */
   const T cb_h = plain_coef<T, false> (mod_h, p);
   long long step = 0;
-  if (!TFSF) step = p.step;
+  if (!TFSF) step = current_step (p);
 
   const int xo = lx * 16;
   const int oA = L::OFF_A + ly * L::RW_A + 16 + xo;

@@ -289,7 +289,7 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
   const T cb_h = dt_dx * rcp_t<T> (p.mu_const * p.mu0); /* homogeneous mu: (m + m) / 2 is m exactly */
 
   long long step = 0;
-  if (!TFSF) step = p.step;
+  if (!TFSF) step = current_step (p);
   const bool src_row = !TFSF && j == p.srcpos[1] && p.srcpos[0] >= i0 && p.srcpos[0] < i0 + V;
 
   /* byte offsets of this thread's operands inside a stage / an exchange buffer */

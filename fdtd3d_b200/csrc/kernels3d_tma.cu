@@ -307,7 +307,7 @@ e_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   }
 
   long long step = 0;
-  if (!TFSF) step = p.step;
+  if (!TFSF) step = current_step (p);
 
   /* per-thread byte offsets inside a stage */
   const int xo = tx * 16;
@@ -506,6 +506,8 @@ h_phase_3d_tma (const __grid_constant__ StepParams<T> p, const __grid_constant__
   if (!cta_work<L> (p, kb, ke, i0t, j0t, k0, k1)) return; /* uniform over the CTA */
   const int i0 = i0t + tx * V, j = j0t + ty;
   const bool active = i0 < p.nx && j < p.ny;
+
+  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && leader) advance_step (p); /* nobody reads it in this half step */
 
   int qmask_full = 0, qmask_core = 0; /* see e_phase_3d_tma */
   if (CORE) quarter_masks<L> (p, i0t, j0t, qmask_full, qmask_core);

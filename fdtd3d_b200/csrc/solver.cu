@@ -122,6 +122,13 @@ struct fdtd_solver
   TmaMaps3D tma_pp[2];  /* per parity, half-step kernels of the shell: E phase reads cur, H phase reads E of nxt */
   int fused_kc;         /* planes marched per CTA of the fused kernel; 0 = default rule */
   int kchunk_forced;    /* fdtd_set_tuning: planes marched per CTA of the half-step kernels; 0 = default rule */
+  /* launch-bound grids: one step captured as a CUDA graph and replayed (run_graph); the step index then lives in
+   * device memory (StepParams::step_ptr).  Any change of what a step launches invalidates the captured graph. */
+  long long *step_dev;
+  cudaGraphExec_t step_graph;
+  void *step_graph_src;   /* the source table the captured launches point at */
+  bool step_graph_prof;
+  int step_graph_launches;
   int fused_policy;     /* fdtd_set_tuning: 0 never, 1 wherever the geometry allows, -1 (default) where it was measured to
                            pay: complex double */
   float prof_f_ms;
@@ -182,6 +189,7 @@ static StepParams<T> make_params (const fdtd_solver *s)
   p.face_stride = s->face_stride;
   p.src = (const T *) s->src;
   p.step = 0;
+  p.step_ptr = NULL;
   p.ninc = s->ninc;
   p.nx = s->nx; p.ny = s->ny; p.nzl = s->nzl; p.kz0 = s->kz0; p.nzg = s->nzg;
   p.pitch = s->pitch; p.pitchM = s->pitchM; p.ps = s->ps; p.psM = s->psM;
@@ -431,8 +439,16 @@ static int configure_fused (fdtd_solver *s);
 static int normalize_parity (fdtd_solver *s);
 static int release_dq (fdtd_solver *s);
 
+/* what a step launches has changed: a captured step is stale */
+static void drop_step_graph (fdtd_solver *s)
+{
+  if (s->step_graph) cudaGraphExecDestroy (s->step_graph);
+  s->step_graph = NULL;
+}
+
 static int configure_3d (fdtd_solver *s, bool first)
 {
+  drop_step_graph (s);
   if (s->cfg.dims != 3) return configure_fused (s); /* TMz: direct-load half-step kernels, no tensor maps of their own */
   const bool alt = s->cfg.exact_mode == 1 || s->core_on;
   int rc0 = normalize_parity (s); /* the maps below describe the first allocation */
@@ -714,6 +730,51 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     int rc = exchange (s, true, s->f);
     if (rc) return rc;
     CUDA_TRY (cudaEventRecord (s->ev_hx, C));
+  }
+
+  /* Small grids are launch-bound (c1: six launches of 5-25 us per step; TMz 4096^2: two of 50 us): there one step is
+   * captured as a CUDA graph and replayed, which takes the per-launch overhead out of the stream.  All steps must then
+   * launch identical parameters, so the step index is read from device memory and advanced by the H kernel. */
+  const long long cells_rank = (long long) s->nx * s->ny * s->nzl;
+  if (!multi && !prof && nsteps >= 8 && (c.dims == 2 || cells_rank <= (4LL << 20)) && s->step_dev)
+  {
+    p.step_ptr = s->step_dev;
+    CUDA_TRY (cudaMemsetAsync (s->step_dev, 0, sizeof (long long), S));
+    auto one_step = [&] () -> int
+    {
+      int nl = 0;
+      if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, exact, S)); ++nl; }
+      if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (true, p, cplx, S)); ++nl; }
+      if (c.dims == 2) CUDA_TRY (launch_phase_tmz<T> (true, p, cplx, pml, tfsf, exact, s->core_on, s->eps_uniform, S));
+      else CUDA_TRY (phase_3d<T> (s, true, p, 0, s->nzl, S));
+      if (tfsf) { CUDA_TRY (launch_incident<T> (false, p, cplx, exact, S)); ++nl; }
+      if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (false, p, cplx, S)); ++nl; }
+      if (c.dims == 2) CUDA_TRY (launch_phase_tmz<T> (false, p, cplx, pml, tfsf, exact, s->core_on, s->mu_uniform, S));
+      else CUDA_TRY (phase_3d<T> (s, false, p, 0, s->nzl, S));
+      s->step_graph_launches = nl + 2;
+      return FDTD_OK;
+    };
+    /* the first step runs as plain launches (first-use set-up of the kernels happens outside a capture) */
+    int rc = one_step ();
+    if (rc) return rc;
+    s->launches += s->step_graph_launches;
+    if (!s->step_graph || s->step_graph_src != s->src)
+    {
+      if (s->step_graph) { cudaGraphExecDestroy (s->step_graph); s->step_graph = NULL; }
+      cudaGraph_t g = NULL;
+      CUDA_TRY (cudaStreamBeginCapture (S, cudaStreamCaptureModeThreadLocal));
+      rc = one_step ();
+      cudaError_t ce = cudaStreamEndCapture (S, &g);
+      if (rc) { if (g) cudaGraphDestroy (g); return rc; }
+      if (ce != cudaSuccess) return fail (FDTD_ERROR, "capturing a time step failed: %s", cudaGetErrorString (ce));
+      ce = cudaGraphInstantiate (&s->step_graph, g, 0);
+      cudaGraphDestroy (g);
+      if (ce != cudaSuccess) { s->step_graph = NULL; return fail (FDTD_ERROR, "cudaGraphInstantiate failed: %s", cudaGetErrorString (ce)); }
+      s->step_graph_src = s->src;
+    }
+    for (long long n = 1; n < nsteps; ++n) CUDA_TRY (cudaGraphLaunch (s->step_graph, S));
+    s->launches += (nsteps - 1) * s->step_graph_launches;
+    return FDTD_OK;
   }
 
   for (long long n = 0; n < nsteps; ++n)
@@ -1053,6 +1114,7 @@ static int transfer (fdtd_solver *s, int field, void *host, int order, long long
   if (rc) return rc;
   if (to_device && field == FDTD_MU) s->mu_uniform = false;
   if (to_device && field == FDTD_EPS) s->eps_uniform = false;
+  if (to_device && (field == FDTD_MU || field == FDTD_EPS)) drop_step_graph (s);
   /* uploads of anything the folded representation depends on, and reads of D / B, need the plain arrays */
   if (!fi.is_inc && (to_device || (field >= FDTD_DX && field <= FDTD_BZ)) && (rc = ensure_unfolded (s))) return rc;
   cudaStream_t S = s->s_compute;
@@ -1279,6 +1341,7 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   CREATE_TRY (cudaMalloc (&s->staging, s->staging_bytes));
   CREATE_TRY (cudaMalloc ((void **) &s->red_partials, sizeof (double) * (size_t) sumsq_partial_count ()));
   CREATE_TRY (cudaMalloc ((void **) &s->red_out, sizeof (double)));
+  CREATE_TRY (cudaMalloc ((void **) &s->step_dev, sizeof (long long)));
 #undef CREATE_TRY
 
   for (int i = 0; i < 6; ++i) s->fA[i] = s->f[i];
@@ -1338,7 +1401,8 @@ int fdtd_destroy (fdtd_handle s)
   for (int f = 0; f < 6; ++f) { if (s->fA[f]) s->f[f] = s->fA[f]; if (s->fB[f]) cudaFree (s->fB[f]); }
   for (int d = 0; d < 2; ++d) for (int a = 0; a < 3; ++a) if (s->dq[d][a]) cudaFree (s->dq[d][a]);
   for (int f = 0; f < 12; ++f) if (s->f[f]) cudaFree (s->f[f]);
-  void *ptrs[] = { s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->staging, s->red_partials, s->red_out };
+  drop_step_graph (s);
+  void *ptrs[] = { s->step_dev, s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->staging, s->red_partials, s->red_out };
   for (void *p : ptrs) if (p) cudaFree (p);
   cudaEvent_t evs[] = { s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx };
   for (cudaEvent_t e : evs) if (e) cudaEventDestroy (e);
@@ -1409,6 +1473,7 @@ int fdtd_fill (fdtd_handle s, int field, double re, double im)
     const double v = s->fp == 4 ? (double) (float) re : re;
     if (field == FDTD_MU) { s->mu_uniform = true; s->mu_value = v; }
     else { s->eps_uniform = true; s->eps_value = v; }
+    drop_step_graph (s);
   }
   CUDA_TRY (launch_fill (fi.dev, count, fi.cell, pat, s->s_compute));
   s->launches++;
@@ -1425,6 +1490,7 @@ int fdtd_init_eps_sphere (fdtd_handle s, double cx, double cy, double cz, double
   if (rc) return rc;
   if ((rc = ensure_unfolded (s))) return rc;
   s->eps_uniform = false;
+  drop_step_graph (s);
   if (s->fp == 4)
     CUDA_TRY (launch_eps_sphere<float> ((float *) s->eps, s->nx + 1, s->ny + 1, s->nzm, s->kz0, s->pitchM, s->psM, (float) cx, (float) cy, (float) cz, (float) radius, (float) eps_inside, s->s_compute));
   else
