@@ -96,7 +96,11 @@ struct StepParams
 template <typename T>
 __device__ __forceinline__ long long current_step (const StepParams<T> &p)
 {
-  return p.step_ptr ? *reinterpret_cast<const volatile long long *> (p.step_ptr) : p.step;
+  /* written as a separate global load: as `cond ? *ptr : p.step` the compiler selected between the two ADDRESSES and
+   * loaded p.step through a generic pointer into the kernel's parameter space, which faults */
+  long long s = p.step;
+  if (p.step_ptr) asm volatile ("ld.volatile.global.s64 %0, [%1];" : "=l"(s) : "l"(p.step_ptr));
+  return s;
 }
 /* called by one thread of the H half-step kernel: the next step's kernels start after this kernel has ended */
 template <typename T>
