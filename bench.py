@@ -290,10 +290,11 @@ def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False,
     s.run(warmup)
     barrier()
     launches0 = s.launch_count
-    # 3D: the per-kernel CUDA events are recorded inside the timed region (4 events per 3.6 ms step).  2D TMz: a step is
-    # two 50-microsecond launches, where 4 events per step would be measured themselves -- the timed region runs without
+    # Large 3D grids: the per-kernel CUDA events are recorded inside the timed region (4 events per 3.6 ms step).  2D TMz
+    # and small 3D grids are launch-bound (a step is a few launches of 5-50 microseconds, replayed as a CUDA graph): there
+    # 4 events per step would be measured themselves and would switch the graph off, so the timed region runs without
     # them and the same K steps are repeated right afterwards with events for the per-kernel times.
-    prof_inline = w["dims"] == 3
+    prof_inline = w["dims"] == 3 and w["nx"] * w["ny"] * (nz_total // world) > (4 << 20)  # small 3D grids: as TMz
     if prof_inline:
         s.set_profiling(True)
     sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
