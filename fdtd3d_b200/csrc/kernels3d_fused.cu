@@ -568,401 +568,6 @@ step_core_3d_fused (const __grid_constant__ StepParams<T> p, const __grid_consta
 #undef SM1
 }
 
-/* ------------------------------------------------------------------ the same step, one warp per row AND component */
-
-/*
- * step_core_3d_comp: the one-pass step with the arithmetic of a tile row split over three warps, one per field component
- * (x, y, z).  step_core_3d_fused above keeps all six components of a cell in one thread: 170-200 registers, 10 warps per
- * SM, and measured latency-bound (profiles/r2_one_pass.md).  Here a thread owns ONE component of its cells -- E'_a in
- * the first phase of a plane, H'_a of the plane below in the second -- which takes a third of the state (<= 72
- * registers) and gives 28 warps per SM with the same tiles, stages and TMA traffic:
- *
- *   E'_a = E_a + cb_a (H_c - H_c[-e_b] - H_b + H_b[-e_c]),   H'_a = H_a + cb_h (E'_b[+e_c] - E'_b - E'_c[+e_b] + E'_c),
- *   (a, b, c) a cyclic permutation of (x, y, z); cb_a from eps averaged along a.
- *
- * Everything a thread needs of the OTHER components comes from shared memory: H from the TMA stage, E' from the
- * exchange ring -- three slots now, because the second phase of plane k (which reads E'(k) and E'(k-1)) is separated
- * from the first phase of plane k+1 (which writes E'(k+1)) by no barrier; one __syncthreads per plane as before.
- * Warps: 3 per tile row (comps x, y, z), 2 for the rim row (x, z: what H'z and H'x of the last row need), 2 for the
- * rim column (y, z: lane = row).  Same box, ping-pong buffers, D pair and shell launches as the kernel above.
- */
-template <typename T, int NC>
-struct CTile : FTile<T, NC>
-{
-  typedef FTile<T, NC> B;
-  static constexpr int NWARPS = 3 * B::TY + 4;
-  static constexpr int NTHREADS = 32 * NWARPS;
-  static constexpr int XSLOTS = 3;
-  __host__ __device__ static constexpr int smem_bytes (int nq) { return B::STAGES * B::stage_bytes (nq) + XSLOTS * B::X_BYTES + 128; }
-};
-
-template <typename T, int NC, bool TFSF, int A>
-__device__ __forceinline__ void comp_role (const StepParams<T> &p, const FusedSet &maps, const FusedBox &fb, unsigned char *smem_raw,
-                                           unsigned long long *full, int lx, int ly, bool valid, bool leader)
-{
-  typedef CTile<T, NC> L;
-  constexpr int V = L::V, W = V * NC, S = L::STAGES, TY = L::TY;
-  constexpr int Bc = (A + 1) % 3, Cc = (A + 2) % 3;   /* the other two components, cyclic */
-  typedef Vec<T, W> FVec;
-  typedef Vec<T, V> MVec;
-
-  const unsigned sbase = smem_u32 (smem_raw);
-  const int sm0 = (int) ((128u - (sbase & 127u)) & 127u);
-  const int stage_sz = L::stage_bytes (fb.nq);
-  const int xbuf0 = sm0 + S * stage_sz;
-
-  const int i0t = blockIdx.x * L::TXC, j0t = fb.fy0 + blockIdx.y * TY;
-  const int k0 = fb.fz0 + blockIdx.z * fb.kc;
-  const int k1 = min (k0 + fb.kc, fb.fz1 + 1);
-  const int i0 = i0t + lx * V, j = j0t + ly;
-  const bool ingrid = valid && i0 < p.nx && j < p.ny;
-  const bool own = lx < 32 && ly < TY && ingrid;
-  const bool rim_from_nxt = ly == TY && j0t + TY > fb.fy1;
-  const bool top_from_nxt = k1 > fb.fz1;
-  const bool compute_e = ingrid && !rim_from_nxt;
-
-  int qmask = 0;
-#pragma unroll
-  for (int q = 0; q < 4; ++q)
-  {
-    const int qa = i0t + q * L::QX, qb = qa + L::QX - 1;
-    if (qa < p.nx && !(qa >= p.core_lo[0] && qb <= p.core_hi[0])) qmask |= 1 << q;
-  }
-  const int myq = lx >> 3;
-  const bool shell = lx < 32 && ((qmask >> myq) & 1);
-  const int qrank = __popc (qmask & ((1 << myq) - 1));
-  auto compact_q = [&] (int q) -> int
-  {
-    const int gq = i0t / L::QX + q;
-    return gq < fb.nlo ? gq : fb.nlo + gq - fb.hq0;
-  };
-
-  auto issue = [&] (int slot, int k)
-  {
-    unsigned char *base = smem_raw + sm0 + slot * stage_sz;
-    unsigned long long *bar = &full[slot];
-    mbar_expect_tx (bar, L::TX_BASE + __popc (qmask) * 3 * (L::SZ_QD + L::SZ_QB));
-    tma_load_3d (base + L::OFF_A, &maps.m[0], bar, (i0t - V) * NC, j0t - 1, k + 1);
-    tma_load_3d (base + L::OFF_B, &maps.m[1], bar, (i0t - V) * NC, j0t, k + 1);
-    tma_load_3d (base + L::OFF_C, &maps.m[2], bar, i0t * NC, j0t - 1, k + 1);
-#pragma unroll
-    for (int a = 0; a < 3; ++a) tma_load_3d (base + L::OFF_E + a * L::E_STRIDE, &maps.m[3 + a], bar, i0t * NC, j0t, k + 1);
-    tma_load_3d (base + L::OFF_M, &maps.m[6], bar, i0t, j0t, k + 2);
-    if (qmask)
-    {
-      int r = 0;
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        if ((qmask >> q) & 1)
-        {
-#pragma unroll
-          for (int a = 0; a < 3; ++a)
-          {
-            tma_load_3d (base + L::OFF_Q + (a * fb.nq + r) * L::SZ_QD, &maps.m[7 + a], bar, compact_q (q) * L::QX * NC, j0t, k + 1);
-            tma_load_3d (base + L::OFF_Q + 3 * fb.nq * L::SZ_QD + (a * fb.nq + r) * L::SZ_QB, &maps.m[10 + a], bar,
-                         (i0t + q * L::QX) * NC, j0t, k);
-          }
-          ++r;
-        }
-    }
-  };
-  if (leader)
-  {
-    for (int s = 0; s < S && k0 + s <= k1; ++s) issue (s, k0 + s);
-  }
-
-  long long o = (((long long) (k0 + 1) * p.ny + j) * p.pitch + i0) * NC;
-  const long long pl = p.ps * NC;
-  const long long om = ((long long) (k0 + 1) * (p.ny + 1) + j) * p.pitchM + i0;
-
-  /* x parts of the update ranges (only the absorber lanes at the x ends of the grid can be outside them) and TF/SF face
-   * candidates, as bit masks over the cells of this thread's vector */
-  int ilo_m = 0, ihi_m = 0, ife_m = 0, ifh_m = 0;
-#pragma unroll
-  for (int v = 0; v < V; ++v)
-  {
-    const int i = i0 + v;
-    if (i >= 1) ilo_m |= 1 << v;
-    if (i < p.nx - 1) ihi_m |= 1 << v;
-    if (TFSF && tfsf_axis_hit (p, 0, i, true)) ife_m |= 1 << v;
-    if (TFSF && tfsf_axis_hit (p, 0, i, false)) ifh_m |= 1 << v;
-  }
-  const int e_do_m = A == 0 ? ihi_m : ilo_m, h_do_m = A == 0 ? ilo_m : ihi_m;
-  const bool j_face_e = TFSF && tfsf_axis_hit (p, 1, j, true);
-  const bool j_face_h = TFSF && tfsf_axis_hit (p, 1, j, false);
-  const T eps0 = p.eps0, dt_dx = p.dt_dx;
-  const T cb_h = dt_dx * rcp_t<T> (p.mu_const * p.mu0);
-
-  /* plane-carried: the z-shifted H operand of E'_a (a = x: Hy, a = y: Hx), the own H_a of the plane below (start value
-   * of H'_a), the material of this plane (and its +x / +y neighbour where the component averages along x / y) */
-  FVec hz_km = {};            /* "H shifted along z": Hy(k-1) for a = x, Hx(k-1) for a = y; unused for a = z */
-  FVec h_own_m = {};          /* H_a (k-1) */
-  MVec eps_c = {}, eps_n = {};/* eps (k); a = y: eps (j+1, k) */
-  T eps_ip = 0;               /* a = x: eps (i + V, k) */
-  if (ingrid)
-  {
-    if (A == 0) hz_km = ldv<T, W> (p.f[4] + o - pl);
-    if (A == 1) hz_km = ldv<T, W> (p.f[3] + o - pl);
-    eps_c = ldv<T, V> (p.eps + om);
-    if (A == 1) eps_n = ldv<T, V> (p.eps + om + p.pitchM);
-    if (A == 0) eps_ip = __ldg (p.eps + om + V);
-  }
-  long long step = 0;
-  if (!TFSF) step = current_step (p);
-  const bool src_row = !TFSF && A == 2 && j == p.srcpos[1] && p.srcpos[0] >= i0 && p.srcpos[0] < i0 + V;
-
-  const int xo = lx * 16;
-  const int oA_own = L::OFF_A + (ly + 1) * L::RW_A + 16 + xo, oA_jm = L::OFF_A + ly * L::RW_A + 16 + xo;   /* Hz */
-  const int oB_own = L::OFF_B + ly * L::RW_A + 16 + xo;                                                     /* Hy */
-  const int oC_own = L::OFF_C + (ly + 1) * L::RW_C + xo, oC_jm = L::OFF_C + ly * L::RW_C + xo;              /* Hx */
-  const int oE = L::OFF_E + A * L::E_STRIDE + ly * L::RW_C + xo;
-  const int oM = L::OFF_M + ly * L::RW_M + lx * V * (int) sizeof (T);
-  const int oQD = L::OFF_Q + (A * fb.nq + qrank) * L::SZ_QD + ly * 128 + (lx & 7) * 16;
-  const int oX = ly * L::RW_C + xo;
-
-  int slot = 0, st = sm0;
-  unsigned phase = 0;
-  int xs = 0;                 /* exchange slot of plane k; (xs + 2) % 3 is the slot of plane k - 1 */
-
-#define SMV(W_, off) lds_s<T, W_> (sbase + (unsigned) (off))
-#define SM1(off) (lds_s<T, 1> (sbase + (unsigned) (off)).v[0])
-
-  for (int k = k0; k <= k1; ++k, o += pl)
-  {
-    mbar_wait (&full[slot], phase);
-    const int gk = p.kz0 + k;
-
-    /* ---------------- phase 1: E'_a (k) at this thread's position.  hc / hb: the two H components of the curl, hcs /
-     * hbs: the same one cell down along b / c */
-    FVec hc, hcs, hb, hbs, h_own;
-    if (A == 0)
-    {
-      hc = SMV (W, st + oA_own); hcs = SMV (W, st + oA_jm); hb = SMV (W, st + oB_own); hbs = hz_km;
-      h_own = SMV (W, st + oC_own);
-    }
-    else if (A == 1)
-    {
-      hc = SMV (W, st + oC_own); hcs = hz_km; hb = SMV (W, st + oA_own);
-      h_own = SMV (W, st + oB_own);
-#pragma unroll
-      for (int s = 0; s < W; ++s) hbs.v[s] = s >= NC ? hb.v[s >= NC ? s - NC : s] : SM1 (st + oA_own - L::CELL + s * (int) sizeof (T));
-    }
-    else
-    {
-      hc = SMV (W, st + oB_own); hb = SMV (W, st + oC_own); hbs = SMV (W, st + oC_jm);
-      h_own = SMV (W, st + oA_own);
-#pragma unroll
-      for (int s = 0; s < W; ++s) hcs.v[s] = s >= NC ? hc.v[s >= NC ? s - NC : s] : SM1 (st + oB_own - L::CELL + s * (int) sizeof (T));
-    }
-    FVec e = SMV (W, st + oE);
-    const MVec eps_kp = SMV (V, st + oM);
-    MVec eps_n_next = {};
-    T eps_ip_next = 0;
-    if (A == 1) eps_n_next = SMV (V, st + oM + L::RW_M);
-    if (A == 0) eps_ip_next = SM1 (st + oM + V * (int) sizeof (T));
-    FVec bq = {};               /* B_a (k-1) of an absorber lane: staged with plane k, needed after the barrier */
-    if (shell && own && k > k0) bq = SMV (W, st + L::OFF_Q + 3 * fb.nq * L::SZ_QD + (A * fb.nq + qrank) * L::SZ_QB + ly * 128 + (lx & 7) * 16);
-
-    if (compute_e && !(k == k1 && top_from_nxt))
-    {
-      const int face_m = !TFSF ? 0 : ((j_face_e || tfsf_axis_hit (p, 2, gk, true)) ? (1 << V) - 1 : ife_m);
-      FVec d;
-      if (shell) d = SMV (W, st + oQD);
-#pragma unroll
-      for (int v = 0; v < V; ++v)
-      {
-        const int i = i0 + v;
-        T curl[NC];
-#pragma unroll
-        for (int c = 0; c < NC; ++c)
-        {
-          const int s = v * NC + c;
-          curl[c] = hc.v[s] - hcs.v[s] - hb.v[s] + hbs.v[s];
-        }
-        if (TFSF && ((face_m >> v) & 1))
-        {
-          const int f = tfsf_e_faces (p, A, i, j, gk);
-          if (f)
-          {
-#pragma unroll
-            for (int c = 0; c < NC; ++c)
-            {
-              const int s = v * NC + c;
-              curl[c] = tfsf_curl_tab<T, NC, true> (p, A, f, c, i, j, k, hc.v[s], hcs.v[s], hb.v[s], hbs.v[s]);
-            }
-          }
-        }
-        const T e_c = eps_c.v[v];
-        const T e_o = A == 0 ? (v + 1 < V ? eps_c.v[v + 1 < V ? v + 1 : v] : eps_ip) : (A == 1 ? eps_n.v[v] : eps_kp.v[v]);
-        const T mod = ((e_c + e_o) / (T) 2) * eps0;
-        if (shell)
-        {
-          /* x absorber lanes: UPML form of component a (coefficients from the tables, as e_phase_3d_tma) */
-          const int pos[3] = { i, j, gk };
-          T cb3, cc3;
-          sweep3_coefs<T, false> (p.tab[A][KIND_BTW].p[pos[A]], p.tab[A][KIND_BTW].m[pos[A]], p.tab[Cc][KIND_AT].invp[pos[Cc]], mod, cb3, cc3);
-          const T ca1 = p.tab[Bc][KIND_AT].ca[pos[Bc]], cb1 = p.tab[Bc][KIND_AT].cbd[pos[Bc]], ca3 = p.tab[Cc][KIND_AT].ca[pos[Cc]];
-          if ((e_do_m >> v) & 1)
-          {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) upml_cell<T, false> (d.v[v * NC + c], e.v[v * NC + c], curl[c], ca1, cb1, ca3, cb3, cc3);
-          }
-        }
-        else
-        {
-          const T cb = dt_dx * rcp_t<T> (mod);
-#pragma unroll
-          for (int c = 0; c < NC; ++c) e.v[v * NC + c] = fma_t<T> (cb, curl[c], e.v[v * NC + c]);
-        }
-        if (A == 2 && !TFSF && src_row && gk == p.srcpos[2] && i == p.srcpos[0])
-        {
-          /* the source overwrites Ez but not Dz (Scheme3D.cpp:1995-2024); see e_phase_3d_tma */
-          if (!shell && own && k < k1)
-          {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) p.f[8][o + v * NC + c] = fma_t<T> (p.tab[0][KIND_AT].cbd[i], curl[c], p.f[8][o + v * NC + c]);
-          }
-#pragma unroll
-          for (int c = 0; c < NC; ++c) e.v[v * NC + c] = p.src[step * NC + c];
-        }
-      }
-      if (own && k < k1)
-      {
-        stv<T, W> (p.fo[A] + o, e);
-        if (shell)
-        {
-          const long long od = ((((long long) (k + 1) * p.ny + j) * fb.dq_pitch) + compact_q (myq) * L::QX + (lx & 7) * V) * NC;
-          stv<T, W> ((T *) fb.dq_out[A] + od, d);
-        }
-      }
-    }
-    else if (ingrid) e = ldv_rw<T, W> (p.fo[A] + o); /* outside the box: E' as the E shell pass wrote it */
-
-    if (valid) sts_s<T, W> (sbase + (unsigned) (xbuf0 + xs * L::X_BYTES + A * L::E_STRIDE + oX), e);
-    if (A == 0) hz_km = hb;
-    if (A == 1) hz_km = hc;
-    eps_c = eps_kp; eps_n = eps_n_next; eps_ip = eps_ip_next;
-
-    /* E' (k) of all components is in the exchange slot; every thread has read the stage: refill it */
-    __syncthreads ();
-    if (leader && k + S <= k1) issue (slot, k + S);
-
-    /* ---------------- phase 2: H'_a (k-1) of the tile's own cells: eb / ec are E'_b, E'_c of plane k-1, ebp / ecp the
-     * same one cell up along c / b (ebp or ecp is in plane k where that direction is z) */
-    if (k > k0 && own)
-    {
-      const int m = k - 1, gm = gk - 1;
-      const int xm = xbuf0 + (xs == 0 ? 2 : xs - 1) * L::X_BYTES + oX, xk = xbuf0 + xs * L::X_BYTES + oX;
-      FVec eb, ebp, ec, ecp;
-      if (A == 0)
-      {
-        eb = SMV (W, xm + 1 * L::E_STRIDE); ebp = SMV (W, xk + 1 * L::E_STRIDE);
-        ec = SMV (W, xm + 2 * L::E_STRIDE); ecp = SMV (W, xm + 2 * L::E_STRIDE + L::RW_C);
-      }
-      else if (A == 1)
-      {
-        eb = SMV (W, xm + 2 * L::E_STRIDE);
-        ec = SMV (W, xm + 0 * L::E_STRIDE); ecp = SMV (W, xk + 0 * L::E_STRIDE);
-#pragma unroll
-        for (int s = 0; s < W; ++s) ebp.v[s] = s + NC < W ? eb.v[s + NC < W ? s + NC : s] : SM1 (xm + 2 * L::E_STRIDE + 16 + (s + NC - W) * (int) sizeof (T));
-      }
-      else
-      {
-        eb = SMV (W, xm + 0 * L::E_STRIDE); ebp = SMV (W, xm + 0 * L::E_STRIDE + L::RW_C);
-        ec = SMV (W, xm + 1 * L::E_STRIDE);
-#pragma unroll
-        for (int s = 0; s < W; ++s) ecp.v[s] = s + NC < W ? ec.v[s + NC < W ? s + NC : s] : SM1 (xm + 1 * L::E_STRIDE + 16 + (s + NC - W) * (int) sizeof (T));
-      }
-      const int face_m = !TFSF ? 0 : ((j_face_h || tfsf_axis_hit (p, 2, gm, false)) ? (1 << V) - 1 : ifh_m);
-      FVec hn = h_own_m;
-#pragma unroll
-      for (int v = 0; v < V; ++v)
-      {
-        const int i = i0 + v;
-        T curl[NC];
-#pragma unroll
-        for (int c = 0; c < NC; ++c)
-        {
-          const int s = v * NC + c;
-          curl[c] = ebp.v[s] - eb.v[s] - ecp.v[s] + ec.v[s];
-        }
-        if (TFSF && ((face_m >> v) & 1))
-        {
-          const int f = tfsf_h_faces (p, A, i, j, gm);
-          if (f)
-          {
-#pragma unroll
-            for (int c = 0; c < NC; ++c)
-            {
-              const int s = v * NC + c;
-              curl[c] = tfsf_curl_tab<T, NC, false> (p, A, f, c, i, j, m, ebp.v[s], eb.v[s], ecp.v[s], ec.v[s]);
-            }
-          }
-        }
-        if (shell)
-        {
-          const int pos[3] = { i, j, gm };
-          const T mod = p.mu_const * p.mu0;
-          T cb3, cc3;
-          sweep3_coefs<T, false> (p.tab[A][KIND_AT].p[pos[A]], p.tab[A][KIND_AT].m[pos[A]], p.tab[Cc][KIND_BTW].invp[pos[Cc]], mod, cb3, cc3);
-          const T ca1 = p.tab[Bc][KIND_BTW].ca[pos[Bc]], cb1 = p.tab[Bc][KIND_BTW].cbd[pos[Bc]], ca3 = p.tab[Cc][KIND_BTW].ca[pos[Cc]];
-          if ((h_do_m >> v) & 1)
-          {
-#pragma unroll
-            for (int c = 0; c < NC; ++c) upml_cell<T, false> (bq.v[v * NC + c], hn.v[v * NC + c], curl[c], ca1, cb1, ca3, cb3, cc3);
-          }
-        }
-        else
-        {
-#pragma unroll
-          for (int c = 0; c < NC; ++c) hn.v[v * NC + c] = fma_t<T> (cb_h, curl[c], hn.v[v * NC + c]);
-        }
-      }
-      stv<T, W> (p.fo[3 + A] + o - pl, hn);
-      if (shell) stv<T, W> (p.f[9 + A] + o - pl, bq);
-    }
-    h_own_m = h_own;
-
-    if (++slot == S) { slot = 0; st = sm0; phase ^= 1u; }
-    else st += stage_sz;
-    xs = xs == 2 ? 0 : xs + 1;
-  }
-#undef SMV
-#undef SM1
-}
-
-template <typename T, int NC, bool TFSF>
-__global__ void __launch_bounds__ ((CTile<T, NC>::NTHREADS), 1)
-step_core_3d_comp (const __grid_constant__ StepParams<T> p, const __grid_constant__ FusedSet maps, const FusedBox fb)
-{
-  typedef CTile<T, NC> L;
-  constexpr int S = L::STAGES, TY = L::TY;
-  extern __shared__ unsigned char smem_raw[];
-  __shared__ __align__ (8) unsigned long long full[S];
-
-  /* warps 0 .. 3 TY - 1: row = warp / 3, component = warp % 3, lane = x vector; then the rim row (components x, z) and
-   * the rim column (components y, z; lane = row) */
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int comp, lx, ly;
-  bool valid = true;
-  if (warp < 3 * TY) { comp = warp % 3; ly = warp / 3; lx = lane; }
-  else if (warp < 3 * TY + 2) { comp = warp == 3 * TY ? 0 : 2; ly = TY; lx = lane; }
-  else { comp = warp == 3 * TY + 2 ? 1 : 2; lx = 32; ly = lane < TY ? lane : 0; valid = lane < TY; }
-  const bool leader = threadIdx.x == 0;
-
-  const int k0 = fb.fz0 + blockIdx.z * fb.kc;
-  if (k0 >= min (k0 + fb.kc, fb.fz1 + 1)) return;
-  if (leader)
-  {
-    for (int s = 0; s < S; ++s) mbar_init (&full[s], 1);
-    asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads ();
-  if (comp == 0) comp_role<T, NC, TFSF, 0> (p, maps, fb, smem_raw, full, lx, ly, valid, leader);
-  else if (comp == 1) comp_role<T, NC, TFSF, 1> (p, maps, fb, smem_raw, full, lx, ly, valid, leader);
-  else comp_role<T, NC, TFSF, 2> (p, maps, fb, smem_raw, full, lx, ly, valid, leader);
-}
-
 /* ------------------------------------------------------------------ host side */
 
 template <typename T, int NC>
@@ -987,35 +592,26 @@ bool prepare_fused_t (FusedMaps3D *out, void *const e[3], void *const h[3], void
   return ok;
 }
 
-/* which of the two kernels runs: 1 = one warp per row and component (step_core_3d_comp), 0 = all six components of a
- * cell in one thread (step_core_3d_fused) */
-#ifndef FDTD_FUSED_COMP
-#define FDTD_FUSED_COMP 1
-#endif
-
 template <typename T, int NC, bool TFSF>
 cudaError_t launch_fused_t (const StepParams<T> &p, const FusedSet &maps, const FusedBox &fb, cudaStream_t stream)
 {
   typedef FTile<T, NC> L;
-  typedef CTile<T, NC> LC;
-  const bool comp = FDTD_FUSED_COMP != 0;
-  const int smem = comp ? LC::smem_bytes (fb.nq) : L::smem_bytes (fb.nq);
+  const int smem = L::smem_bytes (fb.nq);
   static int attr_dev[64] = {};
   int dev = 0;
   cudaError_t de = cudaGetDevice (&dev);
   if (de != cudaSuccess) return de;
   if (attr_dev[dev & 63] < smem)
   {
-    cudaError_t e = comp ? cudaFuncSetAttribute (step_core_3d_comp<T, NC, TFSF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                         : cudaFuncSetAttribute (step_core_3d_fused<T, NC, TFSF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute (step_core_3d_fused<T, NC, TFSF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     attr_dev[dev & 63] = smem;
   }
   const int rows = fb.fy1 - fb.fy0 + 1, planes = fb.fz1 - fb.fz0 + 1;
   if (rows <= 0 || planes <= 0) return cudaSuccess;
+  dim3 block (L::NTHREADS);
   dim3 grid ((p.nx + L::TXC - 1) / L::TXC, rows / L::TY, (planes + fb.kc - 1) / fb.kc);
-  if (comp) step_core_3d_comp<T, NC, TFSF><<<grid, dim3 (LC::NTHREADS), smem, stream>>> (p, maps, fb);
-  else step_core_3d_fused<T, NC, TFSF><<<grid, dim3 (L::NTHREADS), smem, stream>>> (p, maps, fb);
+  step_core_3d_fused<T, NC, TFSF><<<grid, block, smem, stream>>> (p, maps, fb);
   return cudaGetLastError ();
 }
 
@@ -1024,7 +620,7 @@ cudaError_t launch_fused_t (const StepParams<T> &p, const FusedSet &maps, const 
 void fused_tile_geometry (int value_type, int nc, int *tile_cells_x, int *tile_rows, int *ctas_per_sm, int *smem_per_quarter,
                           int *smem_base)
 {
-#define GEOM(T, NC) do { typedef CTile<T, NC> L; if (tile_cells_x) *tile_cells_x = L::TXC; if (tile_rows) *tile_rows = L::TY; \
+#define GEOM(T, NC) do { typedef FTile<T, NC> L; if (tile_cells_x) *tile_cells_x = L::TXC; if (tile_rows) *tile_rows = L::TY; \
     if (ctas_per_sm) *ctas_per_sm = L::MINB; if (smem_per_quarter) *smem_per_quarter = L::smem_bytes (1) - L::smem_bytes (0); \
     if (smem_base) *smem_base = L::smem_bytes (0); } while (0)
   if (value_type == 4 && nc == 1) GEOM (float, 1);
