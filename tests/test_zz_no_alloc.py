@@ -47,6 +47,9 @@ def test_two_calls_in_a_row_match_the_handle_based_reduction(value_type):
             want = s.sumsq("Ez")  # the existing entry point, scratch from the handle's cudaMalloc
         got = _noalloc_sumsq(torch.from_numpy(field).cuda(), out, value_type)
         assert abs(got - want) <= REL_TOL * want, (size, got, want)
+        # and against the sum computed on the host, so the check does not lean on the other entry point alone
+        host = float((field.astype(np.float64) ** 2).sum())
+        assert abs(got - host) <= REL_TOL * host, (size, got, host)
 
 
 def test_sizes_beyond_the_fixed_scratch_are_refused():
