@@ -10,7 +10,10 @@
  * tests/refio.py reads.  Golden fixtures under tests/golden/ are made from these dumps by
  * tests/golden/make_golden.py.
  *
- * argv: nx ny nz pml tfsf steps use_pml use_tfsf dx wavelength theta_deg phi_deg psi_deg out.bin [dump_res]
+ * argv: nx ny nz pml tfsf steps use_pml use_tfsf dx wavelength theta_deg phi_deg psi_deg out.bin [dump_res [dat]]
+ * dat = 1 additionally saves Ez and Hy with the reference's own DATDumper (Source/File-Management/Dumper/DATDumper.h) into
+ * the current directory -- current[<steps>]_rank-0_Ez.dat, ..._Hy.dat -- so that the DAT files the product writes can be
+ * compared with files the reference wrote (tests/golden/make_golden.py keeps their bytes in the fixture).
  * dump_res = 1 constructs the scheme with doDumpRes (--save-res): the reference then turns the total field inside
  * the TF/SF box into the scattered field in place before saving (Scheme3D.cpp:2767-2921); BMP writes are stubbed.
  */
@@ -24,6 +27,7 @@
 #include "Grid.h"
 #include "PhysicsConst.h"
 #include "Settings.h"
+#include "DATDumper.h"
 #ifdef GRID_3D
 #include "Scheme3D.h"
 #endif
@@ -64,7 +68,7 @@ put_grid (const char *name, G &g)
 int
 main (int argc, char **argv)
 {
-  if (argc != 15 && argc != 16)
+  if (argc < 15 || argc > 17)
   {
     fprintf (stderr, "usage: %s nx ny nz pml tfsf steps use_pml use_tfsf dx wavelength theta phi psi out.bin\n", argv[0]);
     return 2;
@@ -78,7 +82,8 @@ main (int argc, char **argv)
   FPValue theta = (FPValue) strtod (argv[11], NULL);
   FPValue phi = (FPValue) strtod (argv[12], NULL);
   FPValue psi = (FPValue) strtod (argv[13], NULL);
-  bool dumpRes = argc == 16 && atoi (argv[15]) != 0;
+  bool dumpRes = argc >= 16 && atoi (argv[15]) != 0;
+  bool dumpDat = argc >= 17 && atoi (argv[16]) != 0;
   out = fopen (argv[14], "wb");
   if (!out) { perror ("fopen"); return 2; }
 
@@ -111,6 +116,23 @@ main (int argc, char **argv)
   gettimeofday (&tv2, NULL);
   double secs = (double) (tv2.tv_usec - tv1.tv_usec) / 1000000 + (double) (tv2.tv_sec - tv1.tv_sec);
   printf ("Total time = %f seconds\n", secs);
+
+  if (dumpDat)
+  {
+#ifdef GRID_3D
+    DATDumper<GridCoordinate3D> dat;
+    dat.init (steps, CURRENT, 0, "Ez");
+    dat.dumpGrid (scheme.Ez, GridCoordinate3D (0, 0, 0), scheme.Ez.getSize ());
+    dat.init (steps, CURRENT, 0, "Hy");
+    dat.dumpGrid (scheme.Hy, GridCoordinate3D (0, 0, 0), scheme.Hy.getSize ());
+#else
+    DATDumper<GridCoordinate2D> dat;
+    dat.init (steps, CURRENT, 0, "Ez");
+    dat.dumpGrid (scheme.Ez, GridCoordinate2D (0, 0), scheme.Ez.getSize ());
+    dat.init (steps, CURRENT, 0, "Hy");
+    dat.dumpGrid (scheme.Hy, GridCoordinate2D (0, 0), scheme.Hy.getSize ());
+#endif
+  }
 
   double scal[8];
   scal[0] = scheme.gridTimeStep;

@@ -51,6 +51,8 @@ CASES = {
     "3d_f_pml_src_core":    ("3d_f", 72, 40, 20, 4, 8, 30, 1, 0, 90, 0, 90),
     # --save-res: the reference subtracts the incident field inside the TF/SF box before saving (Scheme3D.cpp:2767-2921)
     "3d_d_pml_tfsf_saveres": ("3d_d", 30, 28, 26, 5, 8, 40, 1, 1, 70, 40, 55, "saveres"),
+    # the reference's own DATDumper writes Ez and Hy of this run: the fixture keeps the files' bytes (dat_Ez, dat_Hy)
+    "3d_d_pml_tfsf_dat":    ("3d_d", 24, 22, 20, 4, 7, 20, 1, 1, 65, 35, 50, "dat"),
 }
 DX, WAVELENGTH = "0.0005", "0.02"
 
@@ -59,15 +61,21 @@ def main():
     names = sys.argv[1:] or list(CASES)
     for name in names:
         variant, nx, ny, nz, pml, tfsf, steps, use_pml, use_tfsf, th, ph, ps = CASES[name][:12]
-        save_res = len(CASES[name]) > 12
+        save_res = len(CASES[name]) > 12 and CASES[name][12] == "saveres"
+        dump_dat = len(CASES[name]) > 12 and CASES[name][12] == "dat"
         exe = os.path.join(ROOT, "oracle", "_ref", "ref_" + variant)
         with tempfile.TemporaryDirectory() as tmp:
             out = os.path.join(tmp, "dump.bin")
             args = [exe] + [str(v) for v in (nx, ny, nz, pml, tfsf, steps, use_pml, use_tfsf)] + [DX, WAVELENGTH, str(th), str(ph), str(ps), out]
-            if save_res:
+            if save_res or dump_dat:
+                args.append("1" if save_res else "0")
+            if dump_dat:
                 args.append("1")
             subprocess.run(args, check=True, stdout=subprocess.DEVNULL, cwd=tmp)
             rec = read_records(out)
+            if dump_dat:
+                for comp in ("Ez", "Hy"):
+                    rec["dat_" + comp] = np.fromfile(os.path.join(tmp, "current[%d]_rank-0_%s.dat" % (steps, comp)), dtype=np.uint8)
         meta = dict(variant=variant, size=[nx, ny, nz], pml=pml, tfsf=tfsf, steps=steps, use_pml=use_pml,
                     use_tfsf=use_tfsf, theta=th, phi=ph, psi=ps, dx=float(DX), wavelength=float(WAVELENGTH),
                     save_res=int(save_res))

@@ -128,3 +128,12 @@ def test_cli_num_cuda_gpus_is_byte_identical_to_one_gpu(ngpus, flags, tmp_path):
         assert dumps[1][f] == dumps[ngpus][f], f
     ez = np.frombuffer(dumps[1]["current[21]_rank-0_Ez.dat"], dtype=np.float64)
     assert np.abs(ez).max() > 1e-3
+
+
+def test_cli_dat_files_equal_files_written_by_the_reference(tmp_path):
+    """--dump-dat against DAT files the reference's own DATDumper wrote for the same run (bytes kept in the fixture)."""
+    cfg, out, data = _run_cli("3d_d_pml_tfsf_dat", tmp_path, ["--exact"])
+    meta, _ = G.load("3d_d_pml_tfsf_dat")
+    for comp in ("Ez", "Hy"):
+        mine = open(str(tmp_path / ("current[%d]_rank-0_%s.dat" % (meta["steps"], comp))), "rb").read()
+        assert mine == data["dat_" + comp].tobytes(), comp

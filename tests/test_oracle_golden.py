@@ -54,3 +54,15 @@ def test_oracle_matches_the_reference_on_baseline_config_c1(name):
     assert sorted(small) == sorted(gold)
     for key, want in gold.items():
         assert np.array_equal(small[key], want), key
+
+
+def test_dat_files_written_by_the_reference_are_the_raw_cur_layer():
+    """DATDumper (Source/File-Management/Dumper/DATDumper.h:84-118) writes sizeof (FieldValue) bytes of the `cur` value per
+    cell in linear-index order, named current[<step>]_rank-<p>_<name>.dat: the bytes of two files the reference itself wrote
+    (kept in the fixture) are exactly the dumped grids.  The product's --dump-dat is compared with the same bytes on the GPU
+    (tests/test_gpu_cli.py)."""
+    meta, data = G.load("3d_d_pml_tfsf_dat")
+    for comp in ("Ez", "Hy"):
+        raw = data["dat_" + comp]
+        assert raw.dtype == np.uint8 and raw.size == data[comp].size * 8
+        assert np.array_equal(raw.view(np.float64), data[comp]), comp
