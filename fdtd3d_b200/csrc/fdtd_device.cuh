@@ -52,7 +52,6 @@ struct StepParams
    * nreg == 0: planes [kb, ke) of all tile rows, from the launch arguments; else region r covers tile rows
    * [jt0, jt0 + njt) and planes [kb, ke) in chunks of kc planes, and owns the CTAs [cta0, cta0 of region r + 1) of the
    * one-dimensional grid. */
-  int pdl;              /* host side only: launch the TMz half-step kernels with programmatic dependent launch (kernels2d.cu) */
   int nreg;
   struct Region { int jt0, njt, kb, ke, kc, cta0; } reg[5];
   const T *eps, *mu;

@@ -19,8 +19,6 @@
  * Dz / Bx / By and take the direct update E += (dt/dx) / (eps eps0) curl, as in 3D (kernels3d_tma.cu); the solver
  * folds / unfolds the D/B arrays of exactly those cells (p.core_lo/hi, x aligned to whole vectors).
  */
-#include <cstring>
-
 #include "fdtd_device.cuh"
 #include "kernels2d_common.cuh"
 #include "launch.h"
@@ -72,10 +70,6 @@ ez_phase_tmz (const __grid_constant__ StepParams<T> p)
   if (i0 >= p.nx) return;
   int j0, j1;
   if (!tmz_rows (p, j0, j1)) return;
-  /* Programmatic dependent launch (when the launch asks for it): this grid's CTAs may be scheduled while the kernel
-   * before it in the stream is still draining; nothing in global memory is touched before that kernel has completed. */
-  asm volatile ("griddepcontrol.launch_dependents;");
-  asm volatile ("griddepcontrol.wait;" ::: "memory");
 
   const long long row = (long long) p.pitch * NC;
   long long o = (p.ps + (long long) j0 * p.pitch + i0) * NC; /* plane 1 */
@@ -252,15 +246,11 @@ h_phase_tmz (const __grid_constant__ StepParams<T> p)
   typedef Vec<T, W> FVec;
   typedef Vec<T, V> MVec;
 
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) advance_step (p); /* nobody reads it in this half step */
   const int i0 = (blockIdx.x * TX + threadIdx.x) * V;
   if (i0 >= p.nx) return;
   int j0, j1;
   if (!tmz_rows (p, j0, j1)) return;
-  /* Programmatic dependent launch (when the launch asks for it): this grid's CTAs may be scheduled while the kernel
-   * before it in the stream is still draining; nothing in global memory is touched before that kernel has completed. */
-  asm volatile ("griddepcontrol.launch_dependents;");
-  asm volatile ("griddepcontrol.wait;" ::: "memory");
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) advance_step (p); /* nobody reads it in this half step */
 
   const long long row = (long long) p.pitch * NC;
   long long o = (p.ps + (long long) j0 * p.pitch + i0) * NC;
@@ -430,24 +420,17 @@ cudaError_t launch_t (bool e_phase, bool uni, const StepParams<T> &p, cudaStream
     if (total == 0) return cudaSuccess;
     grid.y = total;
   }
-  void (*kern) (const StepParams<T>) =
-    e_phase ? (uni ? ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true> : ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false>)
-            : (uni ? h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true> : h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false>);
-  cudaLaunchConfig_t cfg;
-  memset (&cfg, 0, sizeof (cfg));
-  cfg.gridDim = grid;
-  cfg.blockDim = block;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr;
-  if (p.pdl)
+  if (e_phase)
   {
-    /* the kernel may start while its predecessor drains: it waits (griddepcontrol.wait) before touching memory */
-    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr.val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = &attr;
-    cfg.numAttrs = 1;
+    if (uni) ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (pr);
+    else ez_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (pr);
   }
-  return cudaLaunchKernelEx (&cfg, kern, pr);
+  else
+  {
+    if (uni) h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, true><<<grid, block, 0, stream>>> (pr);
+    else h_phase_tmz<T, NC, PML, TFSF, EXACT, CORE, false><<<grid, block, 0, stream>>> (pr);
+  }
+  return cudaGetLastError ();
 }
 
 template <typename T, int NC>

@@ -125,7 +125,6 @@ struct fdtd_solver
   /* launch-bound grids: one step captured as a CUDA graph and replayed (run_graph); the step index then lives in
    * device memory (StepParams::step_ptr).  Any change of what a step launches invalidates the captured graph. */
   long long *step_dev;
-  bool pdl_off;           /* programmatic dependent launch of the TMz kernels could not be captured on this driver */
   cudaGraphExec_t step_graph;
   void *step_graph_src;   /* the source table the captured launches point at */
   bool step_graph_prof;
@@ -736,7 +735,6 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
   /* Small grids are launch-bound (c1: six launches of 5-25 us per step; TMz 4096^2: two of 50 us): there one step is
    * captured as a CUDA graph and replayed, which takes the per-launch overhead out of the stream.  All steps must then
    * launch identical parameters, so the step index is read from device memory and advanced by the H kernel. */
-  p.pdl = c.dims == 2 && !s->pdl_off ? 1 : 0; /* TMz: E -> H -> E ... without the launch ramp between them (kernels2d.cu) */
   const long long cells_rank = (long long) s->nx * s->ny * s->nzl;
   if (!multi && !prof && nsteps >= 8 && (c.dims == 2 || cells_rank <= (4LL << 20)) && s->step_dev)
   {
@@ -763,27 +761,15 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     if (!s->step_graph || s->step_graph_src != s->src)
     {
       if (s->step_graph) { cudaGraphExecDestroy (s->step_graph); s->step_graph = NULL; }
-      for (int attempt = 0; attempt < 2 && !s->step_graph; ++attempt)
-      {
-        cudaGraph_t g = NULL;
-        CUDA_TRY (cudaStreamBeginCapture (S, cudaStreamCaptureModeThreadLocal));
-        rc = one_step ();
-        cudaError_t ce = cudaStreamEndCapture (S, &g);
-        if (!rc && ce == cudaSuccess) ce = cudaGraphInstantiate (&s->step_graph, g, 0);
-        if (g) cudaGraphDestroy (g);
-        if (!rc && ce == cudaSuccess) break;
-        s->step_graph = NULL;
-        cudaGetLastError ();
-        if (p.pdl && attempt == 0)
-        {
-          /* programmatic edges in a captured graph need a recent driver: once more with plain launches */
-          s->pdl_off = true;
-          p.pdl = 0;
-          continue;
-        }
-        if (rc) return rc;
-        return fail (FDTD_ERROR, "capturing a time step as a CUDA graph failed: %s", cudaGetErrorString (ce));
-      }
+      cudaGraph_t g = NULL;
+      CUDA_TRY (cudaStreamBeginCapture (S, cudaStreamCaptureModeThreadLocal));
+      rc = one_step ();
+      cudaError_t ce = cudaStreamEndCapture (S, &g);
+      if (rc) { if (g) cudaGraphDestroy (g); return rc; }
+      if (ce != cudaSuccess) return fail (FDTD_ERROR, "capturing a time step failed: %s", cudaGetErrorString (ce));
+      ce = cudaGraphInstantiate (&s->step_graph, g, 0);
+      cudaGraphDestroy (g);
+      if (ce != cudaSuccess) { s->step_graph = NULL; return fail (FDTD_ERROR, "cudaGraphInstantiate failed: %s", cudaGetErrorString (ce)); }
       s->step_graph_src = s->src;
     }
     for (long long n = 1; n < nsteps; ++n) CUDA_TRY (cudaGraphLaunch (s->step_graph, S));
