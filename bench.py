@@ -294,7 +294,7 @@ def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False,
     # and small 3D grids are launch-bound (a step is a few launches of 5-50 microseconds, replayed as a CUDA graph): there
     # 4 events per step would be measured themselves and would switch the graph off, so the timed region runs without
     # them and the same K steps are repeated right afterwards with events for the per-kernel times.
-    prof_inline = w["dims"] == 3 and w["nx"] * w["ny"] * (nz_total // world) > (4 << 20)  # small 3D grids: as TMz
+    prof_inline = world == 1 and w["dims"] == 3 and w["nx"] * w["ny"] * (nz_total // world) > (4 << 20)  # small 3D grids: as TMz
     if prof_inline:
         s.set_profiling(True)
     sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
@@ -312,6 +312,21 @@ def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False,
         s.set_profiling(True)
         s.run(steps)
     e_ms, h_ms, psteps = s.phase_times()
+    breakdown = None
+    if world > 1:
+        # N > 1: the same K steps once more with nine events per step on the compute stream (fdtd_step_breakdown): where
+        # a rank's step goes -- the two waits for a neighbour's halo plane against the kernels.  Outside the timed region.
+        import torch
+        part_ms, bsteps = s.step_breakdown()
+        t = torch.tensor(part_ms if bsteps else [0.0] * 8, dtype=torch.float64, device="cuda:%d" % local) / max(bsteps, 1)
+        allp = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allp, t)
+        if bsteps:
+            breakdown = {"parts": ["incident_e", "wait_h_halo", "e_boundary_plane", "e_interior", "incident_h", "wait_e_halo",
+                                   "h_boundary_plane", "h_interior"],
+                         "ms_per_step_by_rank": [[round(float(v), 5) for v in a.tolist()] for a in allp],
+                         "note": "CUDA events on each rank's compute stream, a separate run of the same K steps right after "
+                                 "the timed one; a wait_* part is the time the stream sat behind the neighbour's plane"}
     fused_ms_total = s.fused_ms if psteps else 0.0
     s.set_profiling(False)
     peak, peak_source = _peak()
@@ -341,6 +356,8 @@ def measure(F, env, name, exact, steps, warmup, sample_clocks=False, keep=False,
             f_ms = fused_ms_total / psteps
             res.update({"one_pass_ms": f_ms, "one_pass_frac": frac(bm["alg_f"], f_ms),
                         "one_pass_frac_of_needed_bytes": frac(bm["need_f"], f_ms)})
+    if breakdown:
+        res["step_breakdown"] = breakdown
     if keep:
         return res, s, cfg
     s.close()
@@ -534,6 +551,8 @@ def main():
         roofline = {"bound": "hbm", "achieved": whole, "peak": peak, "unit": "GB/s", "frac": whole / peak, "traffic": None,
                     "peak_source": peak_source, "whole_step_frac_of_needed_bytes": res["whole_step_frac_of_needed_bytes"],
                     "kernel": "whole step per GPU (multi-rank run: boundary + interior launches overlap with the exchange)"}
+        if "step_breakdown" in res:
+            roofline["step_breakdown"] = res["step_breakdown"]
 
     # ---- end to end through the C ABI with host buffers (upload + K steps + download in the timed region)
     e2e = None

@@ -225,6 +225,12 @@ class Solver:
         _check(lib().fdtd_phase_times(self._h, C.byref(e), C.byref(h), C.byref(n)))
         return e.value, h.value, n.value
 
+    def step_breakdown(self):
+        """(ms[8], steps) of the last profiled multi-rank run (fdtd_step_breakdown)."""
+        ms, n = (C.c_float * 8)(), C.c_int64()
+        _check(lib().fdtd_step_breakdown(self._h, ms, C.byref(n)))
+        return list(ms), n.value
+
     @property
     def launch_count(self):
         n = C.c_int64()

@@ -79,6 +79,7 @@ PROTOTYPES = {
     "fdtd_get_fused_box": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "fdtd_fused_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "fdtd_set_tuning": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "fdtd_step_breakdown": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
     "fdtd_busy": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "fdtd_last_run_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "fdtd_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),

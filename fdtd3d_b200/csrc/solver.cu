@@ -132,6 +132,10 @@ struct fdtd_solver
   int fused_policy;     /* fdtd_set_tuning: 0 never, 1 wherever the geometry allows, -1 (default) where it was measured to
                            pay: complex double */
   float prof_f_ms;
+  /* multi-rank runs with profiling on: nine events per step around the eight parts of a step (fdtd_step_breakdown) */
+  std::vector<cudaEvent_t> mprof_ev;
+  long long mprof_steps;
+  float mprof_ms[8];
   bool use_tma;
   int kchunk;
 
@@ -722,6 +726,19 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     s->prof_steps = nsteps;
   }
 
+  const bool mprof = s->profiling && multi;
+  s->mprof_steps = 0;
+  if (mprof)
+  {
+    while ((long long) s->mprof_ev.size () < 9 * nsteps)
+    {
+      cudaEvent_t e;
+      CUDA_TRY (cudaEventCreate (&e));
+      s->mprof_ev.push_back (e);
+    }
+    s->mprof_steps = nsteps;
+  }
+#define MPROF(i) do { if (mprof) CUDA_TRY (cudaEventRecord (s->mprof_ev[9 * n + (i)], S)); } while (0)
   if (multi)
   {
     /* make the low H halo valid for the first E half step */
@@ -781,8 +798,10 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
   {
     /* Scheme3D::performNSteps, Scheme3D.cpp:1986-2069 (SchemeTMz.cpp:1336-1427) */
     p.step = n; /* the parameter block is passed by value with every launch */
+    MPROF (0);
     if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, exact, S)); s->launches++; }
     if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (true, p, cplx, S)); s->launches++; }
+    MPROF (1);
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
     if (c.dims == 2)
     {
@@ -795,13 +814,16 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     else
     {
       CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
+      MPROF (2);
       CUDA_TRY (phase_3d<T> (s, true, p, 0, 1, S)); s->launches++;
+      MPROF (3);
       CUDA_TRY (cudaEventRecord (s->ev_eb, S));
       CUDA_TRY (cudaStreamWaitEvent (C, s->ev_eb, 0));
       int rc = exchange (s, false, s->f);
       if (rc) return rc;
       CUDA_TRY (cudaEventRecord (s->ev_ex, C));
       if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, true, p, 1, s->nzl, S)); s->launches++; }
+      MPROF (4);
     }
 
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
@@ -818,17 +840,22 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     }
     else
     {
+      MPROF (5);
       CUDA_TRY (cudaStreamWaitEvent (S, s->ev_ex, 0));
+      MPROF (6);
       CUDA_TRY (phase_3d<T> (s, false, p, s->nzl - 1, s->nzl, S)); s->launches++;
+      MPROF (7);
       CUDA_TRY (cudaEventRecord (s->ev_hb, S));
       CUDA_TRY (cudaStreamWaitEvent (C, s->ev_hb, 0));
       int rc = exchange (s, true, s->f);
       if (rc) return rc;
       CUDA_TRY (cudaEventRecord (s->ev_hx, C));
       if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, false, p, 0, s->nzl - 1, S)); s->launches++; }
+      MPROF (8);
     }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
   }
+#undef MPROF
   if (multi) CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
   return FDTD_OK;
 }
@@ -1047,6 +1074,14 @@ static int sync_run (fdtd_solver *s)
     const int last = s->runs_pending - 1;
     CUDA_TRY (cudaEventElapsedTime (&s->last_ms, s->run_ev[2 * last], s->run_ev[2 * last + 1]));
     s->runs_pending = 0;
+    for (int i = 0; i < 8; ++i) s->mprof_ms[i] = 0;
+    for (long long n = 0; n < s->mprof_steps && !s->fused_run; ++n)
+      for (int i = 0; i < 8; ++i)
+      {
+        float d = 0;
+        CUDA_TRY (cudaEventElapsedTime (&d, s->mprof_ev[9 * n + i], s->mprof_ev[9 * n + i + 1]));
+        s->mprof_ms[i] += d;
+      }
     s->prof_e_ms = s->prof_h_ms = s->prof_f_ms = 0;
     for (long long n = 0; n < s->prof_steps; ++n)
     {
@@ -1299,7 +1334,15 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
   do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail (FDTD_ERROR, "%s failed: %s", #expr, cudaGetErrorString (e_)); fdtd_destroy (s); return FDTD_ERROR; } } while (0)
 
   CREATE_TRY (cudaStreamCreateWithFlags (&s->s_compute, cudaStreamNonBlocking));
-  CREATE_TRY (cudaStreamCreateWithFlags (&s->s_comm, cudaStreamNonBlocking));
+  {
+    /* The halo exchange runs at the highest stream priority: an interior launch fills every SM for more than a
+     * millisecond, and the send/recv kernel of the plane just computed needs an SM of its own; at equal priority it was
+     * dispatched only when the interior launch had no blocks left to place, and the next half step then waited for it
+     * (profiles/r2_scaling.md, step breakdown at 8 ranks). */
+    int prio_least = 0, prio_greatest = 0;
+    CREATE_TRY (cudaDeviceGetStreamPriorityRange (&prio_least, &prio_greatest));
+    CREATE_TRY (cudaStreamCreateWithPriority (&s->s_comm, cudaStreamNonBlocking, prio_greatest));
+  }
   s->src_ring_bytes = (size_t) 1 << 20; /* 65536 complex-double samples queued at a time */
   CREATE_TRY (cudaHostAlloc ((void **) &s->src_ring, s->src_ring_bytes, cudaHostAllocDefault));
   CREATE_TRY (cudaEventCreateWithFlags (&s->ev_eb, cudaEventDisableTiming));
@@ -1409,6 +1452,7 @@ int fdtd_destroy (fdtd_handle s)
   for (cudaEvent_t e : s->run_ev) cudaEventDestroy (e);
   if (s->src_ring) cudaFreeHost (s->src_ring);
   for (cudaEvent_t e : s->prof_ev) cudaEventDestroy (e);
+  for (cudaEvent_t e : s->mprof_ev) cudaEventDestroy (e);
   if (s->s_compute) cudaStreamDestroy (s->s_compute);
   if (s->s_comm) cudaStreamDestroy (s->s_comm);
   delete s;
@@ -1571,6 +1615,16 @@ int fdtd_phase_times (fdtd_handle s, float *e_ms, float *h_ms, int64_t *steps)
   int rc = sync_run (s);
   if (rc) return rc;
   *e_ms = s->prof_e_ms; *h_ms = s->prof_h_ms; *steps = s->prof_steps;
+  return FDTD_OK;
+}
+
+int fdtd_step_breakdown (fdtd_handle s, float ms[8], int64_t *steps)
+{
+  if (!s || !ms || !steps) return fail (FDTD_INVALID_ARGUMENT, "NULL argument");
+  int rc = sync_run (s);
+  if (rc) return rc;
+  for (int i = 0; i < 8; ++i) ms[i] = s->mprof_ms[i];
+  *steps = s->fused_run ? 0 : s->mprof_steps;
   return FDTD_OK;
 }
 

@@ -191,6 +191,14 @@ int fdtd_last_run_ms (fdtd_handle h, float *ms);
 int fdtd_set_profiling (fdtd_handle h, int enable);
 int fdtd_phase_times (fdtd_handle h, float *e_ms, float *h_ms, int64_t *steps);
 
+/* Where the time of a multi-rank step goes (nranks > 1, two half-step kernels, profiling on): summed over the steps of
+ * the last completed run, the device time between the nine events the time loop records per step on the compute
+ * stream -- ms[0] incident line + face tables (E), [1] waiting for the H halo of the rank below, [2] E boundary plane,
+ * [3] E interior, [4] incident line + face tables (H), [5] waiting for the E halo of the rank above, [6] H boundary
+ * plane, [7] H interior.  *steps = 0 when no such run was profiled.  No reference counterpart (the reference has no
+ * timing inside ParallelGrid::share, Source/Grid/ParallelGrid.cpp:1817-1823). */
+int fdtd_step_breakdown (fdtd_handle h, float ms[8], int64_t *steps);
+
 /* Number of kernels of this library launched by this handle since creation (bench.py's gpu_launches). */
 int fdtd_launch_count (fdtd_handle h, int64_t *count);
 
