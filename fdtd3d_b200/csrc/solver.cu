@@ -95,6 +95,10 @@ struct fdtd_solver
 
   cudaStream_t s_compute, s_comm;
   cudaEvent_t ev_eb, ev_ex, ev_hb, ev_hx;
+  /* 3D TF/SF with face tables: the incident line and the tables depend on no 3-D field, so they are advanced on a
+   * stream of their own, one half step ahead of the half-step kernels that read the tables (enqueue_steps) */
+  cudaStream_t s_inc = NULL;
+  cudaEvent_t ev_i0 = NULL, ev_i1 = NULL, ev_fe = NULL, ev_fh = NULL, ev_ed = NULL, ev_hd = NULL;
   std::vector<cudaEvent_t> run_ev; /* a (start, stop) pair per run queued since the last synchronisation */
   int runs_pending;
   NcclComm comm;
@@ -794,13 +798,40 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     return FDTD_OK;
   }
 
+  /* TF/SF with face tables: the incident line (EInc from HInc, HInc from EInc) and the tables made from it depend on no
+   * 3-D field.  They run on their own stream A, up to one half step ahead: the E tables of step n are written while
+   * the H kernel of step n-1 runs (they wait only for the E kernel of step n-1, their last reader), the H tables while
+   * the E kernel of step n runs.  A has the LOWEST priority: its blocks fill the SMs the running half-step kernel leaves
+   * idle in its tail (at the highest priority they displaced its blocks and the kernel lost what the overlap gained).
+   * On one stream the two small launches sat between the half-step kernels, 0.03 ms per half step of a 3.6 ms step;
+   * half of that is left (profiles/r2_scaling.md). */
+  cudaStream_t A = s->s_inc;
+  const bool side = tfsf && s->face_tab && A && c.dims == 3;
+  if (side)
+  {
+    CUDA_TRY (cudaEventRecord (s->ev_i0, S));
+    CUDA_TRY (cudaStreamWaitEvent (A, s->ev_i0, 0));
+  }
+
   for (long long n = 0; n < nsteps; ++n)
   {
     /* Scheme3D::performNSteps, Scheme3D.cpp:1986-2069 (SchemeTMz.cpp:1336-1427) */
     p.step = n; /* the parameter block is passed by value with every launch */
     MPROF (0);
-    if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, exact, S)); s->launches++; }
-    if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (true, p, cplx, S)); s->launches++; }
+    if (side)
+    {
+      CUDA_TRY (launch_incident<T> (true, p, cplx, exact, A));
+      if (n > 0) CUDA_TRY (cudaStreamWaitEvent (A, s->ev_ed, 0));
+      CUDA_TRY (launch_face_tables<T> (true, p, cplx, A));
+      CUDA_TRY (cudaEventRecord (s->ev_fe, A));
+      CUDA_TRY (cudaStreamWaitEvent (S, s->ev_fe, 0));
+      s->launches += 2;
+    }
+    else
+    {
+      if (tfsf) { CUDA_TRY (launch_incident<T> (true, p, cplx, exact, S)); s->launches++; }
+      if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (true, p, cplx, S)); s->launches++; }
+    }
     MPROF (1);
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 0], S));
     if (c.dims == 2)
@@ -827,8 +858,21 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
     }
 
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 1], S));
-    if (tfsf) { CUDA_TRY (launch_incident<T> (false, p, cplx, exact, S)); s->launches++; }
-    if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (false, p, cplx, S)); s->launches++; }
+    if (side)
+    {
+      CUDA_TRY (cudaEventRecord (s->ev_ed, S));
+      CUDA_TRY (launch_incident<T> (false, p, cplx, exact, A));
+      if (n > 0) CUDA_TRY (cudaStreamWaitEvent (A, s->ev_hd, 0));
+      CUDA_TRY (launch_face_tables<T> (false, p, cplx, A));
+      CUDA_TRY (cudaEventRecord (s->ev_fh, A));
+      CUDA_TRY (cudaStreamWaitEvent (S, s->ev_fh, 0));
+      s->launches += 2;
+    }
+    else
+    {
+      if (tfsf) { CUDA_TRY (launch_incident<T> (false, p, cplx, exact, S)); s->launches++; }
+      if (tfsf && s->face_tab) { CUDA_TRY (launch_face_tables<T> (false, p, cplx, S)); s->launches++; }
+    }
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 2], S));
     if (c.dims == 2)
     {
@@ -853,9 +897,15 @@ static int enqueue_steps (fdtd_solver *s, long long nsteps)
       if (s->nzl > 1) { CUDA_TRY (phase_3d<T> (s, false, p, 0, s->nzl - 1, S)); s->launches++; }
       MPROF (8);
     }
+    if (side) CUDA_TRY (cudaEventRecord (s->ev_hd, S));
     if (prof) CUDA_TRY (cudaEventRecord (s->prof_ev[4 * n + 3], S));
   }
 #undef MPROF
+  if (side)
+  {
+    CUDA_TRY (cudaEventRecord (s->ev_i1, A));
+    CUDA_TRY (cudaStreamWaitEvent (S, s->ev_i1, 0));
+  }
   if (multi) CUDA_TRY (cudaStreamWaitEvent (S, s->ev_hx, 0));
   return FDTD_OK;
 }
@@ -1333,7 +1383,6 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
 #define CREATE_TRY(expr) \
   do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail (FDTD_ERROR, "%s failed: %s", #expr, cudaGetErrorString (e_)); fdtd_destroy (s); return FDTD_ERROR; } } while (0)
 
-  CREATE_TRY (cudaStreamCreateWithFlags (&s->s_compute, cudaStreamNonBlocking));
   {
     /* The halo exchange runs at the highest stream priority: an interior launch fills every SM for more than a
      * millisecond, and the send/recv kernel of the plane just computed needs an SM of its own; at equal priority it was
@@ -1341,7 +1390,16 @@ int fdtd_create (const fdtd_config *cfg, fdtd_handle *out)
      * (profiles/r2_scaling.md, step breakdown at 8 ranks). */
     int prio_least = 0, prio_greatest = 0;
     CREATE_TRY (cudaDeviceGetStreamPriorityRange (&prio_least, &prio_greatest));
+    /* three levels where the device has them: exchange > half-step kernels > incident line and face tables */
+    const int prio_mid = prio_least - 1 > prio_greatest ? prio_least - 1 : prio_least;
+    CREATE_TRY (cudaStreamCreateWithPriority (&s->s_compute, cudaStreamNonBlocking, prio_mid));
     CREATE_TRY (cudaStreamCreateWithPriority (&s->s_comm, cudaStreamNonBlocking, prio_greatest));
+    if (cfg->use_tfsf && cfg->dims == 3)
+    {
+      CREATE_TRY (cudaStreamCreateWithPriority (&s->s_inc, cudaStreamNonBlocking, prio_least));
+      cudaEvent_t *ie[] = { &s->ev_i0, &s->ev_i1, &s->ev_fe, &s->ev_fh, &s->ev_ed, &s->ev_hd };
+      for (cudaEvent_t *e : ie) CREATE_TRY (cudaEventCreateWithFlags (e, cudaEventDisableTiming));
+    }
   }
   s->src_ring_bytes = (size_t) 1 << 20; /* 65536 complex-double samples queued at a time */
   CREATE_TRY (cudaHostAlloc ((void **) &s->src_ring, s->src_ring_bytes, cudaHostAllocDefault));
@@ -1447,7 +1505,7 @@ int fdtd_destroy (fdtd_handle s)
   drop_step_graph (s);
   void *ptrs[] = { s->step_dev, s->face_tab, s->eps, s->mu, s->einc, s->hinc, s->tab_mem, s->src, s->staging, s->red_partials, s->red_out };
   for (void *p : ptrs) if (p) cudaFree (p);
-  cudaEvent_t evs[] = { s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx };
+  cudaEvent_t evs[] = { s->ev_eb, s->ev_ex, s->ev_hb, s->ev_hx, s->ev_i0, s->ev_i1, s->ev_fe, s->ev_fh, s->ev_ed, s->ev_hd };
   for (cudaEvent_t e : evs) if (e) cudaEventDestroy (e);
   for (cudaEvent_t e : s->run_ev) cudaEventDestroy (e);
   if (s->src_ring) cudaFreeHost (s->src_ring);
@@ -1455,6 +1513,7 @@ int fdtd_destroy (fdtd_handle s)
   for (cudaEvent_t e : s->mprof_ev) cudaEventDestroy (e);
   if (s->s_compute) cudaStreamDestroy (s->s_compute);
   if (s->s_comm) cudaStreamDestroy (s->s_comm);
+  if (s->s_inc) cudaStreamDestroy (s->s_inc);
   delete s;
   return FDTD_OK;
 }
