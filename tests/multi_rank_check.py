@@ -74,7 +74,15 @@ def main():
                 failures += 1
                 print("rank %d case %s: the one-pass kernel was expected to be in use" % (rank, size), flush=True)
             s.run(steps - 3)
+            s.set_profiling(True)
             s.run(3)                          # a second run exercises the halo refresh at run start
+            parts, bsteps = s.step_breakdown()   # the eight parts of a rank's step (two half-step kernels only)
+            s.set_profiling(False)
+            if not (bsteps in (0, 3) and (bsteps == 3 or s.fused_box is not None) and all(v >= 0 for v in parts)
+                    and (bsteps == 0 or 0 < sum(parts) <= 1.5 * s.last_run_ms)):
+                failures += 1
+                print("rank %d case %s: step breakdown %s over %d steps (run %.3f ms)" % (rank, size, parts, bsteps, s.last_run_ms),
+                      flush=True)
             scale = {}
             for name in O.field_names(cfg):
                 scale[name[0]] = max(scale.get(name[0], 0.0), float(np.abs(ref[name]).max()))

@@ -134,3 +134,6 @@ def test_profiling_reports_both_half_steps():
         # per step: incident E, E face tables, E phase, incident H, H face tables, H phase
         assert s.launch_count - n0 == 5 * 6
         assert e_ms + h_ms <= s.last_run_ms * 1.05
+        # the eight parts of a MULTI-rank step (fdtd_step_breakdown): nothing to report for a single rank
+        parts, bsteps = s.step_breakdown()
+        assert bsteps == 0 and len(parts) == 8 and not any(parts)
