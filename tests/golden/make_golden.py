@@ -44,6 +44,13 @@ CASES = {
     "tmz_dc_pml_tfsf":      ("tmz_dc", 96, 80, 1, 8, 14, 60, 1, 1, 90, 0, 90),
     "tmz_f_pml_src":        ("tmz_f", 96, 80, 1, 8, 14, 60, 1, 0, 90, 0, 90),
     "tmz_f_pml_tfsf":       ("tmz_f", 96, 80, 1, 8, 14, 60, 1, 1, 90, 0, 90),
+    # TMz at phi = 45 degrees, the one oblique angle SchemeTMz.cpp:40-49 accepts (relPhi != 1), ragged sizes; complex point
+    # source; float and complex at oblique 3D angles
+    "tmz_d_pml_tfsf_45":     ("tmz_d", 90, 77, 1, 7, 13, 50, 1, 1, 90, 45, 90),
+    "tmz_f_pml_tfsf_45":     ("tmz_f", 90, 77, 1, 7, 13, 50, 1, 1, 90, 45, 90),
+    "tmz_dc_pml_src":        ("tmz_dc", 96, 80, 1, 8, 14, 40, 1, 0, 90, 0, 90),
+    "3d_f_pml_tfsf_angled":  ("3d_f", 30, 27, 25, 5, 8, 24, 1, 1, 55, 25, 40),
+    "3d_dc_pml_tfsf_angled": ("3d_dc", 26, 23, 22, 4, 7, 20, 1, 1, 65, 35, 50),
     # large enough for a sigma-free core box in the kernels' tile granularity: fast mode is then compared
     # with the reference itself where it skips D/B, not only with the oracle
     "3d_d_pml_tfsf_core":   ("3d_d", 48, 36, 28, 5, 9, 30, 1, 1, 60, 30, 45),

@@ -77,7 +77,8 @@ def field_rel_errs(out, ref, keys, floor=1e-9):
     The per-field figure SURVEY.md §8c asks for: every component against its OWN largest magnitude, with an absolute
     floor so that a component that is zero in exact arithmetic (nothing but rounding noise, ~1e-16 of its family) does
     not turn noise into a relative error of order one.  family_rel_errs is the bar of the tests; this one is reported
-    beside it and asserted for every component that carries signal (own maximum >= 1e-3 of the family's)."""
+    beside it and asserted for every component that carries signal (significant(): own maximum >= 1e-3 of the family's
+    in double, >= 0.05 in float)."""
     fam = {}
     for k in keys:
         fam[family(k)] = max(fam.get(family(k), 0.0), float(np.abs(ref[k]).max()))
@@ -90,8 +91,17 @@ def field_rel_errs(out, ref, keys, floor=1e-9):
     return errs
 
 
-def significant(ref, keys, frac=1e-3):
-    """The components whose own maximum is at least `frac` of their family's."""
+def significant(ref, keys, frac=None, value_type=8):
+    """The components whose own maximum is at least `frac` of their family's.
+
+    Default frac = 8 ulp / tolerance of the value type: 1e-3 in double (8 * 1.1e-16 / 1e-12), 0.05 in float
+    (8 * 6e-8 / 1e-5).  Every update adds terms of the FAMILY's magnitude (the curl of the other field), so two
+    implementations that round those terms differently differ by a few ulps of the family's scale in every component;
+    a component smaller than that fraction of its family (e.g. Ex of a plane wave whose polarisation projects 1 % onto
+    x) cannot agree to the relative tolerance of its OWN maximum in that arithmetic, whatever the implementation.
+    Such components stay under the family-relative bar of family_rel_errs."""
+    if frac is None:
+        frac = 1e-3 if value_type == 8 else 0.05
     fam = {}
     for k in keys:
         fam[family(k)] = max(fam.get(family(k), 0.0), float(np.abs(ref[k]).max()))

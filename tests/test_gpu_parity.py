@@ -50,7 +50,7 @@ def test_fast_mode_within_tolerance_of_reference_dump(name):
         assert errs[key] <= TOL[cfg.value_type], (key, errs)
     # per field, against the field's own maximum, for every component that carries signal
     own = field_rel_errs(out, data, _keys(cfg))
-    for key in significant(data, _keys(cfg)):
+    for key in significant(data, _keys(cfg), value_type=cfg.value_type):
         assert own[key] <= TOL[cfg.value_type], (key, own)
 
 
